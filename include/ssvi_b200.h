@@ -1,0 +1,194 @@
+/*
+ * ssvi_b200.h -- C ABI of the B200-native SSVI-TF hot path (libssvi_b200.so).
+ *
+ * The reference (dnguyen1196/SSVI-TF) is pure Python: it has NO FFI layer.  The boundary this
+ * library replaces is the Python method SSVI_TF.update_natural_param_batch(dim, col)
+ * (SSVI/SSVI_TF_interface.py:163-219) with its model hooks estimate_di_Di_si_batch
+ * (SSVI_TF_interface.py:222-264, SSVI_TF_robust.py:28-169, SSVI_TF_d.py:31-57,
+ * SSVI_TF_simple.py:23-40), the row updates (:595-719), update_hyper_parameter (:146-160),
+ * check_stop_cond (:967-984) and predict_entry (:1037-1059).  Every entry point below cites the
+ * reference lines it stands in for.  INTEGRATION.md shows the ctypes binding a maintainer of the
+ * reference would add.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes only.  Unless marked HOST, every pointer is a DEVICE
+ *     pointer owned by the caller; the library borrows it for the duration of the call (or, for
+ *     the bind_* calls, until rebinding / destroy) and never frees it.
+ *   - All work is enqueued on the caller's CUDA stream (`stream` = cudaStream_t passed as void*;
+ *     NULL = legacy default stream).  No call synchronises the device except ssvi_check_flags.
+ *   - Return value: 0 on success, negative SSVI_E_* otherwise; ssvi_last_error() gives the text.
+ *     No C++ exception crosses the ABI.  Device-side guards (the reference's asserts on
+ *     NaN/Inf/phi==0, SSVI_TF_interface.py:185-188, 202-205; SSVI_TF_robust.py:87-92, 106) raise
+ *     bits in a device flag word read back by ssvi_check_flags().
+ *   - One handle per host thread / GPU; a handle is not thread-safe.
+ *   - Arithmetic is IEEE fp64 (the reference computes in numpy float64).
+ *
+ * Noise contract ("identical noise draws").  The reference draws from numpy's global RNG; here the
+ * caller supplies STANDARD variates in a pool of `pool_slots` slots.  Entry number b of a row's
+ * minibatch uses slot (b mod pool_slots).  Layouts (k fastest, so 32 lanes read 32 samples):
+ *     z_other [slot][jj][c][k]   jj = other modes in ascending order, c < D, k < k1
+ *     z_own   [slot][c][k]
+ *     r_w     [slot][k]          unit Rayleigh  (ws = w_sigma^2 * r_w;  simple/robust only)
+ *     z_f     [slot][k2][k]      (fs = mean + ws * z_f;                 simple/robust only)
+ * Transforms: x = m + L z with L the lower Cholesky factor of the row covariance
+ * (diagonal covariance: x = m + sqrt(S) * z).  The oracle applies the same transform inside its
+ * patched multivariate_normal (stock NumPy uses an SVD factor).
+ */
+#ifndef SSVI_B200_H
+#define SSVI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSVI_MAX_ORDER 8
+#define SSVI_MAX_RANK 64
+
+enum { SSVI_COV_FULL = 0, SSVI_COV_DIAG = 1 };
+enum { SSVI_MODEL_D = 0, SSVI_MODEL_SIMPLE = 1, SSVI_MODEL_ROBUST = 2 };
+enum { SSVI_LIK_NORMAL = 0, SSVI_LIK_BERNOULLI = 1, SSVI_LIK_POISSON = 2 };
+enum { SSVI_UPDATE_S = 0, SSVI_UPDATE_N = 1 };
+enum { SSVI_NOISE_F64 = 0, SSVI_NOISE_F32 = 1 };
+
+enum {
+  SSVI_OK = 0,
+  SSVI_E_INVALID = -1,   /* bad argument / unsupported configuration */
+  SSVI_E_STATE = -2,     /* call order: data / state / noise not bound */
+  SSVI_E_CUDA = -3       /* CUDA runtime error (text in ssvi_last_error) */
+};
+
+/* bits of the device flag word (ssvi_check_flags) */
+enum {
+  SSVI_FLAG_NONFINITE_ACC = 1,   /* di / Di not finite          (SSVI_TF_interface.py:185-188) */
+  SSVI_FLAG_NONFINITE_COV = 2,   /* S_next not finite           (SSVI_TF_interface.py:202-204) */
+  SSVI_FLAG_PHI_ZERO = 4,        /* phi == 0 or not finite      (SSVI_TF_robust.py:87-92, 106) */
+  SSVI_FLAG_CHOL_FAIL = 8,       /* covariance not positive definite in the sampler refresh     */
+  SSVI_FLAG_EIG_NOCONV = 16      /* Jacobi eigen-iteration hit its sweep limit                  */
+};
+
+/* Constructor kwargs + hidden constants of SSVI_TF.__init__ (SSVI_TF_interface.py:21-98). */
+typedef struct SsviConfig {
+  int32_t order;            /* N = len(tensor.dims)                              (:29)  */
+  int32_t rank;             /* D                                                 (:31)  */
+  int32_t cov_kind;         /* SSVI_COV_*      `diag`                            (:36)  */
+  int32_t model;            /* SSVI_MODEL_*    SSVI_TF_d / _simple / _robust            */
+  int32_t likelihood;       /* SSVI_LIK_*      from tensor.datatype              (:59-77) */
+  int32_t k1;               /* first-layer samples                               (:50)  */
+  int32_t k2;               /* second-layer samples                              (:51)  */
+  int32_t mean_update;      /* SSVI_UPDATE_*   "S" | "N"                         (:32)  */
+  int32_t cov_update;       /* SSVI_UPDATE_*   "S" | "N"                         (:33)  */
+  int32_t noise_dtype;      /* SSVI_NOISE_*    element type of the noise pool           */
+  int32_t reserved0;
+  int32_t reserved1;
+  double eta;               /* (:85)  */
+  double cov_eta;           /* (:86)  */
+  double sigma_eta;         /* (:88)  */
+  double poisson_eta;       /* 0.1   (:87)  */
+  double min_eigenval;      /* 0.01  (:48)  */
+  double cov_floor;         /* 1e-4  self.epsilon, floor of the diagonal covariance (:80, :680) */
+  double likelihood_param;  /* s = 1 for normal (:62) */
+  int64_t dims[SSVI_MAX_ORDER];
+} SsviConfig;
+
+typedef struct SsviHandle SsviHandle;
+
+/* Length (in doubles) of one per-row / per-chunk accumulator record:
+ *   [ di (D) | Di (D*D full, D diag) | si_sum | count ]                                        */
+int64_t ssvi_acc_len(const SsviConfig* cfg);
+
+/* Bytes of dynamic state the library itself allocates for a handle (flag word only). */
+int ssvi_create(const SsviConfig* cfg /*HOST*/, SsviHandle** out /*HOST*/);
+void ssvi_destroy(SsviHandle* h);
+const char* ssvi_last_error(const SsviHandle* h); /* HOST string; h may be NULL for create errors */
+
+/* Observed TRAIN entries in COO form: Tensor.train_entries / train_vals (Tensor/Tensor.py:66-67,
+ * 117-118).  coords int32 [nnz][N] row-major, vals double [nnz]. */
+int ssvi_bind_data(SsviHandle* h, const int32_t* coords, const double* vals, int64_t nnz);
+
+/* Posterior and optimiser state, one device pointer per mode (HOST arrays of N device pointers).
+ *   params[d]        (n_d, D+1, D) full | (n_d, 2, D) diag   == Posterior.params[d] (Model/TF_Models.py:53-93)
+ *   sampler[d]       same shape; row 0 mean, rows 1..D lower Cholesky factor (diag: sqrt(S)); a cache
+ *                    the library maintains (ssvi_refresh_sampler / ssvi_row_update)
+ *   ada_mean[d]      (n_d, D)   transposed ada_acc_grad[d]      (:83, :694-698)
+ *   ada_cov[d]       (n_d, D)   transposed ada_acc_grad_cov[d]  (:41, :705-713); may be NULL for full cov
+ *   norm_changes[d]  (n_d, 2)   (:91, :722-729)
+ *   grad_norms[d]    (n_d, 2)   (:95, :199) */
+int ssvi_bind_state(SsviHandle* h, double* const* params /*HOST*/, double* const* sampler /*HOST*/,
+                    double* const* ada_mean /*HOST*/, double* const* ada_cov /*HOST*/,
+                    double* const* norm_changes /*HOST*/, double* const* grad_norms /*HOST*/);
+
+/* Noise pool (see "Noise contract").  Element type per cfg.noise_dtype.  r_w / z_f may be NULL for
+ * SSVI_MODEL_D. */
+int ssvi_bind_noise(SsviHandle* h, const void* z_other, const void* z_own, const void* r_w,
+                    const void* z_f, int32_t pool_slots);
+
+/* Recompute sampler[dim] rows from params[dim] (Cholesky / sqrt).  rows == NULL: all n_dim rows.
+ * Replaces the per-draw factorisation inside np.random.multivariate_normal at
+ * SSVI_TF_interface.py:743-745, 252-254. */
+int ssvi_refresh_sampler(SsviHandle* h, int32_t dim, const int64_t* rows, int64_t n_rows, void* stream);
+
+/* Stages 1-3 for a list of row-chunks of mode `dim`
+ * (estimate_di_Di_si_batch: SSVI_TF_interface.py:229-264 + SSVI_TF_d.py:31-57 / :562-592 +
+ *  SSVI_TF_simple.py:23-40 / SSVI_TF_robust.py:28-169).
+ * A chunk is a run of consecutive minibatch entries of ONE row:
+ *   chunk_row[c]    int32  index into rows[]
+ *   chunk_start[c]  int64  offset into entry_ids[] of the chunk's first entry
+ *   chunk_len[c]    int32  entries in the chunk (>= 1)
+ *   chunk_slot0[c]  int32  position of the chunk's first entry inside its row's minibatch
+ *                          (entry t of the chunk uses noise slot (chunk_slot0 + t) mod pool_slots)
+ *   entry_ids[]     int64  indices into the bound COO arrays (the per-mode CSR permutation of
+ *                          Tensor.find_observed_ui, Tensor/Tensor.py:251-258, or a subsample of it,
+ *                          SSVI_TF_interface.py:170-172)
+ *   rows[]          int64  row ids of mode `dim`
+ *   w_state         double[3] = { w_sigma, w_ada_grad, w_tau } (simple/robust; may be NULL for d)
+ *   partial_out     double [n_chunks][ssvi_acc_len]   UNSCALED sums over the chunk's entries */
+int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t* chunk_row,
+                    const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
+                    const int64_t* entry_ids, const int64_t* rows, const double* w_state,
+                    double* partial_out, void* stream);
+
+/* Deterministic in-order sum of the chunk records of each row:
+ *   acc_out[r] = sum_{c = row_chunk_ptr[r] .. row_chunk_ptr[r+1]-1} partial[c]
+ * acc_out double [n_rows][ssvi_acc_len] is the payload of the multi-GPU all-reduce. */
+int ssvi_reduce_chunks(SsviHandle* h, int64_t n_rows, const int64_t* row_chunk_ptr,
+                       const double* partial, double* acc_out, void* stream);
+
+/* Stage 4 for the listed rows of mode `dim`: scale = n_obs[r] / count[r] (:181-183), covariance
+ * then mean update (:191-196, 595-681, 694-713), trackers (:199, :217, 722-729), write-back (:219)
+ * and the sampler-cache rows.  Rows whose count is 0 are left untouched (:166-168).
+ *   n_obs        int64 [n_rows]   len(find_observed_ui(dim,row)) summed over all shards
+ *   pSigma       double [N]       (:56, :146-160)
+ *   time_step    cov step = cov_eta / (time_step + 1)  (:701-702)
+ *   si_out       double [n_rows]  si * scale per row, finalised per model (SSVI_TF_simple.py:39 mean,
+ *                                 SSVI_TF_robust.py:137 sum); NaN-free zero for SSVI_MODEL_D; may be NULL */
+int ssvi_row_update(SsviHandle* h, int32_t dim, int64_t n_rows, const int64_t* rows, const double* acc,
+                    const int64_t* n_obs, const double* pSigma, const double* w_state, int32_t time_step,
+                    int32_t fixed_covariance, double* si_out, void* stream);
+
+/* The scalar w_sigma recurrence replayed over the rows in list order
+ * (update_sigma_param :684-691, robust override SSVI_TF_robust.py:216-232, step :716-719).
+ * Rows with count 0 (acc record) are skipped.  w_state double[3] is updated in place. */
+int ssvi_sigma_update(SsviHandle* h, int64_t n_rows, const double* si, const double* acc,
+                      double* w_state, void* stream);
+
+/* update_hyper_parameter(dim) (:146-160) and the per-mode part of check_stop_cond (:967-984):
+ *   out[0] = sum_rows (tr S + m.m) / (n_dim * D)      (the new pSigma[dim])
+ *   out[1] = max_rows norm_changes[dim][:,0]   out[2] = max_rows norm_changes[dim][:,1] */
+int ssvi_hyper_reduce(SsviHandle* h, int32_t dim, double* out /*double[3]*/, void* stream);
+
+/* predict_entry for the posterior-mean predictor (:1039-1052): out[e] = sum_D prod_modes m.
+ * entries int32 [n][N]. */
+int ssvi_predict_mean(SsviHandle* h, const int32_t* entries, int64_t n, double* out, void* stream);
+
+/* Reads and clears the device flag word (synchronises `stream`).  flags_out HOST. */
+int ssvi_check_flags(SsviHandle* h, int32_t* flags_out /*HOST*/, void* stream);
+
+/* Library / kernel build info, e.g. "ssvi_b200 0.1 sm_100a". HOST string. */
+const char* ssvi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSVI_B200_H */

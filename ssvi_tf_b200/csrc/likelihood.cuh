@@ -1,0 +1,84 @@
+// Likelihood terms as device functions: a restatement of the reference's
+// Probability/{normal,bernoulli,poisson}.py + ProbFun.py formulas, quirks included
+// (Q5 normal snd_derivative_pdf, Q7 poisson double link, clipping floors).
+#pragma once
+#include "ssvi_common.cuh"
+
+// ProbFun.py:22-28  sigmoid(x, epsilon): 1/(1+exp(-x)), nan_to_num, clip to [eps, 1-eps]
+__device__ __forceinline__ double sigmoid_ref(double x, double eps) {
+  double r = 1.0 / (1.0 + exp(-x));
+  r = nan_to_num(r);
+  return fmin(fmax(r, eps), 1.0 - eps);
+}
+
+// ProbFun.py:52-55  poisson_link(f): log(1+exp(f)) (not log1p), nan_to_num, floor 1e-8
+__device__ __forceinline__ double poisson_link_ref(double f) {
+  double r = log(1.0 + exp(f));
+  r = nan_to_num(r);
+  return fmax(r, 1e-8);
+}
+
+// y! for integral y in [0,170] (np.math.factorial, Probability/poisson.py:23); beyond 170 the
+// reference's float division overflows to 0 as well (x / inf).
+__device__ __forceinline__ double factorial_ref(double y) {
+  int n = (int)y;
+  if (n > 170) return INFINITY;
+  double r = 1.0;
+  for (int i = 2; i <= n; ++i) r *= (double)i;   // exact in fp64 up to 22!, correctly rounded products after
+  return r;
+}
+
+// poisson.py:19-27  pdf(y, m) = max(A^y / (1+e^m) / y!, 1e-8), A = poisson_link(m)
+__device__ __forceinline__ double poisson_pdf_ref(double y, double m, double yfact) {
+  double A = poisson_link_ref(m);
+  double r = pow(A, y) / (1.0 + exp(m)) / yfact;
+  return fmax(r, 1e-8);
+}
+
+// d / simple models: first and second derivative of log p(y|f) w.r.t. f
+//   normal.py:32-36, bernoulli.py:40-51, poisson.py:70-87
+__device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, double s, double& fst,
+                                               double& snd) {
+  if (lik == SSVI_LIK_NORMAL) {
+    double is2 = 1.0 / (s * s);
+    fst = is2 * (y - f);
+    snd = -is2;
+  } else if (lik == SSVI_LIK_BERNOULLI) {
+    double yf = y * f;
+    double sp = sigmoid_ref(yf, 0.0), sm = sigmoid_ref(-yf, 0.0);
+    fst = y * sm;
+    snd = -sp * sm;
+  } else {
+    double sg = sigmoid_ref(f, 0.0);
+    double A = poisson_link_ref(f);
+    double t = y / A - 1.0;
+    fst = nan_to_num(sg * t);
+    snd = nan_to_num(sg * (1.0 - sg) * t - y * (sg * sg) / (A * A));
+  }
+}
+
+// robust model: pdf and its first / second derivative w.r.t. f
+//   normal.py:16-27, bernoulli.py:16-36, poisson.py:19-57
+__device__ __forceinline__ void pdf_derivs(int lik, double y, double f, double s, double yfact, double& p,
+                                           double& p1, double& p2) {
+  if (lik == SSVI_LIK_NORMAL) {
+    double r = (y - f) / s;
+    p = fmax(exp(-0.5 * r * r) / (2.5066282746310002 * s), 1e-5);
+    p1 = p * ((y - f) / (s * s));
+    p2 = p * (r * r - 1.0 / s);                       // Q5
+  } else if (lik == SSVI_LIK_BERNOULLI) {
+    double sg = sigmoid_ref(y * f, 1e-16);
+    p = sg;
+    p1 = (y * sg) * (1.0 - sg);
+    p2 = sg * (1.0 - sg) * (1.0 - 2.0 * sg);
+  } else {
+    double A = poisson_link_ref(f);
+    double sg = sigmoid_ref(f, 0.0);
+    double t = y / A - 1.0;
+    p = poisson_pdf_ref(y, f, yfact);
+    p1 = p * (sg * t);
+    double pl = poisson_pdf_ref(y, A, yfact);         // Q7: pdf(y, poisson_link(m))
+    double temp = -(y / (A * A)) * (sg * sg) + t * (sg * (1.0 - sg));
+    p2 = p1 * (sg * t) + pl * temp;
+  }
+}

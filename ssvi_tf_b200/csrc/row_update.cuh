@@ -1,0 +1,482 @@
+// Stage 4: the batched per-row update (one CTA per touched row, everything in shared memory).
+//
+// Reference: update_cov_param (SSVI_TF_interface.py:616-637), update_mean_param (:595-613), their
+// diagonal twins (:640-681), the AdaGrad step sizes incl. the aliasing quirk Q1 (:694-713), the
+// trackers (:199, :722-729) and the write-back (:219).
+//
+// Full covariance, cov_update "N":
+//     S+ = inv((1-rho) inv(S) + rho (I/sigma - 2 Di)),  then eigenvalues clamped at min_eigenval.
+// inv(A) and A share eigenvectors, so ONE symmetric eigendecomposition A = V diag(lam) V^T gives
+//     S+ = V diag(max(1/lam, min_eigenval)) V^T
+// which equals the reference's inv-then-eigh-clamp for every non-singular A (a negative lam gives a
+// negative eigenvalue of inv(A), which the reference clamps to min_eigenval as well).
+// inv(S) comes from the cached Cholesky factor: inv(S) = L^-T L^-1.
+#pragma once
+#include "ssvi_common.cuh"
+
+struct RowUpdateArgs {
+  int32_t D, diag, model, lik, k1;
+  int32_t mean_update, cov_update, dim, time_step, fixed_cov;
+  int32_t row_len, cov_len, acc_len;
+  double eta, cov_eta, poisson_eta, min_eigenval, cov_floor;
+  double* params;
+  double* sampler;
+  double* ada_mean;
+  double* ada_cov;
+  double* norm_changes;
+  double* grad_norms;
+  const int64_t* rows;
+  const double* acc;
+  const int64_t* n_obs;
+  const double* pSigma;
+  const double* w_state;
+  double* si_out;
+  int32_t* flags;
+};
+
+// block-wide sum; `red` holds >= 32 doubles of shared memory. All threads must call.
+__device__ __forceinline__ double block_sum(double v, double* red) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  double t = 0.0;
+  for (int i = 0; i < nw; ++i) t += red[i];   // same order in every thread: deterministic
+  return t;
+}
+
+// Cyclic two-sided Jacobi with the round-robin (tournament) parallel ordering.
+// On exit A is (numerically) diagonal with the eigenvalues on its diagonal and the columns of Vm are
+// the eigenvectors.  A, Vm: D*D doubles of shared memory; scratch: 4*(D/2+1) + 32 doubles.
+__device__ void jacobi_eigh(double* A, double* Vm, int D, double* scratch, int32_t* flags) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int n = (D + 1) & ~1;                 // players (even); index D is a bye when D is odd
+  const int np = n / 2;
+  double* cs_c = scratch;
+  double* cs_s = scratch + np;
+  int* pp = (int*)(scratch + 2 * np);
+  int* qq = pp + np;
+  double* red = scratch + 4 * (np + 1);
+  for (int i = tid; i < D * D; i += nt) Vm[i] = (i / D == i % D) ? 1.0 : 0.0;
+  __syncthreads();
+  const int max_sweeps = 30;
+  int sweep = 0;
+  for (; sweep < max_sweeps; ++sweep) {
+    double off = 0.0, tot = 0.0;
+    for (int i = tid; i < D * D; i += nt) {
+      double a = A[i];
+      tot += a * a;
+      if (i / D != i % D) off += a * a;
+    }
+    off = block_sum(off, red);
+    tot = block_sum(tot, red);
+    if (off <= 1e-30 * tot || tot == 0.0) break;
+    for (int r = 0; r < n - 1; ++r) {
+      // tournament pairing of round r: player n-1 fixed, the others rotate
+      if (tid < np) {
+        int a = (tid == 0) ? n - 1 : (r + tid) % (n - 1);
+        int b = (r + n - 1 - tid) % (n - 1);
+        int p = min(a, b), q = max(a, b);
+        double c = 1.0, s = 0.0;
+        if (q < D) {
+          double apq = A[p * D + q];
+          if (apq != 0.0) {
+            double app = A[p * D + p], aqq = A[q * D + q];
+            double tau = (aqq - app) / (2.0 * apq);
+            double t = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
+            c = 1.0 / sqrt(1.0 + t * t);
+            s = t * c;
+          }
+        } else {
+          q = -1;
+        }
+        pp[tid] = p;
+        qq[tid] = q;
+        cs_c[tid] = c;
+        cs_s[tid] = s;
+      }
+      __syncthreads();
+      // columns: A <- A J, Vm <- Vm J
+      for (int w = tid; w < np * D; w += nt) {
+        int t = w / D, i = w % D;
+        int p = pp[t], q = qq[t];
+        if (q < 0) continue;
+        double c = cs_c[t], s = cs_s[t];
+        if (s == 0.0) continue;
+        double ap = A[i * D + p], aq = A[i * D + q];
+        A[i * D + p] = c * ap - s * aq;
+        A[i * D + q] = s * ap + c * aq;
+        double vp = Vm[i * D + p], vq = Vm[i * D + q];
+        Vm[i * D + p] = c * vp - s * vq;
+        Vm[i * D + q] = s * vp + c * vq;
+      }
+      __syncthreads();
+      // rows: A <- J^T A
+      for (int w = tid; w < np * D; w += nt) {
+        int t = w / D, j = w % D;
+        int p = pp[t], q = qq[t];
+        if (q < 0) continue;
+        double c = cs_c[t], s = cs_s[t];
+        if (s == 0.0) continue;
+        double ap = A[p * D + j], aq = A[q * D + j];
+        A[p * D + j] = c * ap - s * aq;
+        A[q * D + j] = s * ap + c * aq;
+      }
+      __syncthreads();
+    }
+  }
+  if (sweep == max_sweeps && tid == 0) atomicOr(flags, SSVI_FLAG_EIG_NOCONV);
+}
+
+// In-place Cholesky of the symmetric matrix in Sx (shared, row-major) into its lower triangle;
+// the strict upper triangle is zeroed.  Returns false (in every thread) on a non-positive pivot.
+__device__ bool cholesky_lower(double* Sx, int D) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  __shared__ int ok;
+  if (tid == 0) ok = 1;
+  __syncthreads();
+  for (int j = 0; j < D; ++j) {
+    if (tid == 0) {
+      double d = Sx[j * D + j];
+      for (int k = 0; k < j; ++k) d -= Sx[j * D + k] * Sx[j * D + k];
+      if (!(d > 0.0)) {
+        ok = 0;
+        d = 1e-300;
+      }
+      Sx[j * D + j] = sqrt(d);
+    }
+    __syncthreads();
+    const double piv = Sx[j * D + j];
+    for (int i = j + 1 + tid; i < D; i += nt) {
+      double a = Sx[i * D + j];
+      for (int k = 0; k < j; ++k) a -= Sx[i * D + k] * Sx[j * D + k];
+      Sx[i * D + j] = a / piv;
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < D * D; i += nt)
+    if (i % D > i / D) Sx[i] = 0.0;
+  __syncthreads();
+  return ok != 0;
+}
+
+// AdaGrad step with the aliasing quirk Q1 (SSVI_TF_interface.py:694-698, 705-713):
+// the stored accumulator becomes acc + g^2, the step uses acc + 2 g^2.
+__device__ __forceinline__ double adagrad_step(double* acc, double g, double eta) {
+  double a = *acc, g2 = g * g;
+  *acc = a + g2;
+  return eta / sqrt(a + g2 + g2);
+}
+
+__device__ __forceinline__ double finalize_si(const RowUpdateArgs& a, double si_sum, double count,
+                                              double scale) {
+  if (a.model == SSVI_MODEL_D) return 0.0;
+  const double w = a.w_state[0];
+  double si = si_sum / ((double)a.k1 * 8.0 * w * w);
+  if (a.model == SSVI_MODEL_SIMPLE) si /= count;     // SSVI_TF_simple.py:39 mean over (B,k1)
+  return si * scale;                                  // update_sigma_param: si_acc *= scale (:685)
+}
+
+// ------------------------------------------------------------------------------------------------
+// Diagonal covariance: one thread per (row, component); blockDim.x >= D, one row per block.
+// ------------------------------------------------------------------------------------------------
+__global__ void row_update_diag_kernel(RowUpdateArgs a) {
+  __shared__ double red[32];
+  const int r = blockIdx.x, n = threadIdx.x, D = a.D;
+  const double* acc = a.acc + (int64_t)r * a.acc_len;
+  const double count = acc[D + a.cov_len + 1];
+  if (count == 0.0) return;                                   // :166-168 nothing observed
+  const int64_t row = a.rows[r];
+  const double scale = (double)a.n_obs[r] / count;            // :181
+  const double sigma = a.pSigma[a.dim];
+  const bool act = n < D;
+  double m = 0, S = 0, di = 0, Di = 0;
+  double* prow = a.params + row * a.row_len;
+  if (act) {
+    m = prow[n];
+    S = prow[D + n];
+    di = acc[n] * scale;
+    Di = acc[D + n] * scale;
+  }
+  bool bad_acc = act && !(isfinite(di) && isfinite(Di));
+  // covariance (:661-681)
+  double covGrad = 0, S_next = S;
+  if (act) {
+    if (a.cov_update == SSVI_UPDATE_S) {                       // Q8: L_next discarded
+      double L = sqrt(S);
+      covGrad = 1.0 / L - L / sigma + 2.0 * L * Di;
+      adagrad_step(a.ada_cov + row * D + n, covGrad, 1.0);
+      S_next = L * L;
+    } else {
+      covGrad = 1.0 / sigma - 2.0 * Di;
+      double eta = (a.lik == SSVI_LIK_POISSON) ? a.poisson_eta : a.eta;   // :710-713
+      double step = adagrad_step(a.ada_cov + row * D + n, covGrad, eta);
+      S_next = 1.0 / ((1.0 - step) * (1.0 / S) + step * covGrad);
+    }
+    S_next = fmax(S_next, a.cov_floor);                        // :680
+  }
+  // mean (:640-658), from the OLD S
+  double g = 0, m_next = m;
+  if (act) {
+    if (a.mean_update == SSVI_UPDATE_S) {
+      g = (1.0 - m) / sigma + di;                              // pmu = ones (:55)
+      double step = adagrad_step(a.ada_mean + row * D + n, g, a.eta);
+      m_next = m + step * g;
+    } else {
+      double C = m / S;
+      g = 1.0 / sigma + di - 2.0 * Di * m;
+      double step = adagrad_step(a.ada_mean + row * D + n, g, a.eta);
+      m_next = S * ((1.0 - step) * C + step * g);
+    }
+  }
+  bool bad_cov = act && !isfinite(S_next);
+  if (a.fixed_cov) S_next = S;                                 // :213-214
+  double gm = block_sum(g * g, red), gc = block_sum(covGrad * covGrad, red);
+  double dm = block_sum((m_next - m) * (m_next - m), red), dc = block_sum((S_next - S) * (S_next - S), red);
+  if (act) {
+    prow[n] = m_next;
+    prow[D + n] = S_next;
+    double* srow = a.sampler + row * a.row_len;
+    srow[n] = m_next;
+    srow[D + n] = sqrt(S_next);
+  }
+  if (bad_acc) atomicOr(a.flags, SSVI_FLAG_NONFINITE_ACC);
+  if (bad_cov) atomicOr(a.flags, SSVI_FLAG_NONFINITE_COV);
+  if (n == 0) {
+    a.grad_norms[row * 2 + 0] = sqrt(gm);
+    a.grad_norms[row * 2 + 1] = sqrt(gc);
+    a.norm_changes[row * 2 + 0] = sqrt(dm);
+    a.norm_changes[row * 2 + 1] = sqrt(dc);
+    if (a.si_out) a.si_out[r] = finalize_si(a, acc[D + a.cov_len], count, scale);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Full covariance: one CTA per row.  Shared memory (doubles): 5*D*D + 6*D + scratch.
+// ------------------------------------------------------------------------------------------------
+__host__ __device__ inline size_t row_update_full_doubles(int D) {
+  return (size_t)5 * D * D + 6 * D + 4 * ((D + 1) / 2 + 1) + 32;
+}
+
+__global__ void __launch_bounds__(128) row_update_full_kernel(RowUpdateArgs a) {
+  extern __shared__ double sm[];
+  const int D = a.D, DD = D * D, tid = threadIdx.x, nt = blockDim.x;
+  double* Sold = sm;             // S before the update
+  double* Lm = Sold + DD;        // cached Cholesky factor of S; later chol(S_next)
+  double* Li = Lm + DD;          // inv(L); later S_next
+  double* A = Li + DD;           // matrix handed to the eigen-solver
+  double* Vm = A + DD;           // eigenvectors
+  double* mv = Vm + DD;          // m
+  double* gv = mv + D;           // mean gradient
+  double* tv = gv + D;           // temp vector
+  double* cv = tv + D;           // C = inv(S) m
+  double* wv = cv + D;           // transformed eigenvalues
+  double* mn = wv + D;           // m_next
+  double* scratch = mn + D;
+  double* red = scratch + 4 * ((D + 1) / 2 + 1);
+
+  const int r = blockIdx.x;
+  const double* acc = a.acc + (int64_t)r * a.acc_len;
+  const double count = acc[D + DD + 1];
+  if (count == 0.0) return;                                    // :166-168
+  const int64_t row = a.rows[r];
+  const double scale = (double)a.n_obs[r] / count;             // :181
+  const double sigma = a.pSigma[a.dim];
+  const double* di = acc;
+  const double* Di = acc + D;
+  double* prow = a.params + row * a.row_len;
+  double* srow = a.sampler + row * a.row_len;
+
+  bool bad = false;
+  for (int i = tid; i < DD; i += nt) {
+    Sold[i] = prow[D + i];
+    Lm[i] = srow[D + i];
+    if (!isfinite(Di[i])) bad = true;
+  }
+  for (int i = tid; i < D; i += nt) {
+    mv[i] = prow[i];
+    if (!isfinite(di[i])) bad = true;
+  }
+  if (bad) atomicOr(a.flags, SSVI_FLAG_NONFINITE_ACC);          // :185-188
+  __syncthreads();
+
+  // inv(L): thread j solves column j by forward substitution
+  for (int j = tid; j < D; j += nt) {
+    for (int i = 0; i < j; ++i) Li[i * D + j] = 0.0;
+    Li[j * D + j] = 1.0 / Lm[j * D + j];
+    for (int i = j + 1; i < D; ++i) {
+      double s = 0.0;
+      for (int k = j; k < i; ++k) s += Lm[i * D + k] * Li[k * D + j];
+      Li[i * D + j] = -s / Lm[i * D + i];
+    }
+  }
+  __syncthreads();
+
+  double gc2 = 0.0;   // ||covGrad||_F^2 partial
+  if (a.cov_update == SSVI_UPDATE_N) {
+    const double rho = a.cov_eta / (double)(a.time_step + 1);   // :701-702
+    for (int idx = tid; idx < DD; idx += nt) {
+      const int i = idx / D, j = idx % D;
+      double p = 0.0;                                           // inv(S)[i][j] = sum_k Li[k][i] Li[k][j]
+      for (int k = max(i, j); k < D; ++k) p += Li[k * D + i] * Li[k * D + j];
+      const double cg = (i == j ? 1.0 / sigma : 0.0) - 2.0 * (scale * Di[idx]);   // :628
+      gc2 += cg * cg;
+      A[idx] = (1.0 - rho) * p + rho * cg;                      // :630 (before the outer inv)
+    }
+  } else {
+    // cov_update "S" (quirk Q8): covGrad only feeds grad_norms; S_next = L L^T, then the clamp
+    for (int idx = tid; idx < DD; idx += nt) {
+      const int i = idx / D, j = idx % D;
+      double s = 0.0;
+      for (int k = 0; k <= min(i, j); ++k) s += Lm[i * D + k] * Lm[j * D + k];
+      A[idx] = s;
+      if (j >= i) {                                             // np.triu (:621-622)
+        double ld = 0.0;
+        for (int k = 0; k <= i; ++k) ld += Lm[i * D + k] * (scale * Di[k * D + j]);
+        double cg = (i == j ? 1.0 / Lm[i * D + i] : 0.0) - (i == j ? Lm[i * D + i] / sigma : 0.0) + 2.0 * ld;
+        gc2 += cg * cg;
+      }
+    }
+  }
+  __syncthreads();
+  // symmetrise (the two triangles of A are computed by different threads in different orders)
+  for (int idx = tid; idx < DD; idx += nt) {
+    const int i = idx / D, j = idx % D;
+    if (i < j) {
+      double s = 0.5 * (A[i * D + j] + A[j * D + i]);
+      A[i * D + j] = s;
+      A[j * D + i] = s;
+    }
+  }
+  __syncthreads();
+
+  // mean gradient (needs inv(S) m for the "N" scheme) -- from the OLD m and S (:191-196, Q10)
+  if (a.mean_update == SSVI_UPDATE_N) {
+    for (int i = tid; i < D; i += nt) {                         // tv = inv(L) m
+      double s = 0.0;
+      for (int k = 0; k <= i; ++k) s += Li[i * D + k] * mv[k];
+      tv[i] = s;
+    }
+    __syncthreads();
+    for (int i = tid; i < D; i += nt) {                         // cv = inv(L)^T tv = inv(S) m   (:605)
+      double s = 0.0;
+      for (int k = i; k < D; ++k) s += Li[k * D + i] * tv[k];
+      cv[i] = s;
+    }
+    __syncthreads();
+  }
+  double gm2 = 0.0, dm2 = 0.0;
+  for (int i = tid; i < D; i += nt) {
+    double g;
+    if (a.mean_update == SSVI_UPDATE_S) {
+      g = (1.0 - mv[i]) / sigma + scale * di[i];               // :600, pmu = ones (:55)
+    } else {
+      double s = 0.0;
+      for (int k = 0; k < D; ++k) s += (scale * Di[i * D + k]) * mv[k];
+      g = 1.0 / sigma + scale * di[i] - 2.0 * s;               // :606
+    }
+    const double step = adagrad_step(a.ada_mean + row * D + i, g, a.eta);
+    gv[i] = g;
+    gm2 += g * g;
+    if (a.mean_update == SSVI_UPDATE_S) {
+      mn[i] = mv[i] + step * g;                                // :602
+    } else {
+      tv[i] = (1.0 - step) * cv[i] + step * g;                 // :608 C_next
+    }
+  }
+  __syncthreads();
+  if (a.mean_update == SSVI_UPDATE_N) {
+    for (int i = tid; i < D; i += nt) {                        // m_next = S C_next (:609)
+      double s = 0.0;
+      for (int k = 0; k < D; ++k) s += Sold[i * D + k] * tv[k];
+      mn[i] = s;
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < D; i += nt) dm2 += (mn[i] - mv[i]) * (mn[i] - mv[i]);
+
+  // eigen-decomposition + clamp (:634-636)
+  jacobi_eigh(A, Vm, D, scratch, a.flags);
+  for (int i = tid; i < D; i += nt) {
+    const double lam = A[i * D + i];
+    const double w = (a.cov_update == SSVI_UPDATE_N) ? 1.0 / lam : lam;
+    wv[i] = fmax(w, a.min_eigenval);                           // NaN -> min_eigenval, like np.maximum? no:
+    if (isnan(w)) wv[i] = w;                                   // np.maximum propagates NaN
+  }
+  __syncthreads();
+  double* Sn = Li;                                             // S_next = V diag(w) V^T
+  bool badS = false;
+  for (int idx = tid; idx < DD; idx += nt) {
+    const int i = idx / D, j = idx % D;
+    if (j > i) continue;
+    double s = 0.0;
+    for (int k = 0; k < D; ++k) s += Vm[i * D + k] * wv[k] * Vm[j * D + k];
+    if (!isfinite(s)) badS = true;
+    Sn[i * D + j] = s;
+    Sn[j * D + i] = s;
+  }
+  if (badS) atomicOr(a.flags, SSVI_FLAG_NONFINITE_COV);        // :202-204
+  __syncthreads();
+  double dc2 = 0.0;
+  if (!a.fixed_cov) {
+    for (int idx = tid; idx < DD; idx += nt) {
+      const double d = Sn[idx] - Sold[idx];
+      dc2 += d * d;
+      prow[D + idx] = Sn[idx];
+    }
+  }
+  for (int i = tid; i < D; i += nt) {
+    prow[i] = mn[i];
+    srow[i] = mn[i];
+  }
+  gm2 = block_sum(gm2, red);
+  gc2 = block_sum(gc2, red);
+  dm2 = block_sum(dm2, red);
+  dc2 = block_sum(dc2, red);
+  if (tid == 0) {
+    a.grad_norms[row * 2 + 0] = sqrt(gm2);                      // :199
+    a.grad_norms[row * 2 + 1] = sqrt(gc2);
+    a.norm_changes[row * 2 + 0] = sqrt(dm2);                    // :722-729
+    a.norm_changes[row * 2 + 1] = sqrt(dc2);
+    if (a.si_out) a.si_out[r] = finalize_si(a, acc[D + DD], count, scale);
+  }
+  if (!a.fixed_cov) {                                           // sampler cache: chol(S_next)
+    __syncthreads();
+    const bool ok = cholesky_lower(Sn, D);
+    if (!ok && tid == 0) atomicOr(a.flags, SSVI_FLAG_CHOL_FAIL);
+    for (int idx = tid; idx < DD; idx += nt) srow[D + idx] = Sn[idx];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sampler refresh: sampler row <- (mean, chol(S)) from params.  One CTA per row (full) / thread per
+// component (diag).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) refresh_sampler_full_kernel(const double* __restrict__ params,
+                                                                   double* __restrict__ sampler,
+                                                                   const int64_t* __restrict__ rows, int D,
+                                                                   int32_t* flags) {
+  extern __shared__ double sm[];
+  const int tid = threadIdx.x, nt = blockDim.x, DD = D * D, row_len = (D + 1) * D;
+  const int64_t row = rows ? rows[blockIdx.x] : (int64_t)blockIdx.x;
+  const double* p = params + row * row_len;
+  double* s = sampler + row * row_len;
+  for (int i = tid; i < DD; i += nt) sm[i] = p[D + i];
+  for (int i = tid; i < D; i += nt) s[i] = p[i];
+  __syncthreads();
+  const bool ok = cholesky_lower(sm, D);
+  if (!ok && tid == 0) atomicOr(flags, SSVI_FLAG_CHOL_FAIL);
+  for (int i = tid; i < DD; i += nt) s[D + i] = sm[i];
+}
+
+__global__ void refresh_sampler_diag_kernel(const double* __restrict__ params, double* __restrict__ sampler,
+                                            const int64_t* __restrict__ rows, int64_t n_rows, int D) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_rows * D) return;
+  const int64_t r = t / D;
+  const int n = (int)(t % D);
+  const int64_t row = rows ? rows[r] : r;
+  sampler[row * 2 * D + n] = params[row * 2 * D + n];
+  sampler[row * 2 * D + D + n] = sqrt(params[row * 2 * D + D + n]);
+}

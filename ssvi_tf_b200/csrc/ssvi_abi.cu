@@ -1,0 +1,410 @@
+// libssvi_b200.so -- C ABI (include/ssvi_b200.h) over the sm_100a kernels.
+#include <stdio.h>
+#include <string.h>
+#include <new>
+
+#include "accumulate_generic.cuh"
+#include "row_update.cuh"
+
+#define SSVI_VERSION_STR "ssvi_b200 0.1 sm_100a"
+
+static char g_create_err[512] = "";
+
+static int fail(SsviHandle* h, int code, const char* fmt, const char* detail = "") {
+  char* dst = h ? h->err : g_create_err;
+  snprintf(dst, 512, fmt, detail);
+  return code;
+}
+
+#define CUDA_TRY(h, expr)                                                                 \
+  do {                                                                                    \
+    cudaError_t e_ = (expr);                                                              \
+    if (e_ != cudaSuccess) return fail((h), SSVI_E_CUDA, #expr ": %s", cudaGetErrorString(e_)); \
+  } while (0)
+
+static inline int cov_len_of(const SsviConfig& c) { return c.cov_kind == SSVI_COV_DIAG ? c.rank : c.rank * c.rank; }
+static inline int row_len_of(const SsviConfig& c) { return c.rank + cov_len_of(c); }
+
+extern "C" const char* ssvi_version(void) { return SSVI_VERSION_STR; }
+
+extern "C" int64_t ssvi_acc_len(const SsviConfig* cfg) {
+  if (!cfg) return 0;
+  return (int64_t)cfg->rank + cov_len_of(*cfg) + 2;
+}
+
+extern "C" const char* ssvi_last_error(const SsviHandle* h) { return h ? h->err : g_create_err; }
+
+extern "C" int ssvi_create(const SsviConfig* cfg, SsviHandle** out) {
+  if (!cfg || !out) return fail(nullptr, SSVI_E_INVALID, "ssvi_create: null argument%s");
+  if (cfg->order < 2 || cfg->order > SSVI_MAX_ORDER) return fail(nullptr, SSVI_E_INVALID, "order must be in [2,8]%s");
+  if (cfg->rank < 1 || cfg->rank > SSVI_MAX_RANK) return fail(nullptr, SSVI_E_INVALID, "rank must be in [1,64]%s");
+  if (cfg->k1 < 1 || cfg->k2 < 1) return fail(nullptr, SSVI_E_INVALID, "k1, k2 must be >= 1%s");
+  if (cfg->cov_kind != SSVI_COV_FULL && cfg->cov_kind != SSVI_COV_DIAG) return fail(nullptr, SSVI_E_INVALID, "bad cov_kind%s");
+  if (cfg->model < SSVI_MODEL_D || cfg->model > SSVI_MODEL_ROBUST) return fail(nullptr, SSVI_E_INVALID, "bad model%s");
+  if (cfg->likelihood < SSVI_LIK_NORMAL || cfg->likelihood > SSVI_LIK_POISSON) return fail(nullptr, SSVI_E_INVALID, "bad likelihood%s");
+  // the reference raises Exception("Unidentified update formula ...") (SSVI_TF_interface.py:612, 632)
+  if (cfg->mean_update != SSVI_UPDATE_S && cfg->mean_update != SSVI_UPDATE_N) return fail(nullptr, SSVI_E_INVALID, "Unidentified update formula for mean param%s");
+  if (cfg->cov_update != SSVI_UPDATE_S && cfg->cov_update != SSVI_UPDATE_N) return fail(nullptr, SSVI_E_INVALID, "Unidentified update formula for covariance param%s");
+  if (cfg->noise_dtype != SSVI_NOISE_F64 && cfg->noise_dtype != SSVI_NOISE_F32) return fail(nullptr, SSVI_E_INVALID, "bad noise_dtype%s");
+  for (int d = 0; d < cfg->order; ++d)
+    if (cfg->dims[d] < 1) return fail(nullptr, SSVI_E_INVALID, "dims must be >= 1%s");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(nullptr, SSVI_E_CUDA, "no CUDA device: libssvi_b200 has no CPU fallback%s");
+  SsviHandle* h = new (std::nothrow) SsviHandle();
+  if (!h) return fail(nullptr, SSVI_E_INVALID, "out of host memory%s");
+  memset(h, 0, sizeof(*h));
+  h->cfg = *cfg;
+  h->acc_len = ssvi_acc_len(cfg);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, dev);
+  cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  cudaError_t e = cudaMalloc(&h->d_flags, sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemset(h->d_flags, 0, sizeof(int32_t));
+  if (e != cudaSuccess) {
+    fail(nullptr, SSVI_E_CUDA, "cudaMalloc(flags): %s", cudaGetErrorString(e));
+    delete h;
+    return SSVI_E_CUDA;
+  }
+  *out = h;
+  return SSVI_OK;
+}
+
+extern "C" void ssvi_destroy(SsviHandle* h) {
+  if (!h) return;
+  if (h->d_flags) cudaFree(h->d_flags);
+  delete h;
+}
+
+extern "C" int ssvi_bind_data(SsviHandle* h, const int32_t* coords, const double* vals, int64_t nnz) {
+  if (!h) return SSVI_E_INVALID;
+  if (nnz < 0 || (nnz > 0 && (!coords || !vals))) return fail(h, SSVI_E_INVALID, "bind_data: null pointer%s");
+  h->coords = coords;
+  h->vals = vals;
+  h->nnz = nnz;
+  h->data_bound = true;
+  return SSVI_OK;
+}
+
+extern "C" int ssvi_bind_state(SsviHandle* h, double* const* params, double* const* sampler,
+                               double* const* ada_mean, double* const* ada_cov, double* const* norm_changes,
+                               double* const* grad_norms) {
+  if (!h) return SSVI_E_INVALID;
+  if (!params || !sampler || !ada_mean || !norm_changes || !grad_norms)
+    return fail(h, SSVI_E_INVALID, "bind_state: null pointer array%s");
+  if (h->cfg.cov_kind == SSVI_COV_DIAG && !ada_cov) return fail(h, SSVI_E_INVALID, "bind_state: ada_cov required for diagonal covariance%s");
+  for (int d = 0; d < h->cfg.order; ++d) {
+    if (!params[d] || !sampler[d] || !ada_mean[d] || !norm_changes[d] || !grad_norms[d])
+      return fail(h, SSVI_E_INVALID, "bind_state: null device pointer%s");
+    if (h->cfg.cov_kind == SSVI_COV_DIAG && !ada_cov[d]) return fail(h, SSVI_E_INVALID, "bind_state: null ada_cov pointer%s");
+    h->params[d] = params[d];
+    h->sampler[d] = sampler[d];
+    h->ada_mean[d] = ada_mean[d];
+    h->ada_cov[d] = ada_cov ? ada_cov[d] : nullptr;
+    h->norm_changes[d] = norm_changes[d];
+    h->grad_norms[d] = grad_norms[d];
+  }
+  h->state_bound = true;
+  return SSVI_OK;
+}
+
+extern "C" int ssvi_bind_noise(SsviHandle* h, const void* z_other, const void* z_own, const void* r_w,
+                               const void* z_f, int32_t pool_slots) {
+  if (!h) return SSVI_E_INVALID;
+  if (!z_other || !z_own || pool_slots < 1) return fail(h, SSVI_E_INVALID, "bind_noise: null pointer or empty pool%s");
+  if (h->cfg.model != SSVI_MODEL_D && (!r_w || !z_f)) return fail(h, SSVI_E_INVALID, "bind_noise: r_w and z_f required for simple/robust%s");
+  h->z_other = z_other;
+  h->z_own = z_own;
+  h->r_w = r_w;
+  h->z_f = z_f;
+  h->pool_slots = pool_slots;
+  h->noise_bound = true;
+  return SSVI_OK;
+}
+
+static DevView make_view(const SsviHandle* h, int dim) {
+  DevView v;
+  memset(&v, 0, sizeof(v));
+  const SsviConfig& c = h->cfg;
+  v.N = c.order;
+  v.D = c.rank;
+  v.k1 = c.k1;
+  v.k2 = c.k2;
+  v.diag = c.cov_kind == SSVI_COV_DIAG;
+  v.model = c.model;
+  v.lik = c.likelihood;
+  v.dim = dim;
+  v.row_len = row_len_of(c);
+  v.cov_len = cov_len_of(c);
+  v.acc_len = (int32_t)h->acc_len;
+  v.pool_slots = h->pool_slots;
+  v.lik_param = c.likelihood_param;
+  v.coords = h->coords;
+  v.vals = h->vals;
+  for (int d = 0; d < c.order; ++d) v.sampler[d] = h->sampler[d];
+  v.flags = h->d_flags;
+  return v;
+}
+
+extern "C" int ssvi_refresh_sampler(SsviHandle* h, int32_t dim, const int64_t* rows, int64_t n_rows, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (!h->state_bound) return fail(h, SSVI_E_STATE, "refresh_sampler: state not bound%s");
+  if (dim < 0 || dim >= h->cfg.order) return fail(h, SSVI_E_INVALID, "refresh_sampler: bad dim%s");
+  if (!rows) n_rows = h->cfg.dims[dim];
+  if (n_rows <= 0) return SSVI_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int D = h->cfg.rank;
+  if (h->cfg.cov_kind == SSVI_COV_DIAG) {
+    const int64_t total = n_rows * D;
+    refresh_sampler_diag_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(h->params[dim], h->sampler[dim], rows, n_rows, D);
+  } else {
+    const size_t smem = (size_t)D * D * sizeof(double);
+    refresh_sampler_full_kernel<<<(unsigned)n_rows, 128, smem, st>>>(h->params[dim], h->sampler[dim], rows, D, h->d_flags);
+  }
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+template <typename ZT>
+static int launch_accumulate_generic(SsviHandle* h, const DevView& v, int64_t n_chunks, const int32_t* chunk_row,
+                                     const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
+                                     const int64_t* entry_ids, const int64_t* rows, const double* w_state,
+                                     double* partial_out, cudaStream_t st) {
+  const size_t per_warp = generic_warp_doubles(v.D, v.k1, v.row_len, v.cov_len) * sizeof(double);
+  int wpb = 4;
+  while (wpb > 1 && per_warp * wpb > (size_t)h->max_smem_optin) wpb >>= 1;
+  const size_t smem = per_warp * wpb;
+  if (smem > (size_t)h->max_smem_optin) return fail(h, SSVI_E_INVALID, "accumulate: D*k1 too large for shared memory%s");
+  auto kern = accumulate_generic_kernel<ZT>;
+  CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const unsigned grid = (unsigned)((n_chunks + wpb - 1) / wpb);
+  kern<<<grid, wpb * 32, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows,
+                                     w_state, (const ZT*)h->z_other, (const ZT*)h->z_own, (const ZT*)h->r_w,
+                                     (const ZT*)h->z_f, partial_out);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+extern "C" int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t* chunk_row,
+                               const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
+                               const int64_t* entry_ids, const int64_t* rows, const double* w_state,
+                               double* partial_out, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (!h->data_bound || !h->state_bound || !h->noise_bound) return fail(h, SSVI_E_STATE, "accumulate: bind data, state and noise first%s");
+  if (dim < 0 || dim >= h->cfg.order) return fail(h, SSVI_E_INVALID, "accumulate: bad dim%s");
+  if (n_chunks == 0) return SSVI_OK;
+  if (n_chunks < 0 || !chunk_row || !chunk_start || !chunk_len || !chunk_slot0 || !entry_ids || !rows || !partial_out)
+    return fail(h, SSVI_E_INVALID, "accumulate: null pointer%s");
+  if (h->cfg.model != SSVI_MODEL_D && !w_state) return fail(h, SSVI_E_INVALID, "accumulate: w_state required for simple/robust%s");
+  const DevView v = make_view(h, dim);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h->cfg.noise_dtype == SSVI_NOISE_F32)
+    return launch_accumulate_generic<float>(h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st);
+  return launch_accumulate_generic<double>(h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st);
+}
+
+// acc_out[r][i] = sum over the row's chunk records, in chunk order (deterministic)
+__global__ void reduce_chunks_kernel(int64_t n_rows, int acc_len, const int64_t* __restrict__ row_chunk_ptr,
+                                     const double* __restrict__ partial, double* __restrict__ acc_out) {
+  const int64_t r = blockIdx.x;
+  const int64_t c0 = row_chunk_ptr[r], c1 = row_chunk_ptr[r + 1];
+  for (int i = threadIdx.x; i < acc_len; i += blockDim.x) {
+    double s = 0.0;
+    for (int64_t c = c0; c < c1; ++c) s += partial[c * acc_len + i];
+    acc_out[r * acc_len + i] = s;
+  }
+}
+
+extern "C" int ssvi_reduce_chunks(SsviHandle* h, int64_t n_rows, const int64_t* row_chunk_ptr, const double* partial,
+                                  double* acc_out, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (n_rows == 0) return SSVI_OK;
+  if (n_rows < 0 || !row_chunk_ptr || !partial || !acc_out) return fail(h, SSVI_E_INVALID, "reduce_chunks: null pointer%s");
+  reduce_chunks_kernel<<<(unsigned)n_rows, 128, 0, (cudaStream_t)stream>>>(n_rows, (int)h->acc_len, row_chunk_ptr, partial, acc_out);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+extern "C" int ssvi_row_update(SsviHandle* h, int32_t dim, int64_t n_rows, const int64_t* rows, const double* acc,
+                               const int64_t* n_obs, const double* pSigma, const double* w_state, int32_t time_step,
+                               int32_t fixed_covariance, double* si_out, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (!h->state_bound) return fail(h, SSVI_E_STATE, "row_update: state not bound%s");
+  if (dim < 0 || dim >= h->cfg.order) return fail(h, SSVI_E_INVALID, "row_update: bad dim%s");
+  if (n_rows == 0) return SSVI_OK;
+  if (n_rows < 0 || !rows || !acc || !n_obs || !pSigma) return fail(h, SSVI_E_INVALID, "row_update: null pointer%s");
+  if (h->cfg.model != SSVI_MODEL_D && !w_state) return fail(h, SSVI_E_INVALID, "row_update: w_state required for simple/robust%s");
+  const SsviConfig& c = h->cfg;
+  RowUpdateArgs a;
+  memset(&a, 0, sizeof(a));
+  a.D = c.rank;
+  a.diag = c.cov_kind == SSVI_COV_DIAG;
+  a.model = c.model;
+  a.lik = c.likelihood;
+  a.k1 = c.k1;
+  a.mean_update = c.mean_update;
+  a.cov_update = c.cov_update;
+  a.dim = dim;
+  a.time_step = time_step;
+  a.fixed_cov = fixed_covariance;
+  a.row_len = row_len_of(c);
+  a.cov_len = cov_len_of(c);
+  a.acc_len = (int32_t)h->acc_len;
+  a.eta = c.eta;
+  a.cov_eta = c.cov_eta;
+  a.poisson_eta = c.poisson_eta;
+  a.min_eigenval = c.min_eigenval;
+  a.cov_floor = c.cov_floor;
+  a.params = h->params[dim];
+  a.sampler = h->sampler[dim];
+  a.ada_mean = h->ada_mean[dim];
+  a.ada_cov = h->ada_cov[dim];
+  a.norm_changes = h->norm_changes[dim];
+  a.grad_norms = h->grad_norms[dim];
+  a.rows = rows;
+  a.acc = acc;
+  a.n_obs = n_obs;
+  a.pSigma = pSigma;
+  a.w_state = w_state;
+  a.si_out = si_out;
+  a.flags = h->d_flags;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (a.diag) {
+    const int threads = ((c.rank + 31) / 32) * 32;
+    row_update_diag_kernel<<<(unsigned)n_rows, threads, 0, st>>>(a);
+  } else {
+    const size_t smem = row_update_full_doubles(c.rank) * sizeof(double);
+    if (smem > (size_t)h->max_smem_optin) return fail(h, SSVI_E_INVALID, "row_update: rank too large for shared memory%s");
+    CUDA_TRY(h, cudaFuncSetAttribute(row_update_full_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    row_update_full_kernel<<<(unsigned)n_rows, 128, smem, st>>>(a);
+  }
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+// update_sigma_param (SSVI_TF_interface.py:684-691; robust: SSVI_TF_robust.py:216-232) replayed in row order.
+__global__ void sigma_update_kernel(int64_t n_rows, int acc_len, int model, double sigma_eta,
+                                    const double* __restrict__ si, const double* __restrict__ acc, double* w_state) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double w_sigma = w_state[0], w_ada = w_state[1];
+  const double w_tau = w_state[2];
+  for (int64_t r = 0; r < n_rows; ++r) {
+    if (acc[r * acc_len + acc_len - 1] == 0.0) continue;
+    const double w_grad = -1.0 / (2.0 * w_tau * w_tau) + si[r];
+    w_ada += w_grad * w_grad;                                  // :716-719
+    const double w_step = sigma_eta / w_ada;
+    const double update = (1.0 - w_step) * (-0.5 / (w_sigma * w_sigma)) + w_step * w_grad;
+    const double nxt = sqrt(-0.5 / update);
+    if (model == SSVI_MODEL_ROBUST && isnan(nxt)) continue;    // SSVI_TF_robust.py:229-230
+    w_sigma = nxt;
+  }
+  w_state[0] = w_sigma;
+  w_state[1] = w_ada;
+}
+
+extern "C" int ssvi_sigma_update(SsviHandle* h, int64_t n_rows, const double* si, const double* acc, double* w_state,
+                                 void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (h->cfg.model == SSVI_MODEL_D || n_rows == 0) return SSVI_OK;
+  if (n_rows < 0 || !si || !acc || !w_state) return fail(h, SSVI_E_INVALID, "sigma_update: null pointer%s");
+  sigma_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(n_rows, (int)h->acc_len, h->cfg.model, h->cfg.sigma_eta, si, acc, w_state);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+// update_hyper_parameter (:146-160) + per-mode check_stop_cond (:967-984).  Single CTA: deterministic.
+__global__ void __launch_bounds__(1024) hyper_reduce_kernel(const double* __restrict__ params,
+                                                            const double* __restrict__ norm_changes, int64_t n_rows,
+                                                            int D, int diag, double* out) {
+  __shared__ double s_sum[32], s_m[32], s_c[32];
+  const int row_len = diag ? 2 * D : (D + 1) * D;
+  double sum = 0.0, mm = 0.0, mc = 0.0;
+  for (int64_t t = threadIdx.x; t < n_rows * D; t += blockDim.x) {
+    const int64_t r = t / D;
+    const int n = (int)(t % D);
+    const double* p = params + r * row_len;
+    const double m = p[n];
+    const double s = diag ? p[D + n] : p[D + n * D + n];
+    sum += s + m * m;
+  }
+  for (int64_t r = threadIdx.x; r < n_rows; r += blockDim.x) {
+    mm = fmax(mm, norm_changes[r * 2]);
+    mc = fmax(mc, norm_changes[r * 2 + 1]);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  sum = warp_sum(sum);
+  for (int o = 16; o > 0; o >>= 1) {
+    mm = fmax(mm, __shfl_xor_sync(0xffffffffu, mm, o));
+    mc = fmax(mc, __shfl_xor_sync(0xffffffffu, mc, o));
+  }
+  if (lane == 0) {
+    s_sum[warp] = sum;
+    s_m[warp] = mm;
+    s_c[warp] = mc;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0, a = 0.0, b = 0.0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) {
+      t += s_sum[i];
+      a = fmax(a, s_m[i]);
+      b = fmax(b, s_c[i]);
+    }
+    out[0] = t / ((double)n_rows * (double)D);
+    out[1] = a;
+    out[2] = b;
+  }
+}
+
+extern "C" int ssvi_hyper_reduce(SsviHandle* h, int32_t dim, double* out, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (!h->state_bound) return fail(h, SSVI_E_STATE, "hyper_reduce: state not bound%s");
+  if (dim < 0 || dim >= h->cfg.order || !out) return fail(h, SSVI_E_INVALID, "hyper_reduce: bad argument%s");
+  hyper_reduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(h->params[dim], h->norm_changes[dim], h->cfg.dims[dim], h->cfg.rank,
+                                                            h->cfg.cov_kind == SSVI_COV_DIAG, out);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+// predict_entry, posterior-mean predictor (:1039-1052): sum_D prod_modes m
+__global__ void predict_mean_kernel(DevView v, const double* const* params_unused, const int32_t* __restrict__ entries,
+                                    int64_t n, double* __restrict__ out, const double* p0, const double* p1,
+                                    const double* p2, const double* p3, const double* p4, const double* p5,
+                                    const double* p6, const double* p7) {
+  const double* P[SSVI_MAX_ORDER] = {p0, p1, p2, p3, p4, p5, p6, p7};
+  const int lane = threadIdx.x & 31;
+  const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (e >= n) return;
+  double s = 0.0;
+  for (int c = lane; c < v.D; c += 32) {
+    double u = 1.0;
+    for (int d = 0; d < v.N; ++d) u *= P[d][(int64_t)entries[e * v.N + d] * v.row_len + c];
+    s += u;
+  }
+  s = warp_sum(s);
+  if (lane == 0) out[e] = s;
+}
+
+extern "C" int ssvi_predict_mean(SsviHandle* h, const int32_t* entries, int64_t n, double* out, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (!h->state_bound) return fail(h, SSVI_E_STATE, "predict_mean: state not bound%s");
+  if (n == 0) return SSVI_OK;
+  if (n < 0 || !entries || !out) return fail(h, SSVI_E_INVALID, "predict_mean: null pointer%s");
+  DevView v = make_view(h, 0);
+  const int threads = 256;
+  const int64_t blocks = (n * 32 + threads - 1) / threads;
+  double** P = h->params;
+  predict_mean_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(v, nullptr, entries, n, out, P[0], P[1], P[2], P[3], P[4], P[5], P[6], P[7]);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+extern "C" int ssvi_check_flags(SsviHandle* h, int32_t* flags_out, void* stream) {
+  if (!h || !flags_out) return SSVI_E_INVALID;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(h, cudaMemcpyAsync(flags_out, h->d_flags, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(h, cudaMemsetAsync(h->d_flags, 0, sizeof(int32_t), st));
+  CUDA_TRY(h, cudaStreamSynchronize(st));
+  return SSVI_OK;
+}

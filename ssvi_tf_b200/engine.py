@@ -1,0 +1,338 @@
+"""Host-side driver of libssvi_b200: device data model + sweep plans + the C-ABI calls.
+
+PyTorch is used for device memory, streams and torch.distributed only; every computation of the hot
+path happens in the hand-written kernels behind include/ssvi_b200.h.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+MODEL_IDS = {"d": _lib.MODEL_D, "simple": _lib.MODEL_SIMPLE, "robust": _lib.MODEL_ROBUST}
+LIK_IDS = {"normal": _lib.LIK_NORMAL, "bernoulli": _lib.LIK_BERNOULLI, "poisson": _lib.LIK_POISSON}
+UPDATE_IDS = {"S": _lib.UPDATE_S, "N": _lib.UPDATE_N}
+FLAG_TEXT = {
+    _lib.FLAG_NONFINITE_ACC: "di/Di not finite (reference asserts SSVI_TF_interface.py:185-188)",
+    _lib.FLAG_NONFINITE_COV: "S_next not finite (reference asserts SSVI_TF_interface.py:202-204)",
+    _lib.FLAG_PHI_ZERO: "phi == 0 or not finite (reference asserts SSVI_TF_robust.py:87-92, 106)",
+    _lib.FLAG_CHOL_FAIL: "covariance not positive definite",
+    _lib.FLAG_EIG_NOCONV: "Jacobi eigen-iteration did not converge",
+}
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def build_csr(coords, dims):
+    """Per-mode inverted index in COO insertion order (Tensor/Tensor.py:76-83, 152-169, 251-258):
+    perm[d][rowptr[d][i]:rowptr[d][i+1]] = entries touching row i of mode d, in append order.
+    Host build (stable sort); returns lists of int64 numpy arrays."""
+    coords = np.asarray(coords)
+    rowptr, perm = [], []
+    for d, n in enumerate(dims):
+        col = coords[:, d]
+        if len(col) and (col.min() < 0 or col.max() >= n):
+            raise ValueError("coordinate out of range in mode %d" % d)
+        perm.append(np.argsort(col, kind="stable").astype(np.int64))
+        rp = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum(np.bincount(col, minlength=n), out=rp[1:])
+        rowptr.append(rp)
+    return rowptr, perm
+
+
+class NoisePool(object):
+    """The supplied standard variates (see include/ssvi_b200.h "Noise contract").
+
+    Device layouts: z_other [P][N-1][D][k1], z_own [P][D][k1], r_w [P][k1], z_f [P][k2][k1].
+    Entry number b of a row's minibatch reads slot b mod P."""
+
+    def __init__(self, z_other, z_own, r_w, z_f):
+        self.z_other, self.z_own, self.r_w, self.z_f = z_other, z_own, r_w, z_f
+        self.slots = int(z_own.shape[0])
+        self.dtype = z_own.dtype
+
+    @classmethod
+    def random(cls, slots, N, D, k1, k2, need_second_layer, device, dtype=torch.float32, seed=319):
+        g = torch.Generator(device=device)
+        g.manual_seed(seed)
+        z_other = torch.randn((slots, N - 1, D, k1), generator=g, device=device, dtype=dtype)
+        z_own = torch.randn((slots, D, k1), generator=g, device=device, dtype=dtype)
+        r_w = z_f = None
+        if need_second_layer:
+            u = torch.rand((slots, k1), generator=g, device=device, dtype=torch.float64).clamp_(min=1e-300)
+            r_w = torch.sqrt(-2.0 * torch.log(u)).to(dtype)          # unit Rayleigh
+            z_f = torch.randn((slots, k2, k1), generator=g, device=device, dtype=dtype)
+        return cls(z_other, z_own, r_w, z_f)
+
+    @classmethod
+    def from_tape(cls, tape, device, dtype=torch.float64):
+        """tape: numpy-natural layout (z_other (B,N-1,k1,D), z_own (B,k1,D), r_w (B,k1), z_f (B,k2,k1))."""
+        def dev(a, perm=None):
+            if a is None:
+                return None
+            t = torch.as_tensor(np.ascontiguousarray(a if perm is None else np.transpose(a, perm)))
+            return t.to(device=device, dtype=dtype).contiguous()
+        return cls(dev(tape.z_other, (0, 1, 3, 2)), dev(tape.z_own, (0, 2, 1)), dev(tape.r_w), dev(tape.z_f))
+
+
+class SweepPlan(object):
+    """Chunk tables for one call of ssvi_accumulate over a list of rows of one mode."""
+
+    def __init__(self, dim, rows, n_obs, entry_ids, chunk_row, chunk_start, chunk_len, chunk_slot0,
+                 row_chunk_ptr, batch_sizes):
+        self.dim = dim
+        self.rows = rows                    # int64 [n_rows] device
+        self.n_obs = n_obs                  # int64 [n_rows] device: len(find_observed_ui(dim,row))
+        self.entry_ids = entry_ids          # int64 device
+        self.chunk_row, self.chunk_start = chunk_row, chunk_start
+        self.chunk_len, self.chunk_slot0 = chunk_len, chunk_slot0
+        self.row_chunk_ptr = row_chunk_ptr  # int64 [n_rows+1] device
+        self.n_rows = int(rows.numel())
+        self.n_chunks = int(chunk_row.numel())
+        self.batch_sizes = batch_sizes      # host int64 [n_rows]: entries in each row's minibatch
+        self.n_entries = int(batch_sizes.sum())
+
+
+class Engine(object):
+    """One GPU's view of the problem: COO shard + CSR index + posterior state + noise pool."""
+
+    def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16):
+        """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
+        cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
+        if not torch.cuda.is_available():
+            raise RuntimeError("ssvi_tf_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.cfg = dict(cfg)
+        self.dims = [int(x) for x in dims]
+        self.N = len(self.dims)
+        self.D = int(cfg["D"])
+        self.diag = bool(cfg["diag"])
+        self.device = torch.device(device)
+        self.chunk_entries = int(chunk_entries)
+        self.noise_dtype = noise_dtype
+        if cfg["mean_update"] not in UPDATE_IDS or cfg["cov_update"] not in UPDATE_IDS:
+            raise Exception("Unidentified update formula for covariance param")   # SSVI_TF_interface.py:612, 632
+
+        c = _lib.SsviConfig()
+        c.order, c.rank = self.N, self.D
+        c.cov_kind = _lib.COV_DIAG if self.diag else _lib.COV_FULL
+        c.model, c.likelihood = MODEL_IDS[cfg["model"]], LIK_IDS[cfg["likelihood"]]
+        c.k1, c.k2 = int(cfg["k1"]), int(cfg["k2"])
+        c.mean_update, c.cov_update = UPDATE_IDS[cfg["mean_update"]], UPDATE_IDS[cfg["cov_update"]]
+        c.noise_dtype = _lib.NOISE_F32 if noise_dtype == torch.float32 else _lib.NOISE_F64
+        c.eta, c.cov_eta, c.sigma_eta = float(cfg["eta"]), float(cfg["cov_eta"]), float(cfg["sigma_eta"])
+        c.poisson_eta = float(cfg.get("poisson_eta", 0.1))
+        c.min_eigenval = float(cfg.get("min_eigenval", 0.01))
+        c.cov_floor = float(cfg.get("epsilon", 1e-4))
+        c.likelihood_param = float(cfg.get("likelihood_param", 1.0 if cfg["likelihood"] == "normal" else 0.0))
+        for d, n in enumerate(self.dims):
+            c.dims[d] = n
+        self._c = c
+        self.acc_len = int(self.lib.ssvi_acc_len(ctypes.byref(c)))
+        h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            rc = self.lib.ssvi_create(ctypes.byref(c), ctypes.byref(h))
+        if rc != 0:
+            raise _lib.SsviError("ssvi_create failed: %s" % self.lib.ssvi_last_error(None).decode())
+        self.h = h
+
+        # ---- data: COO + per-mode CSR -------------------------------------------------------
+        coords = np.ascontiguousarray(np.asarray(coords).reshape(-1, self.N))
+        vals = np.ascontiguousarray(np.asarray(vals, dtype=np.float64).reshape(-1))
+        self.nnz = int(vals.shape[0])
+        self.rowptr_h, perm_h = build_csr(coords, self.dims)
+        self.coords = torch.as_tensor(coords.astype(np.int32)).to(self.device)
+        self.vals = torch.as_tensor(vals).to(self.device)
+        self.perm = [torch.as_tensor(p).to(self.device) for p in perm_h]
+        self.perm_h = perm_h
+        self._call(self.lib.ssvi_bind_data, _ptr(self.coords), _ptr(self.vals), self.nnz)
+
+        # ---- state ------------------------------------------------------------------------------
+        f64 = dict(device=self.device, dtype=torch.float64)
+        rl = 2 * self.D if self.diag else (self.D + 1) * self.D
+        self.row_len = rl
+        self.params = [torch.zeros((n, rl // self.D, self.D), **f64) for n in self.dims]
+        self.sampler = [torch.zeros((n, rl // self.D, self.D), **f64) for n in self.dims]
+        self.ada_mean = [torch.ones((n, self.D), **f64) for n in self.dims]        # ada_acc_grad^T (:83)
+        self.ada_cov = [torch.zeros((n, self.D), **f64) for n in self.dims]        # ada_acc_grad_cov^T (:41)
+        self.norm_changes = [torch.zeros((n, 2), **f64) for n in self.dims]
+        self.grad_norms = [torch.zeros((n, 2), **f64) for n in self.dims]
+        self.pSigma = torch.ones((self.N,), **f64)
+        self.w_state = torch.tensor([1.0, 0.0, 1.0], **f64)                        # w_sigma, w_ada_grad, w_tau
+        self.hyper_out = torch.zeros((self.N, 3), **f64)
+        self.time_step = [0] * self.N
+        self._bind_state()
+        self.noise = None
+        self._full_plans = {}
+        self._scratch = {}
+        self.launches = 0          # kernels of libssvi_b200 launched through this engine
+
+    # -------------------------------------------------------------------------------------------
+    def _call(self, fn, *args):
+        with torch.cuda.device(self.device):
+            rc = fn(self.h, *args)
+        _lib.check(self.lib, self.h, rc)
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _bind_state(self):
+        def arr(lst):
+            a = (ctypes.c_void_p * self.N)()
+            for d, t in enumerate(lst):
+                a[d] = t.data_ptr()
+            return a
+        self._call(self.lib.ssvi_bind_state, arr(self.params), arr(self.sampler), arr(self.ada_mean),
+                   arr(self.ada_cov), arr(self.norm_changes), arr(self.grad_norms))
+
+    def close(self):
+        if getattr(self, "h", None) is not None:
+            self.lib.ssvi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -------------------------------------------------------------------------------------------
+    def set_noise(self, pool):
+        need2 = self.cfg["model"] != "d"
+        assert pool.z_other.shape[1:] == (self.N - 1, self.D, self.cfg["k1"]), pool.z_other.shape
+        assert pool.z_own.shape[1:] == (self.D, self.cfg["k1"])
+        if need2:
+            assert pool.r_w.shape[1:] == (self.cfg["k1"],) and pool.z_f.shape[1:] == (self.cfg["k2"], self.cfg["k1"])
+        want = torch.float32 if self._c.noise_dtype == _lib.NOISE_F32 else torch.float64
+        assert pool.dtype == want, "noise pool dtype %s does not match the engine's noise_dtype" % pool.dtype
+        self.noise = pool
+        self._call(self.lib.ssvi_bind_noise, _ptr(pool.z_other), _ptr(pool.z_own),
+                   _ptr(pool.r_w if need2 else None), _ptr(pool.z_f if need2 else None), pool.slots)
+
+    def refresh_sampler(self, dim=None, rows=None):
+        dims = range(self.N) if dim is None else [dim]
+        for d in dims:
+            n = 0 if rows is None else int(rows.numel())
+            self._call(self.lib.ssvi_refresh_sampler, d, _ptr(rows), n, self._stream())
+            self.launches += 1
+
+    def check_flags(self):
+        """Mirror of the reference's in-line asserts: raises AssertionError when a guard fired."""
+        f = ctypes.c_int32(0)
+        self._call(self.lib.ssvi_check_flags, ctypes.byref(f), self._stream())
+        if f.value:
+            raise AssertionError("; ".join(t for b, t in FLAG_TEXT.items() if f.value & b))
+
+    # -------------------------------------------------------------------------------------------
+    def _chunk_tables(self, dim, rows_h, seg_start, seg_len):
+        """rows_h: host int64 row ids; seg_start/seg_len: each row's minibatch as a run of entry_ids."""
+        W = self.chunk_entries
+        nch = (seg_len + W - 1) // W
+        rcp = np.zeros(len(rows_h) + 1, dtype=np.int64)
+        np.cumsum(nch, out=rcp[1:])
+        total = int(rcp[-1])
+        chunk_row = np.repeat(np.arange(len(rows_h), dtype=np.int64), nch)
+        t = np.arange(total, dtype=np.int64) - rcp[chunk_row]
+        chunk_start = seg_start[chunk_row] + t * W
+        chunk_len = np.minimum(W, seg_len[chunk_row] - t * W)
+        dev = self.device
+        return (torch.as_tensor(chunk_row.astype(np.int32)).to(dev), torch.as_tensor(chunk_start).to(dev),
+                torch.as_tensor(chunk_len.astype(np.int32)).to(dev), torch.as_tensor((t * W).astype(np.int32)).to(dev),
+                torch.as_tensor(rcp).to(dev))
+
+    def plan_full(self, dim, rows=None):
+        """Every observed entry of every listed row (scale = 1): the throughput sweep."""
+        key = (dim, None if rows is None else tuple(int(r) for r in rows))
+        if key in self._full_plans:
+            return self._full_plans[key]
+        rows_h = np.arange(self.dims[dim], dtype=np.int64) if rows is None else np.asarray(rows, dtype=np.int64)
+        rp = self.rowptr_h[dim]
+        seg_start, seg_len = rp[rows_h], rp[rows_h + 1] - rp[rows_h]
+        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len)
+        plan = SweepPlan(dim, torch.as_tensor(rows_h).to(self.device), torch.as_tensor(seg_len).to(self.device),
+                         self.perm[dim], tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
+        self._full_plans[key] = plan
+        return plan
+
+    def plan_minibatch(self, dim, rows, batch_size, rng=None, sub_idx=None):
+        """The reference's minibatch (SSVI_TF_interface.py:170-174): rows holding more than batch_size
+        entries are subsampled without replacement.  sub_idx: optional {row: index array} (noise-tape
+        item #0) overriding the draw; rng: numpy Generator otherwise."""
+        rows_h = np.asarray(rows, dtype=np.int64)
+        rp = self.rowptr_h[dim]
+        lens = rp[rows_h + 1] - rp[rows_h]
+        if not np.any(lens > batch_size):
+            return self.plan_full(dim, rows_h)
+        ids, seg_len = [], np.minimum(lens, batch_size)
+        for r, row in enumerate(rows_h):
+            seg = self.perm_h[dim][rp[row]:rp[row + 1]]
+            if lens[r] > batch_size:
+                if sub_idx is not None and int(row) in sub_idx:
+                    pick = np.asarray(sub_idx[int(row)], dtype=np.int64)
+                else:
+                    pick = (rng or np.random).choice(int(lens[r]), batch_size, replace=False)
+                seg = seg[pick]
+            ids.append(seg)
+        seg_start = np.zeros(len(rows_h), dtype=np.int64)
+        np.cumsum(seg_len[:-1], out=seg_start[1:])
+        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len)
+        entry_ids = torch.as_tensor(np.concatenate(ids) if ids else np.zeros(0, np.int64)).to(self.device)
+        return SweepPlan(dim, torch.as_tensor(rows_h).to(self.device), torch.as_tensor(lens).to(self.device),
+                         entry_ids, tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
+
+    # -------------------------------------------------------------------------------------------
+    def _buf(self, name, numel):
+        t = self._scratch.get(name)
+        if t is None or t.numel() < numel:
+            t = torch.empty((max(numel, 1),), device=self.device, dtype=torch.float64)
+            self._scratch[name] = t
+        return t
+
+    def accumulate(self, plan):
+        """Stages 1-3 + in-order chunk reduction -> acc [n_rows, acc_len] (a view of a scratch buffer)."""
+        assert self.noise is not None, "set_noise() first"
+        partial = self._buf("partial", plan.n_chunks * self.acc_len)
+        acc = self._buf("acc", plan.n_rows * self.acc_len)
+        st = self._stream()
+        self._call(self.lib.ssvi_accumulate, plan.dim, plan.n_chunks, _ptr(plan.chunk_row), _ptr(plan.chunk_start),
+                   _ptr(plan.chunk_len), _ptr(plan.chunk_slot0), _ptr(plan.entry_ids), _ptr(plan.rows),
+                   _ptr(self.w_state), _ptr(partial), st)
+        self._call(self.lib.ssvi_reduce_chunks, plan.n_rows, _ptr(plan.row_chunk_ptr), _ptr(partial), _ptr(acc), st)
+        self.launches += 2 if plan.n_chunks else 0
+        return acc[:plan.n_rows * self.acc_len].view(plan.n_rows, self.acc_len)
+
+    def row_update(self, plan, acc, fixed_covariance=False, n_obs=None):
+        """Stage 4 + the w_sigma recurrence for the plan's rows."""
+        si = self._buf("si", plan.n_rows)
+        st = self._stream()
+        n_obs = plan.n_obs if n_obs is None else n_obs
+        self._call(self.lib.ssvi_row_update, plan.dim, plan.n_rows, _ptr(plan.rows), _ptr(acc), _ptr(n_obs),
+                   _ptr(self.pSigma), _ptr(self.w_state), int(self.time_step[plan.dim]), int(bool(fixed_covariance)),
+                   _ptr(si), st)
+        self.launches += 1 if plan.n_rows else 0
+        if self.cfg["model"] != "d":
+            self._call(self.lib.ssvi_sigma_update, plan.n_rows, _ptr(si), _ptr(acc), _ptr(self.w_state), st)
+            self.launches += 1 if plan.n_rows else 0
+
+    def step(self, plan, fixed_covariance=False):
+        """update_natural_param_batch for every row of the plan, from one state snapshot."""
+        acc = self.accumulate(plan)
+        self.row_update(plan, acc, fixed_covariance)
+
+    def hyper_reduce(self, dim):
+        """update_hyper_parameter(dim) (:146-160): refreshes pSigma[dim]; also leaves the mode's maximum
+        mean / covariance change in hyper_out[dim, 1:3] for check_stop_cond (:967-984)."""
+        self._call(self.lib.ssvi_hyper_reduce, dim, _ptr(self.hyper_out[dim]), self._stream())
+        self.pSigma[dim:dim + 1].copy_(self.hyper_out[dim, 0:1])
+        self.launches += 1
+
+    def predict_mean(self, entries):
+        """entries: int32 device tensor [n, N] -> posterior-mean prediction per entry."""
+        n = int(entries.shape[0])
+        out = torch.empty((n,), device=self.device, dtype=torch.float64)
+        self._call(self.lib.ssvi_predict_mean, _ptr(entries), n, _ptr(out), self._stream())
+        self.launches += 1 if n else 0
+        return out

@@ -1,0 +1,130 @@
+"""GPU: the CUDA path (through the C ABI) against the golden fixtures (reference outputs) and against
+the oracle on seeded inputs.  Parity bar (BASELINE.json): fp64, 1e-5 relative on the updated means and
+covariances; row ids / counts bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ssvi_oracle as so
+from tests.helpers import (assert_state_close, engine_dump_state, engine_load_state, golden_cases, load_golden,
+                           random_problem, random_state)
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+def _engine(cfg, dims, coords, vals, noise_dtype=torch.float64, chunk_entries=4):
+    from ssvi_tf_b200.engine import Engine
+    return Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=noise_dtype, chunk_entries=chunk_entries)
+
+
+@pytest.mark.parametrize("noise_dtype", [torch.float64, torch.float32])
+@pytest.mark.parametrize("name", golden_cases())
+def test_cuda_matches_reference_golden(name, noise_dtype):
+    from ssvi_tf_b200.engine import NoisePool
+    case = load_golden(name)
+    cfg, dims = case["cfg"], case["dims"]
+    eng = _engine(cfg, dims, case["coords"], case["vals"], noise_dtype)
+    for k, step in enumerate(case["steps"]):
+        engine_load_state(eng, case["state0"])
+        dim, row, tape = step["dim"], step["row"], step["tape"]
+        eng.set_noise(NoisePool.from_tape(tape, eng.device, noise_dtype))
+        sub = None if tape.sub_idx is None else {row: tape.sub_idx}
+        plan = eng.plan_minibatch(dim, [row], cfg["batch_size"], sub_idx=sub)
+        # touched rows / counts are integers: exact
+        assert plan.n_rows == 1 and int(plan.batch_sizes[0]) == tape.z_own.shape[0]
+        eng.step(plan, fixed_covariance=case["state0"]["fixed_covariance"])
+        eng.check_flags()
+        got = engine_dump_state(eng, case["state0"])
+        assert_state_close(got, step["after"], cfg, RTOL, what="%s step %d" % (name, k))
+    eng.close()
+
+
+@pytest.mark.parametrize("model,lik,diag", [("d", "normal", False), ("simple", "bernoulli", False),
+                                            ("robust", "poisson", False), ("simple", "normal", True),
+                                            ("robust", "bernoulli", True), ("d", "poisson", True)])
+def test_cuda_batched_rows_match_oracle(model, lik, diag):
+    """A whole mode (all rows, ragged lengths incl. empty rows) in ONE launch == the oracle's
+    rows_step (the equivalence class of SURVEY.md 8b)."""
+    from ssvi_tf_b200.engine import NoisePool
+    rng = np.random.default_rng(11)
+    dims, D, k1, k2, B = [9, 7, 6], 7, 16, 8, 8
+    cfg = so.make_config(model, lik, D, diag=diag, k1=k1, k2=k2, batch_size=B)
+    coords, vals = random_problem(rng, lik, dims, 150)
+    coords = coords[coords[:, 0] != 3]                 # leave row 3 of mode 0 empty
+    vals = vals[:len(coords)]
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    eng = _engine(cfg, dims, coords, vals, chunk_entries=3)
+    pool = so.make_tape(rng, cfg, 3, B)                # B slots: entry b of every row uses slot b
+    eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64))
+    for dim in range(3):
+        engine_load_state(eng, st0)
+        rows = np.arange(dims[dim])
+        sub, entries, tapes = {}, [], []
+        for row in rows:
+            ids = perm[dim][rowptr[dim][row]:rowptr[dim][row + 1]]
+            n = len(ids)
+            t = so.Tape(pool.z_other[:min(n, B)], pool.z_own[:min(n, B)], pool.r_w[:min(n, B)], pool.z_f[:min(n, B)])
+            if n > B:
+                t.sub_idx = rng.choice(n, B, replace=False)
+                sub[int(row)] = t.sub_idx
+            entries.append((coords[ids], vals[ids]))
+            tapes.append(t)
+        plan = eng.plan_minibatch(dim, rows, B, sub_idx=sub)
+        eng.step(plan)
+        eng.check_flags()
+        want = so.copy_state(st0)
+        touched = so.rows_step(want, cfg, dim, rows, entries, tapes)
+        got = engine_dump_state(eng, st0)
+        assert_state_close(got, want, cfg, RTOL, what="mode %d" % dim)
+        # bit-exact bookkeeping: which rows were touched, and how many entries each consumed
+        acc = eng._scratch["acc"][:plan.n_rows * eng.acc_len].view(plan.n_rows, eng.acc_len).cpu().numpy()
+        counts = acc[:, -1].astype(np.int64)
+        assert [int(r) for r in rows[counts > 0]] == touched
+        want_counts = np.minimum(np.diff(rowptr[dim]), B)
+        np.testing.assert_array_equal(counts, want_counts)
+        if dim == 0:
+            assert counts[3] == 0
+            np.testing.assert_array_equal(got["params"][0][3], st0["params"][0][3])
+        # hyper-parameter + stop-condition reductions
+        eng.hyper_reduce(dim)
+        so.update_hyper_parameter(want, cfg, dim)
+        np.testing.assert_allclose(eng.pSigma.cpu().numpy()[dim], want["pSigma"][dim], rtol=1e-12)
+        ho = eng.hyper_out[dim].cpu().numpy()
+        np.testing.assert_allclose(ho[1:], want["norm_changes"][dim].max(axis=0), rtol=RTOL)
+    eng.close()
+
+
+def test_full_row_sweep_chunking_is_invariant():
+    """Splitting rows into chunks of different sizes changes only the summation order."""
+    from ssvi_tf_b200.engine import NoisePool
+    rng = np.random.default_rng(3)
+    dims, D = [5, 40, 30], 6
+    cfg = so.make_config("d", "normal", D, k1=32, k2=4, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, "normal", dims, 900)
+    st0 = random_state(rng, cfg, dims)
+    outs = []
+    for ce in (1, 7, 64):
+        eng = _engine(cfg, dims, coords, vals, chunk_entries=ce)
+        eng.set_noise(NoisePool.random(16, 3, D, 32, 4, False, eng.device, torch.float64, seed=1))
+        engine_load_state(eng, st0)
+        acc = eng.accumulate(eng.plan_full(0)).cpu().numpy().copy()
+        outs.append(acc)
+        eng.close()
+    np.testing.assert_allclose(outs[1], outs[0], rtol=1e-11, atol=1e-12)
+    np.testing.assert_allclose(outs[2], outs[0], rtol=1e-11, atol=1e-12)
+    np.testing.assert_array_equal(outs[0][:, -1], np.bincount(coords[:, 0], minlength=5))
+
+
+def test_predict_mean_matches_oracle():
+    rng = np.random.default_rng(4)
+    dims, D = [6, 5, 4, 3], 9
+    cfg = so.make_config("d", "normal", D, diag=True, k1=8, k2=4)
+    coords, vals = random_problem(rng, "normal", dims, 100)
+    st0 = random_state(rng, cfg, dims)
+    eng = _engine(cfg, dims, coords, vals)
+    engine_load_state(eng, st0)
+    got = eng.predict_mean(eng.coords).cpu().numpy()
+    np.testing.assert_allclose(got, so.predict_mean(st0, coords), rtol=1e-12)
+    eng.close()
