@@ -1,0 +1,393 @@
+#!/usr/bin/env python
+"""bench.py -- observed-entry SVI updates/s of the SSVI-TF hot path on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--config c2] [--impl b200|reference]
+
+A "step" is one full pass of the hot path over the workload: for every mode, stages 1-4 over every
+observed TRAIN entry of every row (a Jacobi sweep, scale = 1) + the hyper-parameter reduction.  One
+(entry, mode) contribution = one unit, so a step processes N * nnz_train units per GPU.
+N > 1 (torchrun): observed entries are sharded by rank (weak scaling: every rank holds its own
+nnz_train entries of the same index space), per-row accumulators are all-reduced over NCCL.
+
+Prints ONE JSON line (rank 0).  --impl reference times the CPU oracle port (the reference is pure
+Python and cannot travel to the GPU box; the oracle is its numpy restatement, pinned to the reference
+by tests/golden) on all host cores.
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "observed_entry_svi_updates_per_sec"
+UNIT = "entry-updates/s"
+
+# BASELINE.json configs (sizes per GPU).  nnz = observed entries, 80 % of which are TRAIN entries.
+CONFIGS = {
+    "c1": dict(dims=[50, 50, 50], nnz=125000, D=10, lik="normal", model="d", diag=False, k1=64, k2=128,
+               desc="synthetic_test.py real 50x50x50 dense, D=10, normal, SSVI_TF_d full cov"),
+    "c2": dict(dims=[1000, 1000, 1000], nnz=10_000_000, D=20, lik="bernoulli", model="d", diag=False, k1=64, k2=64,
+               desc="binary 1000^3 at 1% density, D=20, bernoulli, SSVI_TF_d full cov"),
+    "c3": dict(dims=[2000, 2000, 300], nnz=100_000_000, D=30, lik="poisson", model="robust", diag=False, k1=64,
+               k2=64, cov_eta=0.001, desc="count 2000x2000x300, 1e8 nnz, D=30, poisson, SSVI_TF_robust full cov"),
+    "c4": dict(dims=[500, 500, 500, 100], nnz=100_000_000, D=50, lik="normal", model="simple", diag=True, k1=64,
+               k2=64, desc="real 500x500x500x100, 1e8 nnz, D=50, normal, SSVI_TF_simple diag cov"),
+    "c5": dict(dims=[10000, 10000, 10000], nnz=1_000_000_000, D=32, lik="normal", model="d", diag=False, k1=64,
+               k2=64, desc="real 10k^3, 1e9 nnz, D=32, normal, SSVI_TF_d full cov"),
+}
+DATATYPE = {"normal": "real", "bernoulli": "binary", "poisson": "count"}
+
+
+def algorithmic_bytes_per_unit(c, mean_row_len):
+    """coords + value + gathered other-mode (mean, cov) rows + amortised own row."""
+    N, D, w = len(c["dims"]), c["D"], 8
+    r_row = (2 * D if c["diag"] else D + D * D) * w
+    return 4 * N + w + (N - 1) * r_row + (2 * r_row + 2 * D * w) / max(mean_row_len, 1.0)
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for n, v in zip(names, r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class DeviceTensorData(object):
+    """Synthetic tensor of a BASELINE config, generated on the device: uniform distinct
+    cells, ground-truth CP factors U_d ~ N(mu_d, 0.1 I) of rank D, values through the data link."""
+
+    def __init__(self, c, device, seed, scale=1.0):
+        import torch
+        self.datatype = DATATYPE[c["lik"]]
+        self.dims = list(c["dims"])
+        N, D = len(self.dims), c["D"]
+        nnz = max(int(c["nnz"] * scale), 1000)
+        g = torch.Generator(device=device)
+        g.manual_seed(seed)
+        total = int(np.prod(self.dims))
+        if nnz >= total:                      # dense (config 1): every cell, shuffled
+            lin = torch.randperm(total, generator=g, device=device)
+            nnz = total
+        else:
+            lin = torch.unique(torch.randint(0, total, (int(nnz * 1.03) + 64,), generator=g, device=device))
+            lin = lin[torch.randperm(lin.numel(), generator=g, device=device)][:nnz]
+            nnz = int(lin.numel())
+        coords = torch.empty((nnz, N), dtype=torch.int32, device=device)
+        rem = lin
+        for d in range(N - 1, -1, -1):
+            coords[:, d] = (rem % self.dims[d]).to(torch.int32)
+            rem = rem // self.dims[d]
+        del lin, rem
+        if c["lik"] == "bernoulli":
+            mus = np.linspace(-1, 1, N)          # binary_tensor.py:12-19
+        elif c["lik"] == "poisson":
+            mus = np.linspace(0, 1.5, N)         # count_tensor.py:16-23
+        else:
+            mus = [0.5, 1.0, 0.2, 0.5][:N]
+        f = torch.ones((nnz, D), dtype=torch.float32, device=device)
+        for d in range(N):
+            U = float(mus[d]) + math.sqrt(0.1) * torch.randn((self.dims[d], D), generator=g, device=device)
+            f *= U[coords[:, d].long()]
+        f = f.sum(dim=1).double()
+        if c["lik"] == "normal":
+            vals = f + 0.05 * f.abs() * torch.randn(f.shape, generator=g, device=device, dtype=torch.float64)
+        elif c["lik"] == "bernoulli":
+            u = torch.rand(f.shape, generator=g, device=device, dtype=torch.float64)
+            vals = torch.where(u < torch.sigmoid(f), 1.0, -1.0).double()
+        else:
+            lam = torch.clamp(torch.log1p(torch.exp(f)), min=1e-8)
+            vals = torch.clamp(torch.poisson(lam, generator=g), max=170.0)      # y! finite in fp64
+        n_train = int(nnz * 0.8)
+        self.train_entries, self.train_vals = coords[:n_train].contiguous(), vals[:n_train].contiguous()
+        self.test_entries = coords[n_train:].cpu().numpy().astype(np.int64)
+        self.test_vals = vals[n_train:].cpu().numpy()
+        self.max_count = int(vals.max().item()) if c["lik"] == "poisson" else 0
+        self.min_count = int(vals.min().item()) if c["lik"] == "poisson" else 0
+
+
+def build_model(c, data, device, group, chunk_entries, noise_slots):
+    import torch
+    import ssvi_tf_b200 as pkg
+    cls = {"d": pkg.SSVI_TF_d, "simple": pkg.SSVI_TF_simple, "robust": pkg.SSVI_TF_robust}[c["model"]]
+    D = c["D"]
+    mean0 = np.ones(D) if c["lik"] == "normal" else np.zeros(D)       # synthetic_test.py:25-35
+    np.random.seed(319)
+    return cls(data, D, diag=c["diag"], mean0=mean0, cov0=np.eye(D) * 0.1, k1=c["k1"], k2=c["k2"], batch_size=128,
+               cov_eta=c.get("cov_eta", 1), randstart=True, device=device, noise_dtype=torch.float32,
+               noise_slots=noise_slots, chunk_entries=chunk_entries, process_group=group)
+
+
+def one_step(model):
+    for dim in range(model.order):
+        model.sweep(dim)
+        model.update_hyper_parameter(dim)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU baseline: the oracle port (numpy restatement of the reference step) on host cores
+# ------------------------------------------------------------------------------------------------
+def _cpu_worker(args):
+    c, seed, budget_s, max_rows = args
+    os.environ.setdefault("OMP_NUM_THREADS", "1")
+    from oracle import ssvi_oracle as so
+    rng = np.random.default_rng(seed)
+    N, D, B = len(c["dims"]), c["D"], 128
+    dims = [min(n, 64) for n in c["dims"]]           # per-update cost does not depend on the tensor size
+    cfg = so.make_config(c["model"], c["lik"], D, diag=c["diag"], k1=c["k1"], k2=c["k2"], batch_size=B,
+                         cov_eta=c.get("cov_eta", 1.0))
+    st = so.new_state(cfg, dims, rng=rng, mean0=np.ones(D) if c["lik"] == "normal" else np.zeros(D),
+                      cov0=np.eye(D) * 0.1)
+    units, rows_done = 0, 0
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < budget_s and rows_done < max_rows:
+        dim = rows_done % N
+        row = (rows_done // N) % dims[dim]
+        coords = rng.integers(0, dims, size=(B, N))
+        coords[:, dim] = row
+        if c["lik"] == "normal":
+            ys = rng.normal(0.5, 1.0, B)
+        elif c["lik"] == "bernoulli":
+            ys = rng.choice([-1.0, 1.0], B)
+        else:
+            ys = rng.poisson(2.0, B).astype(float)
+        so.row_step(st, cfg, dim, row, coords, ys, so.make_tape(rng, cfg, N, B))
+        units += B
+        rows_done += 1
+    return units, time.perf_counter() - t0
+
+
+def cpu_baseline(c, cores, budget_s, max_rows=10 ** 9):
+    """units/s of the oracle over `cores` independent processes on disjoint synthetic rows (the
+    reference has no intra-process parallelism; this mirrors its one-job-per-core Slurm usage)."""
+    if cores == 1:
+        res = [_cpu_worker((c, 1, budget_s, max_rows))]
+    else:
+        import multiprocessing as mp
+        with mp.get_context("spawn").Pool(cores) as pool:
+            res = pool.map(_cpu_worker, [(c, 100 + i, budget_s, max_rows) for i in range(cores)])
+    units = sum(r[0] for r in res)
+    wall = max(r[1] for r in res)
+    return units / wall, units, wall
+
+
+def run_reference_arm(args, c, rank, world):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_step = max(2.0, min(20.0, 90.0 / max(args.steps + args.warmup, 1)))
+    for _ in range(args.warmup):
+        cpu_baseline(c, cores, min(per_step, 2.0))
+    tot_units, tot_wall = 0, 0.0
+    for _ in range(args.steps):
+        _, u, w = cpu_baseline(c, cores, per_step)
+        tot_units += u
+        tot_wall += w
+    v = tot_units / tot_wall
+    sample = ("%d row updates of B=128 entries (same D/k1/k2/model/likelihood as %s, dims shrunk to <=64), "
+              "%.0f s per step x %d procs" % (tot_units // 128, args.config, per_step, cores))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * tot_wall / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": c["desc"], "sweep": "reference-style minibatch rows (B=128)"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scale", type=float, default=1.0, help="fraction of the config's nnz (debug only)")
+    ap.add_argument("--chunk-entries", type=int, default=16)
+    ap.add_argument("--noise-slots", type=int, default=128)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    c = CONFIGS[args.config]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference_arm(args, c, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    assert args.warmup >= 3 or args.scale != 1.0, "timing rules: W >= 3"
+    torch.cuda.set_device(local)
+    device = "cuda:%d" % local
+    group = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(device))
+        group = dist.group.WORLD
+    data = DeviceTensorData(c, device, seed=319 + int(args.config[1:]) + 1000 * rank, scale=args.scale)
+    model = build_model(c, data, device, group, args.chunk_entries, args.noise_slots)
+    eng = model.engine
+    N = model.order
+    nnz_train = eng.nnz
+    units_per_step = N * nnz_train                       # per rank
+    model.fresh_noise()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident arm: `value` ------------------------------------------------------------
+    for _ in range(args.warmup):
+        one_step(model)
+    eng.check_flags()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    eng.profile_events = []
+    launches0 = eng.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        one_step(model)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = eng.launches - launches0
+    events, eng.profile_events = eng.profile_events, None
+    clocks = sampler.stop() if rank == 0 else None
+    eng.check_flags()
+    t = torch.tensor([ms], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * units_per_step * args.steps / (ms * 1e-3)
+
+    # roofline of the dominant kernel (ssvi_accumulate), from CUDA events inside the timed region
+    acc_ms = [a.elapsed_time(b) for a, b, _ in events]
+    acc_units = [n for _, _, n in events]
+    mean_row = nnz_train * N / float(sum(c["dims"]))
+    bpu = algorithmic_bytes_per_unit(c, mean_row)
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    achieved = sum(acc_units) * bpu / (sum(acc_ms) * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "accumulate (stages 1-3)", "peak_source": peak_src,
+                "algorithmic_bytes_per_unit": bpu, "kernel_ms_per_launch": float(np.mean(acc_ms)),
+                "kernel_share_of_step": sum(acc_ms) / ms,
+                "note": "fp64 work is bounded by the FP64 pipe (36 TFLOP/s measured), see DESIGN.md"}
+
+    # ---- end-to-end arm: host buffers in, host result out, every step ----------------------------
+    pin = lambda x: x.cpu().pin_memory()                                      # noqa: E731
+    h_coords, h_vals = pin(eng.coords), pin(eng.vals)
+    h_perm = [pin(p) for p in eng.perm]
+    nz = eng.noise
+    h_noise = [pin(x) for x in (nz.z_other, nz.z_own, nz.r_w, nz.z_f) if x is not None]
+    d_noise = [x for x in (nz.z_other, nz.z_own, nz.r_w, nz.z_f) if x is not None]
+    h_out = [torch.empty(p.shape, dtype=p.dtype).pin_memory() for p in eng.params]
+    h2d = (h_coords.numel() * 4 + h_vals.numel() * 8 + sum(p.numel() * 8 for p in h_perm)
+           + sum(x.numel() * x.element_size() for x in h_noise))
+    d2h = sum(p.numel() * 8 for p in h_out)
+
+    def e2e_step():
+        eng.coords.copy_(h_coords, non_blocking=True)
+        eng.vals.copy_(h_vals, non_blocking=True)
+        for dp, hp in zip(eng.perm, h_perm):
+            dp.copy_(hp, non_blocking=True)
+        for dn, hn in zip(d_noise, h_noise):
+            dn.copy_(hn, non_blocking=True)
+        one_step(model)
+        for ho, p in zip(h_out, eng.params):
+            ho.copy_(p, non_blocking=True)
+
+    e2e_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * units_per_step * args.steps / (float(t.item()) * 1e-3)
+    eng.check_flags()
+
+    if rank == 0:
+        cpu = None
+        if not args.no_cpu_baseline and world == 1:
+            v, u, w = cpu_baseline(c, 1, args.cpu_seconds)
+            cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+                   "sample": "%d row updates of B=128 entries, same D/k1/k2/model/likelihood, dims shrunk to <=64, "
+                             "%.1f s, 1 thread (oracle/ssvi_oracle.py)" % (u // 128, w)}
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": c["desc"], "config_id": args.config, "nnz_train_per_gpu": nnz_train,
+                       "units_per_step_per_gpu": units_per_step, "sweep": "full rows (scale=1), all modes",
+                       "noise": "f32 pool, %d slots" % eng.noise.slots, "chunk_entries": args.chunk_entries,
+                       "l2": "inputs larger than L2 (COO+CSR %.0f MB per GPU)" % (h2d / 1e6),
+                       "parallelism": "entries sharded x%d, all-reduce of row accumulators" % world},
+            "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": launches, "clocks": clocks}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,437 @@
+"""SSVI_TF: the reference's factorizer surface (SSVI/SSVI_TF_interface.py) over the B200 engine.
+
+Same constructor kwargs, same attribute names, same factorize() loop; the per-row stochastic
+variational update (update_natural_param_batch, :163-219) runs as hand-written sm_100a kernels behind
+the C ABI of include/ssvi_b200.h.  New, batched entry points: update_natural_param_rows(dim, rows)
+(any set of rows of one mode from one state snapshot -- the equivalence class of DESIGN.md) and
+sweep(dim) (every observed entry of every row, scale = 1).
+
+There is no CPU fallback: constructing a model without a CUDA device raises.
+"""
+import time
+
+import numpy as np
+import torch
+
+from ..engine import Engine, NoisePool
+from ..Model.TF_Models import Posterior_Diag_Covariance, Posterior_Full_Covariance
+from ..Probability import ProbFun as probs
+from ..Probability.bernoulli import BernoulliDistribution
+from ..Probability.normal import NormalDistribution
+from ..Probability.poisson import PoissonDistribution
+
+
+class SSVI_TF(object):
+    _model = "d"          # "d" | "simple" | "robust"; set by the subclasses
+
+    def __init__(self, tensor, rank, mean_update="S", cov_update="N", noise_update="N",
+                 diag=False, mean0=None, cov0=None, sigma0=1,
+                 unstable_cov=False, k1=64, k2=64, batch_size=128,
+                 eta=1, cov_eta=1, sigma_eta=1, randstart=True,
+                 device=None, noise_dtype=torch.float32, noise_slots=None, noise_seed=319,
+                 chunk_entries=16, process_group=None):
+        self.tensor = tensor
+        self.dims = list(tensor.dims)
+        self.datatype = tensor.datatype
+        self.order = len(tensor.dims)
+        self.randstart = randstart
+        self.D = rank
+        self.mean_update = mean_update
+        self.cov_update = cov_update
+        self.noise_update = noise_update
+        self.diag = diag
+        if mean_update not in ("S", "N") or cov_update not in ("S", "N"):
+            raise Exception("Unidentified update formula for covariance param")     # :612, :632
+        cls = Posterior_Diag_Covariance if diag else Posterior_Full_Covariance
+        self.posterior = cls(self.dims, self.D, mean0, cov0, randstart)             # :37-41
+
+        self.mean0 = mean0
+        self.cov0 = cov0
+        self.w_sigma0 = sigma0
+        self.unstable_cov = unstable_cov
+        self.cov_epsilon = 1e-7
+        self.min_eigenval = 0.01
+        self.k1 = k1
+        self.k2 = k2
+        self.batch_size = batch_size
+        self.predict_num_samples = 32
+        self.pmu = np.ones((self.D,))
+
+        if self.datatype == "real":                                                # :59-77
+            self.link_fun = lambda m: m
+            self.likelihood_type = "normal"
+            self.likelihood_param = 1
+            self.likelihood = NormalDistribution()
+        elif self.datatype == "binary":
+            self.link_fun = lambda m: probs.sigmoid(m)
+            self.likelihood_type = "bernoulli"
+            self.likelihood_param = 0
+            self.likelihood = BernoulliDistribution()
+        elif self.datatype == "count":
+            self.likelihood_type = "poisson"
+            self.max_count = tensor.max_count
+            self.min_count = tensor.min_count
+            self.link_fun = lambda m: probs.poisson_link(m)
+            self.likelihood_param = 0
+            self.likelihood = PoissonDistribution()
+        else:
+            raise Exception("unsupported datatype " + str(self.datatype))
+
+        self.epsilon = 0.0001
+        self.eta = eta
+        self.cov_eta = cov_eta
+        self.poisson_eta = 0.1
+        self.sigma_eta = sigma_eta
+        self.noise_added = self._model != "d"
+        self.d_mean = 1.
+        self.d_cov = 1.
+        self.w_changes = 0.
+        self.missing = {}
+        self.fixed_covariance = False
+        self.rows_per_iteration = 1
+        self.process_group = process_group
+
+        cfg = dict(model=self._model, likelihood=self.likelihood_type, D=rank, diag=diag, k1=k1, k2=k2,
+                   batch_size=batch_size, mean_update=mean_update, cov_update=cov_update, eta=eta,
+                   cov_eta=cov_eta, sigma_eta=sigma_eta, poisson_eta=self.poisson_eta,
+                   min_eigenval=self.min_eigenval, epsilon=self.epsilon,
+                   likelihood_param=float(self.likelihood_param))
+        if device is None:
+            device = "cuda:%d" % torch.cuda.current_device() if torch.cuda.is_available() else "cuda"
+        self.engine = Engine(cfg, self.dims, tensor.train_entries, tensor.train_vals, device=device,
+                             noise_dtype=noise_dtype, chunk_entries=chunk_entries)
+        eng = self.engine
+        for d, p in enumerate(self.posterior.initial_values()):
+            eng.params[d].copy_(torch.as_tensor(p))
+        self.posterior.attach(eng.params, self._posterior_written)
+        eng.refresh_sampler()
+        eng.w_state.copy_(torch.tensor([1.0, 0.0, 1.0], dtype=torch.float64))       # SSVI_TF_simple.py:15-17
+        self.norm_changes = eng.norm_changes                                        # :91  (n_d, 2) device
+        self.grad_norms = eng.grad_norms                                            # :95
+        self._noise_slots = int(noise_slots) if noise_slots else max(int(batch_size), 1)
+        self._noise_gen_seed = int(noise_seed)
+        self._noise_draws = 0
+        self._np_rng = np.random.default_rng(noise_seed)
+        self._n_obs_global = {}
+
+    # ---------------------------------------------------------------------------------------------
+    # state the reference keeps as numpy arrays, exposed with the reference's names and shapes
+    # ---------------------------------------------------------------------------------------------
+    @property
+    def ada_acc_grad(self):            # list of (D, n_d) views (:83)
+        return [a.t() for a in self.engine.ada_mean]
+
+    @property
+    def ada_acc_grad_cov(self):        # (:41)
+        return [a.t() for a in self.engine.ada_cov]
+
+    @property
+    def pSigma(self):                  # (:56)
+        return self.engine.pSigma.cpu().numpy()
+
+    @pSigma.setter
+    def pSigma(self, v):
+        self.engine.pSigma.copy_(torch.as_tensor(np.asarray(v, dtype=np.float64)))
+
+    @property
+    def time_step(self):               # (:79)
+        return self.engine.time_step
+
+    @time_step.setter
+    def time_step(self, v):
+        self.engine.time_step = [int(t) for t in v]
+
+    def _w(self, i):
+        return float(self.engine.w_state[i].item())
+
+    w_sigma = property(lambda self: self._w(0), lambda self, v: self.engine.w_state[0:1].fill_(float(v)))
+    w_ada_grad = property(lambda self: self._w(1), lambda self, v: self.engine.w_state[1:2].fill_(float(v)))
+    w_tau = property(lambda self: self._w(2), lambda self, v: self.engine.w_state[2:3].fill_(float(v)))
+
+    def _posterior_written(self, dim, row):
+        rows = None if row is None else torch.tensor([int(row)], device=self.engine.device, dtype=torch.int64)
+        self.engine.refresh_sampler(dim, rows)
+
+    # ---------------------------------------------------------------------------------------------
+    # noise
+    # ---------------------------------------------------------------------------------------------
+    def set_noise(self, pool):
+        """Supply the Monte-Carlo variates explicitly (a NoisePool, e.g. NoisePool.from_tape)."""
+        self.engine.set_noise(pool)
+
+    def fresh_noise(self):
+        """Draw a new pool of standard variates on the device (the stand-in for the reference's global
+        numpy RNG): batch_size slots, so every entry of a row's minibatch has its own draws."""
+        self._noise_draws += 1
+        e = self.engine
+        self.engine.set_noise(NoisePool.random(self._noise_slots, self.order, self.D, self.k1, self.k2,
+                                               self.noise_added, e.device, e.noise_dtype,
+                                               seed=self._noise_gen_seed + self._noise_draws))
+
+    # ---------------------------------------------------------------------------------------------
+    # the hot path
+    # ---------------------------------------------------------------------------------------------
+    def _global_n_obs(self, plan):
+        """len(find_observed_ui) summed over all shards (multi-GPU: entries are sharded by rank)."""
+        if self.process_group is None:
+            return plan.n_obs
+        key = id(plan)
+        if key not in self._n_obs_global:
+            import torch.distributed as dist
+            t = plan.n_obs.clone()
+            dist.all_reduce(t, group=self.process_group)
+            self._n_obs_global[key] = (plan, t)
+        return self._n_obs_global[key][1]
+
+    def _run_plan(self, plan):
+        eng = self.engine
+        if eng.noise is None:
+            self.fresh_noise()
+        acc = eng.accumulate(plan)
+        if self.process_group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(acc, group=self.process_group)      # the exchange step: per-row (di, Di, si, count)
+        eng.row_update(plan, acc, self.fixed_covariance, n_obs=self._global_n_obs(plan))
+
+    def update_natural_param_rows(self, dim, rows, noise=None, sub_idx=None):
+        """update_natural_param_batch (:163-219) for every row in `rows` of mode `dim`, evaluated from one
+        state snapshot (pSigma, time_step, w_sigma frozen; the w_sigma recurrence is replayed in row
+        order afterwards).  Rows without observations are recorded in self.missing (:166-168)."""
+        if noise is not None:
+            self.set_noise(noise)
+        rows = np.atleast_1d(np.asarray(rows, dtype=np.int64))
+        if self.process_group is None:
+            rp = self.engine.rowptr_h[dim]
+            for r in rows[rp[rows + 1] == rp[rows]]:
+                self.missing[(dim, int(r))] = True
+        plan = self.engine.plan_minibatch(dim, rows, self.batch_size, rng=self._np_rng, sub_idx=sub_idx)
+        self._run_plan(plan)
+        return plan
+
+    def update_natural_param_batch(self, dim, i, noise=None, sub_idx=None):
+        """The reference's per-row entry point (:163): the one-row case of update_natural_param_rows."""
+        sub = None if sub_idx is None else {int(i): sub_idx}
+        w_before = self.w_sigma if self.noise_added else 0.0
+        self.update_natural_param_rows(dim, [i], noise=noise, sub_idx=sub)
+        if self.noise_added:
+            self.w_changes = abs(self.w_sigma - w_before)                            # :209
+
+    def sweep(self, dim):
+        """One Jacobi sweep over mode `dim`: every observed entry of every row (scale = 1)."""
+        self._run_plan(self.engine.plan_full(dim))
+
+    def update_hyper_parameter(self, dim):
+        """pSigma[dim] = sum_rows (tr S + m.m) / (n_dim D)  (:146-160), as a device reduction."""
+        self.engine.hyper_reduce(dim)
+
+    def check_stop_cond(self):
+        """Largest per-row mean / covariance change over all modes (:967-984)."""
+        eng = self.engine
+        for d in range(self.order):
+            if not getattr(self, "_hyper_fresh", {}).get(d, False):
+                eng.hyper_reduce(d)
+        mx = eng.hyper_out[:, 1:3].max(dim=0).values.cpu().numpy()
+        self.d_mean, self.d_cov = float(mx[0]), float(mx[1])
+        return self.d_mean, self.d_cov
+
+    # ---------------------------------------------------------------------------------------------
+    # factorize loop (:101-143)
+    # ---------------------------------------------------------------------------------------------
+    def factorize(self, report=100, max_iteration=2000, fixed_covariance=False, to_report=[], detailed_report=True,
+                  output_folder="output", rows_per_iteration=None):
+        """The reference's loop: per iteration and per mode, update the next row(s) in round-robin order,
+        refresh pSigma, advance the pointers (time_step += 1 on wrap-around), test the stop condition.
+        rows_per_iteration=1 (default) is the reference's schedule; "all" makes every iteration a full
+        sweep of every mode."""
+        self.report = report
+        self.header_printed = False
+        self.to_report = to_report
+        self.max_iteration = max_iteration
+        self.fixed_covariance = fixed_covariance
+        self.detailed_report = detailed_report
+        self.missing = {}
+        self.max_changes = [[0, 0] for _ in self.dims]
+        self.output_folder = output_folder
+        rpi = self.rows_per_iteration if rows_per_iteration is None else rows_per_iteration
+        print("Factorizing with max_iteration =", max_iteration, " fixing covariance?: ", fixed_covariance)
+
+        update_column_pointer = [0 for _ in range(self.order)]
+        start = time.time()
+        for iteration in range(self.max_iteration + 1):
+            self.fresh_noise()
+            self._hyper_fresh = {}
+            advance = []
+            for dim in range(self.order):
+                n = self.dims[dim]
+                step = n if rpi == "all" else min(int(rpi), n)
+                col = update_column_pointer[dim]
+                rows = np.arange(col, min(col + step, n))
+                self.update_natural_param_rows(dim, rows)                            # :124
+                self.update_hyper_parameter(dim)                                     # :125
+                self._hyper_fresh[dim] = True
+                advance.append(len(rows))
+            for dim in range(self.order):                                            # :128-133
+                nxt = update_column_pointer[dim] + advance[dim]
+                if nxt >= self.dims[dim]:
+                    self.engine.time_step[dim] += 1
+                    nxt = 0
+                update_column_pointer[dim] = nxt
+            mean_change, cov_change = self.check_stop_cond()                         # :135
+            if (iteration != 0 and (iteration % self.report == 0)) or iteration in to_report:
+                self.engine.check_flags()
+                if self.detailed_report:
+                    self.report_metrics(iteration, start, mean_change, cov_change)
+                else:
+                    self.report_metrics_mini(iteration, start, mean_change, cov_change, output_folder)
+            if max(mean_change, cov_change) < self.epsilon:                          # :142
+                break
+        self.engine.check_flags()
+
+    # ---------------------------------------------------------------------------------------------
+    # prediction / evaluation (:987-1059)
+    # ---------------------------------------------------------------------------------------------
+    def _missing_mask(self, entries):
+        keep = np.ones(len(entries), dtype=bool)
+        if self.missing:
+            for (dim, col) in self.missing:
+                keep &= entries[:, dim] != col
+        return keep
+
+    def predict_entries(self, entries):
+        """predict_entry (:1037-1059) for an (n, N) array of coordinates, evaluated on the device."""
+        entries = np.asarray(entries, dtype=np.int64).reshape(-1, self.order)
+        dev = torch.as_tensor(entries.astype(np.int32)).to(self.engine.device)
+        if self.likelihood_type == "normal":
+            return self.engine.predict_mean(dev).cpu().numpy()
+        if self.likelihood_type == "bernoulli" and not self.noise_added:
+            f = self.engine.predict_mean(dev).cpu().numpy()
+            return np.where(f > 0, 1, -1)
+        res = self._expected_observation_via_sampling(dev).cpu().numpy()
+        if self.likelihood_type == "bernoulli":
+            return np.where(res >= 0.5, 1, -1)
+        return np.rint(res)
+
+    def predict_entry(self, entry):
+        return self.predict_entries(np.asarray(entry)[None, :])[0]
+
+    def _expected_observation_via_sampling(self, entries_dev, chunk=1 << 16):
+        """estimate_expected_observation_via_sampling (:1168-1189), batched with torch on the device:
+        predict_num_samples draws of every factor row, Hadamard product, (noise layer,) link, mean.
+        Off the timed path."""
+        eng, S = self.engine, self.predict_num_samples
+        g = torch.Generator(device=eng.device)
+        g.manual_seed(self._noise_gen_seed + 7919)
+        out = []
+        for s in range(0, entries_dev.shape[0], chunk):
+            e = entries_dev[s:s + chunk].long()
+            ms = torch.ones((e.shape[0], S, self.D), device=eng.device, dtype=torch.float64)
+            for d in range(self.order):
+                rows = eng.sampler[d][e[:, d]]                       # (n, D+1, D) | (n, 2, D): mean + Cholesky
+                z = torch.randn((e.shape[0], S, self.D), generator=g, device=eng.device, dtype=torch.float64)
+                if self.diag:
+                    x = rows[:, None, 0, :] + z * rows[:, None, 1, :]
+                else:
+                    x = rows[:, None, 0, :] + torch.einsum("nsc,ndc->nsd", z, rows[:, 1:, :])
+                ms = ms * x
+            f = ms.sum(dim=2)                                        # (n, S)
+            if self.noise_added:
+                u = torch.rand(f.shape, generator=g, device=eng.device, dtype=torch.float64).clamp_(min=1e-300)
+                ws = (self.w_sigma ** 2) * torch.sqrt(-2.0 * torch.log(u))
+                zf = torch.randn((f.shape[0], S, S), generator=g, device=eng.device, dtype=torch.float64)
+                f = (f[:, None, :] + ws[:, None, :] * zf).reshape(f.shape[0], -1)
+            if self.likelihood_type == "bernoulli":
+                p = torch.sigmoid(f)
+            elif self.likelihood_type == "poisson":
+                p = torch.clamp(torch.log(1.0 + torch.exp(f)), min=1e-8)
+            else:
+                p = f
+            out.append(p.mean(dim=1))
+        return torch.cat(out) if out else torch.zeros(0, device=eng.device, dtype=torch.float64)
+
+    def evaluate_error(self, entries, vals):
+        """(rsme, error) over entries not touching an unlearned row (:997-1030)."""
+        entries = np.asarray(entries, dtype=np.int64).reshape(-1, self.order)
+        vals = np.asarray(vals, dtype=np.float64)
+        keep = self._missing_mask(entries)
+        num = int(keep.sum())
+        if num == 0:
+            return float("nan"), float("nan")
+        pred = self.predict_entries(entries[keep])
+        diff = pred - vals[keep]
+        rsme = float(np.sqrt(np.sum(np.square(diff)) / num))
+        if self.likelihood_type == "normal":
+            error = float(np.sum(np.abs(diff)) / num)
+        elif self.likelihood_type == "bernoulli":
+            error = float(np.sum(pred != vals[keep]) / num)
+        else:
+            error = 0.0        # the reference compares self.likelihood (an object) with "poisson" (:1023): never true
+        return rsme, error
+
+    def evaluate_train_error(self):
+        return self.evaluate_error(self.tensor.train_entries, self.tensor.train_vals)
+
+    def evaluate_test_error(self):
+        return self.evaluate_error(self.tensor.test_entries, self.tensor.test_vals)
+
+    # ---------------------------------------------------------------------------------------------
+    # reports (:764-871).  The VLB / NLL columns of the detailed report are SURVEY.md 8f rank 4 (not
+    # built yet): the detailed report prints the optimisation columns and leaves those as nan.
+    # ---------------------------------------------------------------------------------------------
+    def _print_header(self, detailed):
+        self.header_printed = True
+        print("Tensor dimensions: ", self.dims)
+        print("Mean update scheme: ", self.mean_update)
+        print("Covariance update : ", self.cov_update)
+        print("Using diagonal covariance?: ", self.diag)
+        print("Factorization rank: ", self.D)
+        print("k1 samples = ", self.k1, " k2 samples = ", self.k2)
+        print("eta = ", self.eta, " cov eta = ", self.cov_eta, " sigma eta = ", self.sigma_eta)
+        if detailed:
+            print("iteration |   time   | test_mae |rel-te-err|train_mae |rel-tr-err|   d_mean  |   d_cov  |avg_grad_m|avg_grad_c|"
+                  + ("   dw   |" if self.noise_added else ""))
+        else:
+            print("iteration |   time   |  test_err  |  test_mae  |  trainerr  |  trainmae |")
+
+    def _header_due(self, iteration):
+        return not self.header_printed and (iteration == self.report or
+                                            (len(self.to_report) > 0 and iteration == self.to_report[0]))
+
+    def report_metrics(self, iteration, start, mean_change, cov_change):
+        if self._header_due(iteration):
+            self._print_header(True)
+        mae_train, error_train = self.evaluate_train_error()
+        mae_test, error_test = self.evaluate_test_error()
+        avg = [g.mean(dim=0).cpu().numpy() for g in self.grad_norms]                 # :797-805
+        avg_grad_m = float(np.mean([a[0] for a in avg]))
+        avg_grad_c = float(np.mean([a[1] for a in avg]))
+        dec = 4
+        cols = [iteration, np.around(time.time() - start, 2), np.around(mae_test, dec), np.around(error_test, dec),
+                np.around(mae_train, dec), np.around(error_train, dec), np.around(mean_change, dec),
+                np.around(cov_change, dec), np.around(avg_grad_m, dec), np.around(avg_grad_c, dec)]
+        if self.noise_added:
+            cols.append(np.around(self.w_changes, dec))
+        print(" ".join("{:^10}".format(c) for c in cols))
+
+    def report_metrics_mini(self, iteration, start, mean_change, cov_change, output_folder):
+        if self._header_due(iteration):
+            self._print_header(False)
+        mae_train, error_train = self.evaluate_train_error()
+        mae_test, error_test = self.evaluate_test_error()
+        dec = 4
+        print("{:^10} {:^10} {:^10} {:^10} {:^10} {:^10}".format(
+            iteration, np.around(time.time() - start, 2), np.around(error_test, dec), np.around(mae_test, dec),
+            np.around(error_train, dec), np.around(mae_train, dec)))                 # :856-858
+
+    # ---------------------------------------------------------------------------------------------
+    def reset(self):
+        """reset() (:1195-1210), quirk Q9 included: ada_acc_grad restarts at ZEROS (the constructor uses
+        ones), ada_acc_grad_cov is not reset."""
+        eng = self.engine
+        self.posterior.reset()
+        eng.pSigma.fill_(1.0)
+        eng.time_step = [0 for _ in range(self.order)]
+        for d in range(self.order):
+            eng.ada_mean[d].zero_()
+            eng.norm_changes[d].zero_()
+        if self.noise_added:
+            eng.w_state.copy_(torch.tensor([1.0, 0.0, 1.0], dtype=torch.float64))

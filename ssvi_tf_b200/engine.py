@@ -140,14 +140,31 @@ class Engine(object):
         self.h = h
 
         # ---- data: COO + per-mode CSR -------------------------------------------------------
-        coords = np.ascontiguousarray(np.asarray(coords).reshape(-1, self.N))
-        vals = np.ascontiguousarray(np.asarray(vals, dtype=np.float64).reshape(-1))
-        self.nnz = int(vals.shape[0])
-        self.rowptr_h, perm_h = build_csr(coords, self.dims)
-        self.coords = torch.as_tensor(coords.astype(np.int32)).to(self.device)
-        self.vals = torch.as_tensor(vals).to(self.device)
-        self.perm = [torch.as_tensor(p).to(self.device) for p in perm_h]
-        self.perm_h = perm_h
+        if torch.is_tensor(coords) and coords.is_cuda:
+            # device build of the index: stable sort by row == append order
+            self.coords = coords.to(device=self.device, dtype=torch.int32).reshape(-1, self.N).contiguous()
+            self.vals = vals.to(device=self.device, dtype=torch.float64).reshape(-1).contiguous()
+            self.nnz = int(self.vals.shape[0])
+            self.perm, self.rowptr_h = [], []
+            for d, n in enumerate(self.dims):
+                col = self.coords[:, d].long()
+                if self.nnz and (int(col.min()) < 0 or int(col.max()) >= n):
+                    raise ValueError("coordinate out of range in mode %d" % d)
+                self.perm.append(torch.sort(col, stable=True).indices.contiguous())
+                rp = torch.zeros(n + 1, dtype=torch.int64, device=self.device)
+                rp[1:] = torch.cumsum(torch.bincount(col, minlength=n), 0)
+                self.rowptr_h.append(rp.cpu().numpy())
+                del col
+            self._perm_h = None
+        else:
+            coords = np.ascontiguousarray(np.asarray(coords).reshape(-1, self.N))
+            vals = np.ascontiguousarray(np.asarray(vals, dtype=np.float64).reshape(-1))
+            self.nnz = int(vals.shape[0])
+            self.rowptr_h, perm_h = build_csr(coords, self.dims)
+            self.coords = torch.as_tensor(coords.astype(np.int32)).to(self.device)
+            self.vals = torch.as_tensor(vals).to(self.device)
+            self.perm = [torch.as_tensor(p).to(self.device) for p in perm_h]
+            self._perm_h = perm_h
         self._call(self.lib.ssvi_bind_data, _ptr(self.coords), _ptr(self.vals), self.nnz)
 
         # ---- state ------------------------------------------------------------------------------
@@ -169,6 +186,13 @@ class Engine(object):
         self._full_plans = {}
         self._scratch = {}
         self.launches = 0          # kernels of libssvi_b200 launched through this engine
+        self.profile_events = None  # set to a list to time every ssvi_accumulate launch with CUDA events
+
+    @property
+    def perm_h(self):
+        if self._perm_h is None:
+            self._perm_h = [p.cpu().numpy() for p in self.perm]
+        return self._perm_h
 
     # -------------------------------------------------------------------------------------------
     def _call(self, fn, *args):
@@ -297,9 +321,16 @@ class Engine(object):
         partial = self._buf("partial", plan.n_chunks * self.acc_len)
         acc = self._buf("acc", plan.n_rows * self.acc_len)
         st = self._stream()
+        ev = None
+        if self.profile_events is not None:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
         self._call(self.lib.ssvi_accumulate, plan.dim, plan.n_chunks, _ptr(plan.chunk_row), _ptr(plan.chunk_start),
                    _ptr(plan.chunk_len), _ptr(plan.chunk_slot0), _ptr(plan.entry_ids), _ptr(plan.rows),
                    _ptr(self.w_state), _ptr(partial), st)
+        if ev is not None:
+            ev[1].record()
+            self.profile_events.append((ev[0], ev[1], plan.n_entries))
         self._call(self.lib.ssvi_reduce_chunks, plan.n_rows, _ptr(plan.row_chunk_ptr), _ptr(partial), _ptr(acc), st)
         self.launches += 2 if plan.n_chunks else 0
         return acc[:plan.n_rows * self.acc_len].view(plan.n_rows, self.acc_len)

@@ -90,7 +90,7 @@ def test_cuda_batched_rows_match_oracle(model, lik, diag):
         # hyper-parameter + stop-condition reductions
         eng.hyper_reduce(dim)
         so.update_hyper_parameter(want, cfg, dim)
-        np.testing.assert_allclose(eng.pSigma.cpu().numpy()[dim], want["pSigma"][dim], rtol=1e-12)
+        np.testing.assert_allclose(eng.pSigma.cpu().numpy()[dim], want["pSigma"][dim], rtol=RTOL)
         ho = eng.hyper_out[dim].cpu().numpy()
         np.testing.assert_allclose(ho[1:], want["norm_changes"][dim].max(axis=0), rtol=RTOL)
     eng.close()
