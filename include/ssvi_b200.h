@@ -80,7 +80,7 @@ typedef struct SsviConfig {
   int32_t mean_update;      /* SSVI_UPDATE_*   "S" | "N"                         (:32)  */
   int32_t cov_update;       /* SSVI_UPDATE_*   "S" | "N"                         (:33)  */
   int32_t noise_dtype;      /* SSVI_NOISE_*    element type of the noise pool           */
-  int32_t reserved0;
+  int32_t kernel_path;      /* 0 = auto; 1 = force the generic CUDA-core accumulate path (testing)  */
   int32_t reserved1;
   double eta;               /* (:85)  */
   double cov_eta;           /* (:86)  */

@@ -26,7 +26,7 @@ class SsviConfig(ctypes.Structure):
         ("order", ctypes.c_int32), ("rank", ctypes.c_int32), ("cov_kind", ctypes.c_int32),
         ("model", ctypes.c_int32), ("likelihood", ctypes.c_int32), ("k1", ctypes.c_int32),
         ("k2", ctypes.c_int32), ("mean_update", ctypes.c_int32), ("cov_update", ctypes.c_int32),
-        ("noise_dtype", ctypes.c_int32), ("reserved0", ctypes.c_int32), ("reserved1", ctypes.c_int32),
+        ("noise_dtype", ctypes.c_int32), ("kernel_path", ctypes.c_int32), ("reserved1", ctypes.c_int32),
         ("eta", ctypes.c_double), ("cov_eta", ctypes.c_double), ("sigma_eta", ctypes.c_double),
         ("poisson_eta", ctypes.c_double), ("min_eigenval", ctypes.c_double), ("cov_floor", ctypes.c_double),
         ("likelihood_param", ctypes.c_double), ("dims", ctypes.c_int64 * MAX_ORDER),

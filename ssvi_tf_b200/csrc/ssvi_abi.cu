@@ -3,7 +3,7 @@
 #include <string.h>
 #include <new>
 
-#include "accumulate_generic.cuh"
+#include "accumulate_mma.cuh"
 #include "row_update.cuh"
 
 #define SSVI_VERSION_STR "ssvi_b200 0.1 sm_100a"
@@ -186,6 +186,51 @@ static int launch_accumulate_generic(SsviHandle* h, const DevView& v, int64_t n_
   return SSVI_OK;
 }
 
+template <int NT, typename ZT, bool SECOND>
+static int launch_accumulate_mma(SsviHandle* h, const DevView& v, int64_t n_chunks, const int32_t* chunk_row,
+                                 const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
+                                 const int64_t* entry_ids, const int64_t* rows, const double* w_state,
+                                 double* partial_out, cudaStream_t st) {
+  const int wpb = 4;
+  const size_t smem = (size_t)mma_warp_doubles<NT, SECOND>() * wpb * sizeof(double);
+  auto kern = accumulate_mma_kernel<NT, ZT, SECOND>;
+  CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const unsigned grid = (unsigned)((n_chunks + wpb - 1) / wpb);
+  kern<<<grid, wpb * 32, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows,
+                                     w_state, (const ZT*)h->z_other, (const ZT*)h->z_own, (const ZT*)h->r_w,
+                                     (const ZT*)h->z_f, partial_out);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+template <typename ZT>
+static int dispatch_accumulate(SsviHandle* h, const DevView& v, int64_t n_chunks, const int32_t* chunk_row,
+                               const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
+                               const int64_t* entry_ids, const int64_t* rows, const double* w_state,
+                               double* partial_out, cudaStream_t st) {
+#define SSVI_ARGS h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st
+  const bool mma_ok = !v.diag && v.D <= 32 && (v.k1 % 8) == 0 && v.k1 <= 64 && h->cfg.kernel_path != 1;
+  if (mma_ok) {
+    const int nt = (v.D + 7) / 8;
+    if (v.model == SSVI_MODEL_D) {
+      switch (nt) {
+        case 1: return launch_accumulate_mma<1, ZT, false>(SSVI_ARGS);
+        case 2: return launch_accumulate_mma<2, ZT, false>(SSVI_ARGS);
+        case 3: return launch_accumulate_mma<3, ZT, false>(SSVI_ARGS);
+        default: return launch_accumulate_mma<4, ZT, false>(SSVI_ARGS);
+      }
+    }
+    switch (nt) {
+      case 1: return launch_accumulate_mma<1, ZT, true>(SSVI_ARGS);
+      case 2: return launch_accumulate_mma<2, ZT, true>(SSVI_ARGS);
+      case 3: return launch_accumulate_mma<3, ZT, true>(SSVI_ARGS);
+      default: return launch_accumulate_mma<4, ZT, true>(SSVI_ARGS);
+    }
+  }
+  return launch_accumulate_generic<ZT>(SSVI_ARGS);
+#undef SSVI_ARGS
+}
+
 extern "C" int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t* chunk_row,
                                const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
                                const int64_t* entry_ids, const int64_t* rows, const double* w_state,
@@ -200,8 +245,8 @@ extern "C" int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, con
   const DevView v = make_view(h, dim);
   cudaStream_t st = (cudaStream_t)stream;
   if (h->cfg.noise_dtype == SSVI_NOISE_F32)
-    return launch_accumulate_generic<float>(h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st);
-  return launch_accumulate_generic<double>(h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st);
+    return dispatch_accumulate<float>(h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st);
+  return dispatch_accumulate<double>(h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st);
 }
 
 // acc_out[r][i] = sum over the row's chunk records, in chunk order (deterministic)

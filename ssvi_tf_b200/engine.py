@@ -99,7 +99,8 @@ class SweepPlan(object):
 class Engine(object):
     """One GPU's view of the problem: COO shard + CSR index + posterior state + noise pool."""
 
-    def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16):
+    def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16,
+                 kernel_path=0):
         """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
         cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
         if not torch.cuda.is_available():
@@ -123,6 +124,7 @@ class Engine(object):
         c.k1, c.k2 = int(cfg["k1"]), int(cfg["k2"])
         c.mean_update, c.cov_update = UPDATE_IDS[cfg["mean_update"]], UPDATE_IDS[cfg["cov_update"]]
         c.noise_dtype = _lib.NOISE_F32 if noise_dtype == torch.float32 else _lib.NOISE_F64
+        c.kernel_path = int(kernel_path)      # 0 auto, 1 force the generic CUDA-core accumulate path
         c.eta, c.cov_eta, c.sigma_eta = float(cfg["eta"]), float(cfg["cov_eta"]), float(cfg["sigma_eta"])
         c.poisson_eta = float(cfg.get("poisson_eta", 0.1))
         c.min_eigenval = float(cfg.get("min_eigenval", 0.01))

@@ -128,3 +128,52 @@ def test_predict_mean_matches_oracle():
     got = eng.predict_mean(eng.coords).cpu().numpy()
     np.testing.assert_allclose(got, so.predict_mean(st0, coords), rtol=1e-12)
     eng.close()
+
+
+@pytest.mark.parametrize("D,k1,model,lik", [(12, 64, "d", "bernoulli"), (20, 64, "d", "bernoulli"),
+                                            (20, 24, "robust", "normal"), (27, 40, "simple", "poisson"),
+                                            (32, 64, "d", "normal"), (30, 64, "robust", "poisson")])
+def test_mma_path_matches_oracle_and_generic(D, k1, model, lik):
+    """The FP64 tensor-pipe kernel (every n-tile count) == the generic CUDA-core kernel == the oracle."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(D * 100 + k1)
+    dims, B, k2 = [6, 5, 4], 6, 8
+    cfg = so.make_config(model, lik, D, diag=False, k1=k1, k2=k2, batch_size=B)
+    coords, vals = random_problem(rng, lik, dims, 70)
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    pool = so.make_tape(rng, cfg, 3, B)
+    results = []
+    for path in (0, 1):
+        eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=4,
+                     kernel_path=path)
+        eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float32))
+        engine_load_state(eng, st0)
+        dim = 1
+        rows = np.arange(dims[dim])
+        sub = {}
+        entries, tapes = [], []
+        for row in rows:
+            ids = perm[dim][rowptr[dim][row]:rowptr[dim][row + 1]]
+            n = min(len(ids), B)
+            t = so.Tape(pool.z_other[:n], pool.z_own[:n], pool.r_w[:n], pool.z_f[:n])
+            if len(ids) > B:
+                t.sub_idx = np.arange(len(ids))[::-1][:B].copy()
+                sub[int(row)] = t.sub_idx
+            entries.append((coords[ids], vals[ids]))
+            tapes.append(t)
+        plan = eng.plan_minibatch(dim, rows, B, sub_idx=sub)
+        acc = eng.accumulate(plan).cpu().numpy().copy()
+        eng.row_update(plan, eng.accumulate(plan))
+        eng.check_flags()
+        results.append((acc, engine_dump_state(eng, st0)))
+        eng.close()
+    want = so.copy_state(st0)
+    so.rows_step(want, cfg, dim, rows, entries, tapes)
+    for acc, got in results:
+        assert_state_close(got, want, cfg, RTOL, what="D=%d" % D)
+    scale = np.abs(results[1][0]).max()
+    np.testing.assert_allclose(results[0][0], results[1][0], rtol=1e-9, atol=1e-12 * scale)
+    # Di block of the accumulator record is exactly symmetric
+    Di = results[0][0][:, D:D + D * D].reshape(-1, D, D)
+    np.testing.assert_array_equal(Di, np.transpose(Di, (0, 2, 1)))
