@@ -26,8 +26,8 @@
  * Noise contract ("identical noise draws").  The reference draws from numpy's global RNG; here the
  * caller supplies STANDARD variates in a pool of `pool_slots` slots.  Entry number b of a row's
  * minibatch uses slot (b mod pool_slots).  Layouts (k fastest, so 32 lanes read 32 samples):
- *     z_other [slot][jj][c][k]   jj = other modes in ascending order, c < D, k < k1
- *     z_own   [slot][c][k]
+ *     z_other [slot][jj][block]  jj = other modes in ascending order; block = ssvi_noise_block_len
+ *     z_own   [slot][block]      elements, element (c < D, k < k1) at ssvi_noise_offset(c, k)
  *     r_w     [slot][k]          unit Rayleigh  (ws = w_sigma^2 * r_w;  simple/robust only)
  *     z_f     [slot][k2][k]      (fs = mean + ws * z_f;                 simple/robust only)
  * Transforms: x = m + L z with L the lower Cholesky factor of the row covariance
@@ -98,7 +98,17 @@ typedef struct SsviHandle SsviHandle;
  *   [ di (D) | Di (D*D full, D diag) | si_sum | count ]                                        */
 int64_t ssvi_acc_len(const SsviConfig* cfg);
 
-/* Bytes of dynamic state the library itself allocates for a handle (flag word only). */
+/* Doubles per row of the sampler cache (library-internal layout: mean + Cholesky factor in DMMA
+ * fragment order for full covariance; mean + sqrt(S) for diagonal).  sampler[d] holds n_d such rows. */
+int64_t ssvi_sampler_row_len(const SsviConfig* cfg);
+
+/* Noise block of one (slot, mode): its length in elements and the offset of element (c, k)
+ * (c < D component, k < k1 sample).  Diagonal covariance: c*k1 + k.  Full covariance: DMMA B-fragment
+ * order ((k/8)*ceil(D/4) + c/4)*32 + (k%8)*4 + c%4, zero-padded to multiples of 4 (c) and 8 (k). */
+int64_t ssvi_noise_block_len(const SsviConfig* cfg);
+int64_t ssvi_noise_offset(const SsviConfig* cfg, int32_t c, int32_t k);
+
+/* The library itself allocates only the device flag word of a handle. */
 int ssvi_create(const SsviConfig* cfg /*HOST*/, SsviHandle** out /*HOST*/);
 void ssvi_destroy(SsviHandle* h);
 const char* ssvi_last_error(const SsviHandle* h); /* HOST string; h may be NULL for create errors */
@@ -109,7 +119,7 @@ int ssvi_bind_data(SsviHandle* h, const int32_t* coords, const double* vals, int
 
 /* Posterior and optimiser state, one device pointer per mode (HOST arrays of N device pointers).
  *   params[d]        (n_d, D+1, D) full | (n_d, 2, D) diag   == Posterior.params[d] (Model/TF_Models.py:53-93)
- *   sampler[d]       same shape; row 0 mean, rows 1..D lower Cholesky factor (diag: sqrt(S)); a cache
+ *   sampler[d]       (n_d, ssvi_sampler_row_len): mean + lower Cholesky factor (diag: sqrt(S)); a cache
  *                    the library maintains (ssvi_refresh_sampler / ssvi_row_update)
  *   ada_mean[d]      (n_d, D)   transposed ada_acc_grad[d]      (:83, :694-698)
  *   ada_cov[d]       (n_d, D)   transposed ada_acc_grad_cov[d]  (:41, :705-713); may be NULL for full cov

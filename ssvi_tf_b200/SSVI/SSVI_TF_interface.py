@@ -166,32 +166,32 @@ class SSVI_TF(object):
         e = self.engine
         self.engine.set_noise(NoisePool.random(self._noise_slots, self.order, self.D, self.k1, self.k2,
                                                self.noise_added, e.device, e.noise_dtype,
-                                               seed=self._noise_gen_seed + self._noise_draws))
+                                               seed=self._noise_gen_seed + self._noise_draws, diag=self.diag))
 
     # ---------------------------------------------------------------------------------------------
     # the hot path
     # ---------------------------------------------------------------------------------------------
-    def _global_n_obs(self, plan):
-        """len(find_observed_ui) summed over all shards (multi-GPU: entries are sharded by rank)."""
+    def _shard_info(self, dim, rows_h, lens):
+        """Multi-GPU: (slot_offset, n_obs_global) of the listed rows; single GPU: (None, None)."""
         if self.process_group is None:
-            return plan.n_obs
-        key = id(plan)
+            return None, None
+        from .. import dist as sdist
+        key = (dim, rows_h.tobytes(), lens.tobytes())
         if key not in self._n_obs_global:
-            import torch.distributed as dist
-            t = plan.n_obs.clone()
-            dist.all_reduce(t, group=self.process_group)
-            self._n_obs_global[key] = (plan, t)
-        return self._n_obs_global[key][1]
+            local = torch.as_tensor(lens).to(self.engine.device)
+            off, tot = sdist.row_slot_offsets(local, self.process_group)
+            self._n_obs_global[key] = (off.cpu().numpy(), tot)
+        return self._n_obs_global[key]
 
-    def _run_plan(self, plan):
+    def _run_plan(self, plan, n_obs_global=None):
         eng = self.engine
         if eng.noise is None:
             self.fresh_noise()
         acc = eng.accumulate(plan)
         if self.process_group is not None:
-            import torch.distributed as dist
-            dist.all_reduce(acc, group=self.process_group)      # the exchange step: per-row (di, Di, si, count)
-        eng.row_update(plan, acc, self.fixed_covariance, n_obs=self._global_n_obs(plan))
+            from .. import dist as sdist
+            sdist.allreduce_accumulators(acc, self.process_group)   # the exchange step: (di, Di, si, count)
+        eng.row_update(plan, acc, self.fixed_covariance, n_obs=n_obs_global)
 
     def update_natural_param_rows(self, dim, rows, noise=None, sub_idx=None):
         """update_natural_param_batch (:163-219) for every row in `rows` of mode `dim`, evaluated from one
@@ -204,8 +204,13 @@ class SSVI_TF(object):
             rp = self.engine.rowptr_h[dim]
             for r in rows[rp[rows + 1] == rp[rows]]:
                 self.missing[(dim, int(r))] = True
-        plan = self.engine.plan_minibatch(dim, rows, self.batch_size, rng=self._np_rng, sub_idx=sub_idx)
-        self._run_plan(plan)
+        rp = self.engine.rowptr_h[dim]
+        lens = np.minimum(rp[rows + 1] - rp[rows], self.batch_size)
+        off, _ = self._shard_info(dim, rows, lens)
+        _, n_obs = self._shard_info(dim, rows, rp[rows + 1] - rp[rows])
+        plan = self.engine.plan_minibatch(dim, rows, self.batch_size, rng=self._np_rng, sub_idx=sub_idx,
+                                          slot_offset=off)
+        self._run_plan(plan, n_obs)
         return plan
 
     def update_natural_param_batch(self, dim, i, noise=None, sub_idx=None):
@@ -218,7 +223,10 @@ class SSVI_TF(object):
 
     def sweep(self, dim):
         """One Jacobi sweep over mode `dim`: every observed entry of every row (scale = 1)."""
-        self._run_plan(self.engine.plan_full(dim))
+        rp = self.engine.rowptr_h[dim]
+        rows = np.arange(self.dims[dim], dtype=np.int64)
+        off, n_obs = self._shard_info(dim, rows, rp[1:] - rp[:-1])
+        self._run_plan(self.engine.plan_full(dim, None, off), n_obs)
 
     def update_hyper_parameter(self, dim):
         """pSigma[dim] = sum_rows (tr S + m.m) / (n_dim D)  (:146-160), as a device reduction."""
@@ -326,12 +334,12 @@ class SSVI_TF(object):
             e = entries_dev[s:s + chunk].long()
             ms = torch.ones((e.shape[0], S, self.D), device=eng.device, dtype=torch.float64)
             for d in range(self.order):
-                rows = eng.sampler[d][e[:, d]]                       # (n, D+1, D) | (n, 2, D): mean + Cholesky
+                rows = eng.params[d][e[:, d]]                        # (n, D+1, D) | (n, 2, D)
                 z = torch.randn((e.shape[0], S, self.D), generator=g, device=eng.device, dtype=torch.float64)
                 if self.diag:
-                    x = rows[:, None, 0, :] + z * rows[:, None, 1, :]
+                    x = rows[:, None, 0, :] + z * torch.sqrt(rows[:, None, 1, :])
                 else:
-                    x = rows[:, None, 0, :] + torch.einsum("nsc,ndc->nsd", z, rows[:, 1:, :])
+                    x = rows[:, None, 0, :] + torch.einsum("nsc,ndc->nsd", z, torch.linalg.cholesky(rows[:, 1:, :]))
                 ms = ms * x
             f = ms.sum(dim=2)                                        # (n, S)
             if self.noise_added:

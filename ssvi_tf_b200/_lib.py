@@ -39,6 +39,9 @@ _I32, _I64 = ctypes.c_int32, ctypes.c_int64
 SIGNATURES = {
     "ssvi_version": (ctypes.c_char_p, []),
     "ssvi_acc_len": (_I64, [ctypes.POINTER(SsviConfig)]),
+    "ssvi_sampler_row_len": (_I64, [ctypes.POINTER(SsviConfig)]),
+    "ssvi_noise_block_len": (_I64, [ctypes.POINTER(SsviConfig)]),
+    "ssvi_noise_offset": (_I64, [ctypes.POINTER(SsviConfig), _I32, _I32]),
     "ssvi_create": (ctypes.c_int, [ctypes.POINTER(SsviConfig), ctypes.POINTER(_P)]),
     "ssvi_destroy": (None, [_P]),
     "ssvi_last_error": (ctypes.c_char_p, [_P]),

@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(128) accumulate_generic_kernel(
   const int64_t c = (int64_t)blockIdx.x * wpb + warp;
   if (c >= n_chunks) return;
   const int N = v.N, D = v.D, k1 = v.k1, dim = v.dim, diag = v.diag;
-  const int row_len = v.row_len, cov_len = v.cov_len, KS = generic_ks(k1);
+  const int row_len = v.srow_len, cov_len = v.cov_len, KS = generic_ks(k1);
   double* own = smem + (size_t)warp * generic_warp_doubles(D, k1, row_len, cov_len);
   double* oth = own + row_len;
   double* V = oth + row_len;
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(128) accumulate_generic_kernel(
   const double w_sigma = (v.model == SSVI_MODEL_D) ? 1.0 : w_state[0];
 
   {
-    const double* src = v.sampler[dim] + row * row_len;
+    const double* src = v.sampler[dim] + row * (int64_t)row_len;
     for (int i = lane; i < row_len; i += 32) own[i] = src[i];
     for (int i = lane; i < cov_len; i += 32) G[i] = 0.0;
     for (int i = lane; i < D; i += 32) g[i] = 0.0;
@@ -123,18 +123,17 @@ __global__ void __launch_bounds__(128) accumulate_generic_kernel(
     for (int d = 0; d < N; ++d) {
       if (d == dim) continue;
       const int64_t col = v.coords[eid * N + d];
-      const double* src = v.sampler[d] + col * row_len;
+      const double* src = v.sampler[d] + col * (int64_t)row_len;
       for (int i = lane; i < row_len; i += 32) oth[i] = src[i];
       __syncwarp();
-      const ZT* z = z_other + ((int64_t)slot * (N - 1) + jj) * D * k1;
+      const ZT* z = z_other + ((int64_t)slot * (N - 1) + jj) * v.zblk;
       for (int k = lane; k < k1; k += 32) {
         for (int n = 0; n < D; ++n) {
           double x = oth[n];
           if (diag) {
             x += oth[D + n] * ldz(z, (int64_t)n * k1 + k);
           } else {
-            const double* Ln = oth + D + n * D;
-            for (int cc = 0; cc <= n; ++cc) x += Ln[cc] * ldz(z, (int64_t)cc * k1 + k);
+            for (int cc = 0; cc <= n; ++cc) x += oth[smp_L_offset(n, cc, D)] * ldz(z, smp_z_offset(cc, k, D, k1, false));
           }
           V[n * KS + k] = (jj == 0) ? x : V[n * KS + k] * x;
         }
@@ -143,7 +142,7 @@ __global__ void __launch_bounds__(128) accumulate_generic_kernel(
       ++jj;
     }
     // ---- own-row sample, predictive mean, likelihood weights ---------------------------------
-    const ZT* zo = z_own + (int64_t)slot * D * k1;
+    const ZT* zo = z_own + (int64_t)slot * v.zblk;
     double sum_a = 0.0, sum_d = 0.0;
     for (int k0 = 0; k0 < k1; k0 += 32) {
       const int k = k0 + lane;
@@ -155,8 +154,7 @@ __global__ void __launch_bounds__(128) accumulate_generic_kernel(
           if (diag) {
             u += own[D + n] * ldz(zo, (int64_t)n * k1 + k);
           } else {
-            const double* Ln = own + D + n * D;
-            for (int cc = 0; cc <= n; ++cc) u += Ln[cc] * ldz(zo, (int64_t)cc * k1 + k);
+            for (int cc = 0; cc <= n; ++cc) u += own[smp_L_offset(n, cc, D)] * ldz(zo, smp_z_offset(cc, k, D, k1, false));
           }
           f += u * V[n * KS + k];
         }

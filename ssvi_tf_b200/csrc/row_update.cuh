@@ -17,7 +17,7 @@
 struct RowUpdateArgs {
   int32_t D, diag, model, lik, k1;
   int32_t mean_update, cov_update, dim, time_step, fixed_cov;
-  int32_t row_len, cov_len, acc_len;
+  int32_t row_len, srow_len, cov_len, acc_len;
   double eta, cov_eta, poisson_eta, min_eigenval, cov_floor;
   double* params;
   double* sampler;
@@ -161,6 +161,30 @@ __device__ bool cholesky_lower(double* Sx, int D) {
   return ok != 0;
 }
 
+// Sampler-cache row (full covariance, layout in ssvi_common.cuh) <-> row-major lower-triangular D x D.
+__device__ void sampler_store_full(double* __restrict__ srow, const double* mean, const double* Lsm, int D) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int NT = smp_nt(D), NS = smp_ns(D), len = smp_row_len(D, false);
+  for (int i = tid; i < 8 * NT; i += nt) srow[i] = (i < D) ? mean[i] : 0.0;
+  for (int o = 8 * NT + tid; o < len; o += nt) {
+    const int e = o - 8 * NT, tile = e >> 5, g = (e >> 2) & 7, q = e & 3;
+    int ti = 0, base = 0;
+    while (base + smp_tiles_in_row(ti, NS) <= tile) {
+      base += smp_tiles_in_row(ti, NS);
+      ++ti;
+    }
+    const int n = 8 * ti + g, c = 4 * (tile - base) + q;
+    srow[o] = (n < D && c <= n) ? Lsm[n * D + c] : 0.0;
+  }
+}
+
+__device__ void sampler_load_L(const double* __restrict__ srow, double* Lsm, int D) {
+  for (int idx = threadIdx.x; idx < D * D; idx += blockDim.x) {
+    const int n = idx / D, c = idx % D;
+    Lsm[idx] = (c <= n) ? srow[smp_L_offset(n, c, D)] : 0.0;
+  }
+}
+
 // AdaGrad step with the aliasing quirk Q1 (SSVI_TF_interface.py:694-698, 705-713):
 // the stored accumulator becomes acc + g^2, the step uses acc + 2 g^2.
 __device__ __forceinline__ double adagrad_step(double* acc, double g, double eta) {
@@ -286,12 +310,12 @@ __global__ void __launch_bounds__(128) row_update_full_kernel(RowUpdateArgs a) {
   const double* di = acc;
   const double* Di = acc + D;
   double* prow = a.params + row * a.row_len;
-  double* srow = a.sampler + row * a.row_len;
+  double* srow = a.sampler + row * (int64_t)a.srow_len;
 
   bool bad = false;
+  sampler_load_L(srow, Lm, D);
   for (int i = tid; i < DD; i += nt) {
     Sold[i] = prow[D + i];
-    Lm[i] = srow[D + i];
     if (!isfinite(Di[i])) bad = true;
   }
   for (int i = tid; i < D; i += nt) {
@@ -426,10 +450,7 @@ __global__ void __launch_bounds__(128) row_update_full_kernel(RowUpdateArgs a) {
       prow[D + idx] = Sn[idx];
     }
   }
-  for (int i = tid; i < D; i += nt) {
-    prow[i] = mn[i];
-    srow[i] = mn[i];
-  }
+  for (int i = tid; i < D; i += nt) prow[i] = mn[i];
   gm2 = block_sum(gm2, red);
   gc2 = block_sum(gc2, red);
   dm2 = block_sum(dm2, red);
@@ -441,11 +462,13 @@ __global__ void __launch_bounds__(128) row_update_full_kernel(RowUpdateArgs a) {
     a.norm_changes[row * 2 + 1] = sqrt(dc2);
     if (a.si_out) a.si_out[r] = finalize_si(a, acc[D + DD], count, scale);
   }
-  if (!a.fixed_cov) {                                           // sampler cache: chol(S_next)
-    __syncthreads();
+  __syncthreads();
+  if (!a.fixed_cov) {                                           // sampler cache: (m_next, chol(S_next))
     const bool ok = cholesky_lower(Sn, D);
     if (!ok && tid == 0) atomicOr(a.flags, SSVI_FLAG_CHOL_FAIL);
-    for (int idx = tid; idx < DD; idx += nt) srow[D + idx] = Sn[idx];
+    sampler_store_full(srow, mn, Sn, D);
+  } else {
+    for (int i = tid; i < D; i += nt) srow[i] = mn[i];
   }
 }
 
@@ -461,13 +484,14 @@ __global__ void __launch_bounds__(128) refresh_sampler_full_kernel(const double*
   const int tid = threadIdx.x, nt = blockDim.x, DD = D * D, row_len = (D + 1) * D;
   const int64_t row = rows ? rows[blockIdx.x] : (int64_t)blockIdx.x;
   const double* p = params + row * row_len;
-  double* s = sampler + row * row_len;
+  double* s = sampler + row * (int64_t)smp_row_len(D, false);
+  double* mean = sm + DD;
   for (int i = tid; i < DD; i += nt) sm[i] = p[D + i];
-  for (int i = tid; i < D; i += nt) s[i] = p[i];
+  for (int i = tid; i < D; i += nt) mean[i] = p[i];
   __syncthreads();
   const bool ok = cholesky_lower(sm, D);
   if (!ok && tid == 0) atomicOr(flags, SSVI_FLAG_CHOL_FAIL);
-  for (int i = tid; i < DD; i += nt) s[D + i] = sm[i];
+  sampler_store_full(s, mean, sm, D);
 }
 
 __global__ void refresh_sampler_diag_kernel(const double* __restrict__ params, double* __restrict__ sampler,

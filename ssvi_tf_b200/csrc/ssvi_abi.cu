@@ -32,6 +32,21 @@ extern "C" int64_t ssvi_acc_len(const SsviConfig* cfg) {
   return (int64_t)cfg->rank + cov_len_of(*cfg) + 2;
 }
 
+extern "C" int64_t ssvi_sampler_row_len(const SsviConfig* cfg) {
+  if (!cfg) return 0;
+  return smp_row_len(cfg->rank, cfg->cov_kind == SSVI_COV_DIAG);
+}
+
+extern "C" int64_t ssvi_noise_block_len(const SsviConfig* cfg) {
+  if (!cfg) return 0;
+  return smp_zblk(cfg->rank, cfg->k1, cfg->cov_kind == SSVI_COV_DIAG);
+}
+
+extern "C" int64_t ssvi_noise_offset(const SsviConfig* cfg, int32_t c, int32_t k) {
+  if (!cfg) return -1;
+  return smp_z_offset(c, k, cfg->rank, cfg->k1, cfg->cov_kind == SSVI_COV_DIAG);
+}
+
 extern "C" const char* ssvi_last_error(const SsviHandle* h) { return h ? h->err : g_create_err; }
 
 extern "C" int ssvi_create(const SsviConfig* cfg, SsviHandle** out) {
@@ -136,6 +151,8 @@ static DevView make_view(const SsviHandle* h, int dim) {
   v.lik = c.likelihood;
   v.dim = dim;
   v.row_len = row_len_of(c);
+  v.srow_len = smp_row_len(c.rank, c.cov_kind == SSVI_COV_DIAG);
+  v.zblk = smp_zblk(c.rank, c.k1, c.cov_kind == SSVI_COV_DIAG);
   v.cov_len = cov_len_of(c);
   v.acc_len = (int32_t)h->acc_len;
   v.pool_slots = h->pool_slots;
@@ -159,7 +176,7 @@ extern "C" int ssvi_refresh_sampler(SsviHandle* h, int32_t dim, const int64_t* r
     const int64_t total = n_rows * D;
     refresh_sampler_diag_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(h->params[dim], h->sampler[dim], rows, n_rows, D);
   } else {
-    const size_t smem = (size_t)D * D * sizeof(double);
+    const size_t smem = (size_t)(D * D + D) * sizeof(double);
     refresh_sampler_full_kernel<<<(unsigned)n_rows, 128, smem, st>>>(h->params[dim], h->sampler[dim], rows, D, h->d_flags);
   }
   CUDA_TRY(h, cudaGetLastError());
@@ -191,8 +208,11 @@ static int launch_accumulate_mma(SsviHandle* h, const DevView& v, int64_t n_chun
                                  const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
                                  const int64_t* entry_ids, const int64_t* rows, const double* w_state,
                                  double* partial_out, cudaStream_t st) {
-  const int wpb = 4;
-  const size_t smem = (size_t)mma_warp_doubles<NT, SECOND>() * wpb * sizeof(double);
+  const MmaSmem L = mma_smem_layout(NT, v.D, v.k1, (int)sizeof(ZT), SECOND);
+  int wpb = 8;                                        // one CTA per SM; as many warps as shared memory holds
+  while (wpb > 1 && (size_t)L.total * wpb > (size_t)h->max_smem_optin) --wpb;
+  const size_t smem = (size_t)L.total * wpb;
+  if (smem > (size_t)h->max_smem_optin) return fail(h, SSVI_E_INVALID, "accumulate: shared memory%s");
   auto kern = accumulate_mma_kernel<NT, ZT, SECOND>;
   CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const unsigned grid = (unsigned)((n_chunks + wpb - 1) / wpb);
@@ -294,6 +314,7 @@ extern "C" int ssvi_row_update(SsviHandle* h, int32_t dim, int64_t n_rows, const
   a.time_step = time_step;
   a.fixed_cov = fixed_covariance;
   a.row_len = row_len_of(c);
+  a.srow_len = smp_row_len(c.rank, c.cov_kind == SSVI_COV_DIAG);
   a.cov_len = cov_len_of(c);
   a.acc_len = (int32_t)h->acc_len;
   a.eta = c.eta;

@@ -40,7 +40,9 @@ struct DevView {
   int32_t N, D, k1, k2;
   int32_t diag, model, lik;
   int32_t dim;           // mode being swept
-  int32_t row_len;       // doubles per posterior / sampler row: (D+1)*D full, 2*D diag
+  int32_t row_len;       // doubles per posterior row: (D+1)*D full, 2*D diag
+  int32_t srow_len;      // doubles per sampler-cache row (smp_row_len)
+  int32_t zblk;          // elements per (slot, mode) noise block (smp_zblk)
   int32_t cov_len;       // D*D or D
   int32_t acc_len;
   int32_t pool_slots;
@@ -50,6 +52,43 @@ struct DevView {
   const double* sampler[SSVI_MAX_ORDER];
   int32_t* flags;
 };
+
+// ------------------------------------------------------------------------------------------------
+// Sampler cache row layout (library-internal; the posterior `params` keep the reference's layout).
+//   diagonal covariance : [ mean (D) | sqrt(S) (D) ]
+//   full covariance     : [ mean, zero-padded to 8*NT | lower-triangle tiles of L ]
+// with NT = ceil(D/8) row tiles and NS = ceil(D/4) column steps.  Tile (i, j) holds the 8x4 block
+// L[8i..8i+7][4j..4j+3] as 32 doubles in DMMA A-fragment order (element (g, q) at g*4 + q), so one
+// warp reads a fragment as 32 consecutive doubles.  Only tiles touching the lower triangle are stored
+// (j <= min(2i+1, NS-1)), in (i, j) order; entries above the diagonal inside a stored tile are zero.
+// ------------------------------------------------------------------------------------------------
+__host__ __device__ inline int smp_nt(int D) { return (D + 7) >> 3; }
+__host__ __device__ inline int smp_ns(int D) { return (D + 3) >> 2; }
+__host__ __device__ inline int smp_tiles_in_row(int i, int NS) { return (2 * (i + 1) < NS) ? 2 * (i + 1) : NS; }
+__host__ __device__ inline int smp_tile_base(int i, int NS) {
+  int s = 0;
+  for (int r = 0; r < i; ++r) s += smp_tiles_in_row(r, NS);
+  return s;
+}
+__host__ __device__ inline int smp_row_len(int D, bool diag) {
+  if (diag) return 2 * D;
+  return 8 * smp_nt(D) + 32 * smp_tile_base(smp_nt(D), smp_ns(D));
+}
+// offset of L[n][c] (c <= n) inside a full-covariance sampler row
+__host__ __device__ inline int smp_L_offset(int n, int c, int D) {
+  const int NS = smp_ns(D);
+  return 8 * smp_nt(D) + 32 * (smp_tile_base(n >> 3, NS) + (c >> 2)) + (n & 7) * 4 + (c & 3);
+}
+// Noise block of one (slot, mode): element (c, k).
+//   diagonal covariance : [c][k]                       (lanes over k read consecutive elements)
+//   full covariance     : DMMA B-fragment order, ((k/8)*NS + c/4)*32 + (k%8)*4 + (c%4)
+__host__ __device__ inline int smp_zblk(int D, int k1, bool diag) {
+  return diag ? D * k1 : ((k1 + 7) >> 3) * smp_ns(D) * 32;
+}
+__host__ __device__ inline int smp_z_offset(int c, int k, int D, int k1, bool diag) {
+  if (diag) return c * k1 + k;
+  return ((k >> 3) * smp_ns(D) + (c >> 2)) * 32 + (k & 7) * 4 + (c & 3);
+}
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

@@ -43,11 +43,26 @@ def build_csr(coords, dims):
     return rowptr, perm
 
 
+def noise_block_len(D, k1, diag):
+    """Elements of one (slot, mode) noise block == ssvi_noise_block_len (include/ssvi_b200.h)."""
+    return D * k1 if diag else ((k1 + 7) // 8) * ((D + 3) // 4) * 32
+
+
+def noise_offsets(D, k1, diag):
+    """off[c, k] = position of element (component c, sample k) inside a block == ssvi_noise_offset."""
+    c = np.arange(D)[:, None]
+    k = np.arange(k1)[None, :]
+    if diag:
+        return c * k1 + k
+    return ((k // 8) * ((D + 3) // 4) + c // 4) * 32 + (k % 8) * 4 + (c % 4)
+
+
 class NoisePool(object):
     """The supplied standard variates (see include/ssvi_b200.h "Noise contract").
 
-    Device layouts: z_other [P][N-1][D][k1], z_own [P][D][k1], r_w [P][k1], z_f [P][k2][k1].
-    Entry number b of a row's minibatch reads slot b mod P."""
+    Device layouts: z_other [P][N-1][block], z_own [P][block], r_w [P][k1], z_f [P][k2][k1]; element
+    (c, k) of a block sits at noise_offsets(D, k1, diag)[c, k] (plain [c][k] for a diagonal covariance,
+    DMMA B-fragment order for a full one).  Entry number b of a row's minibatch reads slot b mod P."""
 
     def __init__(self, z_other, z_own, r_w, z_f):
         self.z_other, self.z_own, self.r_w, self.z_f = z_other, z_own, r_w, z_f
@@ -55,11 +70,12 @@ class NoisePool(object):
         self.dtype = z_own.dtype
 
     @classmethod
-    def random(cls, slots, N, D, k1, k2, need_second_layer, device, dtype=torch.float32, seed=319):
+    def random(cls, slots, N, D, k1, k2, need_second_layer, device, dtype=torch.float32, seed=319, diag=False):
         g = torch.Generator(device=device)
         g.manual_seed(seed)
-        z_other = torch.randn((slots, N - 1, D, k1), generator=g, device=device, dtype=dtype)
-        z_own = torch.randn((slots, D, k1), generator=g, device=device, dtype=dtype)
+        blk = noise_block_len(D, k1, diag)
+        z_other = torch.randn((slots, N - 1, blk), generator=g, device=device, dtype=dtype)
+        z_own = torch.randn((slots, blk), generator=g, device=device, dtype=dtype)
         r_w = z_f = None
         if need_second_layer:
             u = torch.rand((slots, k1), generator=g, device=device, dtype=torch.float64).clamp_(min=1e-300)
@@ -68,14 +84,21 @@ class NoisePool(object):
         return cls(z_other, z_own, r_w, z_f)
 
     @classmethod
-    def from_tape(cls, tape, device, dtype=torch.float64):
+    def from_tape(cls, tape, device, dtype=torch.float64, diag=False):
         """tape: numpy-natural layout (z_other (B,N-1,k1,D), z_own (B,k1,D), r_w (B,k1), z_f (B,k2,k1))."""
-        def dev(a, perm=None):
-            if a is None:
-                return None
-            t = torch.as_tensor(np.ascontiguousarray(a if perm is None else np.transpose(a, perm)))
-            return t.to(device=device, dtype=dtype).contiguous()
-        return cls(dev(tape.z_other, (0, 1, 3, 2)), dev(tape.z_own, (0, 2, 1)), dev(tape.r_w), dev(tape.z_f))
+        k1, D = tape.z_own.shape[1], tape.z_own.shape[2]
+        off = noise_offsets(D, k1, diag).reshape(-1)                  # [c, k] flattened
+        blk = noise_block_len(D, k1, diag)
+
+        def block(a):                                                 # (..., k1, D) -> (..., blk)
+            src = np.swapaxes(a, -1, -2).reshape(a.shape[:-2] + (D * k1,))
+            out = np.zeros(a.shape[:-2] + (blk,), dtype=np.float64)
+            out[..., off] = src
+            return torch.as_tensor(out).to(device=device, dtype=dtype).contiguous()
+
+        def dev(a):
+            return None if a is None else torch.as_tensor(np.ascontiguousarray(a)).to(device=device, dtype=dtype)
+        return cls(block(tape.z_other), block(tape.z_own), dev(tape.r_w), dev(tape.z_f))
 
 
 class SweepPlan(object):
@@ -174,7 +197,8 @@ class Engine(object):
         rl = 2 * self.D if self.diag else (self.D + 1) * self.D
         self.row_len = rl
         self.params = [torch.zeros((n, rl // self.D, self.D), **f64) for n in self.dims]
-        self.sampler = [torch.zeros((n, rl // self.D, self.D), **f64) for n in self.dims]
+        self.srow_len = int(self.lib.ssvi_sampler_row_len(ctypes.byref(c)))
+        self.sampler = [torch.zeros((n, self.srow_len), **f64) for n in self.dims]
         self.ada_mean = [torch.ones((n, self.D), **f64) for n in self.dims]        # ada_acc_grad^T (:83)
         self.ada_cov = [torch.zeros((n, self.D), **f64) for n in self.dims]        # ada_acc_grad_cov^T (:41)
         self.norm_changes = [torch.zeros((n, 2), **f64) for n in self.dims]
@@ -228,8 +252,10 @@ class Engine(object):
     # -------------------------------------------------------------------------------------------
     def set_noise(self, pool):
         need2 = self.cfg["model"] != "d"
-        assert pool.z_other.shape[1:] == (self.N - 1, self.D, self.cfg["k1"]), pool.z_other.shape
-        assert pool.z_own.shape[1:] == (self.D, self.cfg["k1"])
+        blk = int(self.lib.ssvi_noise_block_len(ctypes.byref(self._c)))
+        assert blk == noise_block_len(self.D, self.cfg["k1"], self.diag)
+        assert pool.z_other.shape[1:] == (self.N - 1, blk), pool.z_other.shape
+        assert pool.z_own.shape[1:] == (blk,)
         if need2:
             assert pool.r_w.shape[1:] == (self.cfg["k1"],) and pool.z_f.shape[1:] == (self.cfg["k2"], self.cfg["k1"])
         want = torch.float32 if self._c.noise_dtype == _lib.NOISE_F32 else torch.float64
@@ -253,8 +279,9 @@ class Engine(object):
             raise AssertionError("; ".join(t for b, t in FLAG_TEXT.items() if f.value & b))
 
     # -------------------------------------------------------------------------------------------
-    def _chunk_tables(self, dim, rows_h, seg_start, seg_len):
-        """rows_h: host int64 row ids; seg_start/seg_len: each row's minibatch as a run of entry_ids."""
+    def _chunk_tables(self, dim, rows_h, seg_start, seg_len, slot_offset=None):
+        """rows_h: host int64 row ids; seg_start/seg_len: each row's minibatch as a run of entry_ids;
+        slot_offset: per-row position of this shard's first entry inside the GLOBAL minibatch (multi-GPU)."""
         W = self.chunk_entries
         nch = (seg_len + W - 1) // W
         rcp = np.zeros(len(rows_h) + 1, dtype=np.int64)
@@ -265,25 +292,28 @@ class Engine(object):
         chunk_start = seg_start[chunk_row] + t * W
         chunk_len = np.minimum(W, seg_len[chunk_row] - t * W)
         dev = self.device
+        slot0 = t * W if slot_offset is None else t * W + np.asarray(slot_offset, dtype=np.int64)[chunk_row]
         return (torch.as_tensor(chunk_row.astype(np.int32)).to(dev), torch.as_tensor(chunk_start).to(dev),
-                torch.as_tensor(chunk_len.astype(np.int32)).to(dev), torch.as_tensor((t * W).astype(np.int32)).to(dev),
+                torch.as_tensor(chunk_len.astype(np.int32)).to(dev),
+                torch.as_tensor(slot0.astype(np.int32)).to(dev),
                 torch.as_tensor(rcp).to(dev))
 
-    def plan_full(self, dim, rows=None):
+    def plan_full(self, dim, rows=None, slot_offset=None):
         """Every observed entry of every listed row (scale = 1): the throughput sweep."""
-        key = (dim, None if rows is None else tuple(int(r) for r in rows))
+        key = (dim, None if rows is None else tuple(int(r) for r in rows),
+               None if slot_offset is None else hash(np.asarray(slot_offset).tobytes()))
         if key in self._full_plans:
             return self._full_plans[key]
         rows_h = np.arange(self.dims[dim], dtype=np.int64) if rows is None else np.asarray(rows, dtype=np.int64)
         rp = self.rowptr_h[dim]
         seg_start, seg_len = rp[rows_h], rp[rows_h + 1] - rp[rows_h]
-        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len)
+        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset)
         plan = SweepPlan(dim, torch.as_tensor(rows_h).to(self.device), torch.as_tensor(seg_len).to(self.device),
                          self.perm[dim], tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
         self._full_plans[key] = plan
         return plan
 
-    def plan_minibatch(self, dim, rows, batch_size, rng=None, sub_idx=None):
+    def plan_minibatch(self, dim, rows, batch_size, rng=None, sub_idx=None, slot_offset=None):
         """The reference's minibatch (SSVI_TF_interface.py:170-174): rows holding more than batch_size
         entries are subsampled without replacement.  sub_idx: optional {row: index array} (noise-tape
         item #0) overriding the draw; rng: numpy Generator otherwise."""
@@ -291,7 +321,7 @@ class Engine(object):
         rp = self.rowptr_h[dim]
         lens = rp[rows_h + 1] - rp[rows_h]
         if not np.any(lens > batch_size):
-            return self.plan_full(dim, rows_h)
+            return self.plan_full(dim, rows_h, slot_offset)
         ids, seg_len = [], np.minimum(lens, batch_size)
         for r, row in enumerate(rows_h):
             seg = self.perm_h[dim][rp[row]:rp[row + 1]]
@@ -304,7 +334,7 @@ class Engine(object):
             ids.append(seg)
         seg_start = np.zeros(len(rows_h), dtype=np.int64)
         np.cumsum(seg_len[:-1], out=seg_start[1:])
-        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len)
+        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset)
         entry_ids = torch.as_tensor(np.concatenate(ids) if ids else np.zeros(0, np.int64)).to(self.device)
         return SweepPlan(dim, torch.as_tensor(rows_h).to(self.device), torch.as_tensor(lens).to(self.device),
                          entry_ids, tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)

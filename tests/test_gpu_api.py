@@ -44,7 +44,7 @@ def test_update_natural_param_batch_is_drop_in(name):
         m.time_step = st0["time_step"]
         m.w_sigma, m.w_ada_grad = st0["w_sigma"], st0["w_ada_grad"]
         dim, row, tape = step["dim"], step["row"], step["tape"]
-        m.update_natural_param_batch(dim, row, noise=pkg.NoisePool.from_tape(tape, m.engine.device, torch.float64),
+        m.update_natural_param_batch(dim, row, noise=pkg.NoisePool.from_tape(tape, m.engine.device, torch.float64, diag=cfg["diag"]),
                                      sub_idx=tape.sub_idx)
         m.engine.check_flags()
         mean, cov = m.posterior.get_vector_distribution(dim, row)

@@ -28,7 +28,7 @@ def test_cuda_matches_reference_golden(name, noise_dtype):
     for k, step in enumerate(case["steps"]):
         engine_load_state(eng, case["state0"])
         dim, row, tape = step["dim"], step["row"], step["tape"]
-        eng.set_noise(NoisePool.from_tape(tape, eng.device, noise_dtype))
+        eng.set_noise(NoisePool.from_tape(tape, eng.device, noise_dtype, diag=cfg["diag"]))
         sub = None if tape.sub_idx is None else {row: tape.sub_idx}
         plan = eng.plan_minibatch(dim, [row], cfg["batch_size"], sub_idx=sub)
         # touched rows / counts are integers: exact
@@ -57,7 +57,7 @@ def test_cuda_batched_rows_match_oracle(model, lik, diag):
     rowptr, perm = so.build_index(coords, dims)
     eng = _engine(cfg, dims, coords, vals, chunk_entries=3)
     pool = so.make_tape(rng, cfg, 3, B)                # B slots: entry b of every row uses slot b
-    eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64))
+    eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=diag))
     for dim in range(3):
         engine_load_state(eng, st0)
         rows = np.arange(dims[dim])
@@ -107,7 +107,7 @@ def test_full_row_sweep_chunking_is_invariant():
     outs = []
     for ce in (1, 7, 64):
         eng = _engine(cfg, dims, coords, vals, chunk_entries=ce)
-        eng.set_noise(NoisePool.random(16, 3, D, 32, 4, False, eng.device, torch.float64, seed=1))
+        eng.set_noise(NoisePool.random(16, 3, D, 32, 4, False, eng.device, torch.float64, seed=1, diag=False))
         engine_load_state(eng, st0)
         acc = eng.accumulate(eng.plan_full(0)).cpu().numpy().copy()
         outs.append(acc)
@@ -147,7 +147,7 @@ def test_mma_path_matches_oracle_and_generic(D, k1, model, lik):
     for path in (0, 1):
         eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=4,
                      kernel_path=path)
-        eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float32))
+        eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float32, diag=False))
         engine_load_state(eng, st0)
         dim = 1
         rows = np.arange(dims[dim])
