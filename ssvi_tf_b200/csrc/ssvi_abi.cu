@@ -188,7 +188,7 @@ static int launch_accumulate_generic(SsviHandle* h, const DevView& v, int64_t n_
                                      const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
                                      const int64_t* entry_ids, const int64_t* rows, const double* w_state,
                                      double* partial_out, cudaStream_t st) {
-  const size_t per_warp = generic_warp_doubles(v.D, v.k1, v.row_len, v.cov_len) * sizeof(double);
+  const size_t per_warp = generic_warp_doubles(v.D, v.k1, v.srow_len, v.cov_len) * sizeof(double);
   int wpb = 4;
   while (wpb > 1 && per_warp * wpb > (size_t)h->max_smem_optin) wpb >>= 1;
   const size_t smem = per_warp * wpb;
