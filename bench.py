@@ -151,7 +151,7 @@ class DeviceTensorData(object):
         self.min_count = int(vals.min().item()) if c["lik"] == "poisson" else 0
 
 
-def build_model(c, data, device, group, chunk_entries, noise_slots):
+def build_model(c, data, device, group, chunk_entries, noise_slots, engine_kwargs=None):
     import torch
     import ssvi_tf_b200 as pkg
     cls = {"d": pkg.SSVI_TF_d, "simple": pkg.SSVI_TF_simple, "robust": pkg.SSVI_TF_robust}[c["model"]]
@@ -160,7 +160,7 @@ def build_model(c, data, device, group, chunk_entries, noise_slots):
     np.random.seed(319)
     return cls(data, D, diag=c["diag"], mean0=mean0, cov0=np.eye(D) * 0.1, k1=c["k1"], k2=c["k2"], batch_size=128,
                cov_eta=c.get("cov_eta", 1), randstart=True, device=device, noise_dtype=torch.float32,
-               noise_slots=noise_slots, chunk_entries=chunk_entries, process_group=group)
+               noise_slots=noise_slots, chunk_entries=chunk_entries, process_group=group, engine_kwargs=engine_kwargs)
 
 
 def one_step(model):
@@ -253,6 +253,8 @@ def main():
     ap.add_argument("--chunk-entries", type=int, default=16)
     ap.add_argument("--noise-slots", type=int, default=128)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--table-mb", type=float, default=48.0, help="sample-table budget per call (L2-resident)")
+    ap.add_argument("--sweep-chunk", type=int, default=64, help="max entries of one (row, slot) chunk")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     c = CONFIGS[args.config]
@@ -273,7 +275,8 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device(device))
         group = dist.group.WORLD
     data = DeviceTensorData(c, device, seed=319 + int(args.config[1:]) + 1000 * rank, scale=args.scale)
-    model = build_model(c, data, device, group, args.chunk_entries, args.noise_slots)
+    model = build_model(c, data, device, group, args.chunk_entries, args.noise_slots,
+                        dict(table_budget_bytes=int(args.table_mb * (1 << 20)), sweep_chunk_entries=args.sweep_chunk))
     eng = model.engine
     N = model.order
     nnz_train = eng.nnz
@@ -333,7 +336,9 @@ def main():
     # ---- end-to-end arm: host buffers in, host result out, every step ----------------------------
     pin = lambda x: x.cpu().pin_memory()                                      # noqa: E731
     h_coords, h_vals = pin(eng.coords), pin(eng.vals)
-    h_perm = [pin(p) for p in eng.perm]
+    # per-mode entry lists the sweep kernels read: the slot-major lists of the sample-table path where it applies
+    d_perm = [eng.plan_sweep(d).entry_ids if eng.sweep_supported else eng.perm[d] for d in range(N)]
+    h_perm = [pin(p) for p in d_perm]
     nz = eng.noise
     h_noise = [pin(x) for x in (nz.z_other, nz.z_own, nz.r_w, nz.z_f) if x is not None]
     d_noise = [x for x in (nz.z_other, nz.z_own, nz.r_w, nz.z_f) if x is not None]
@@ -345,7 +350,7 @@ def main():
     def e2e_step():
         eng.coords.copy_(h_coords, non_blocking=True)
         eng.vals.copy_(h_vals, non_blocking=True)
-        for dp, hp in zip(eng.perm, h_perm):
+        for dp, hp in zip(d_perm, h_perm):
             dp.copy_(hp, non_blocking=True)
         for dn, hn in zip(d_noise, h_noise):
             dn.copy_(hn, non_blocking=True)
@@ -380,6 +385,8 @@ def main():
             "config": {"workload": c["desc"], "config_id": args.config, "nnz_train_per_gpu": nnz_train,
                        "units_per_step_per_gpu": units_per_step, "sweep": "full rows (scale=1), all modes",
                        "noise": "f32 pool, %d slots" % eng.noise.slots, "chunk_entries": args.chunk_entries,
+                       "path": ("sample-table sweep (slot-major), %d slots/call" % eng.plan_sweep(0).groups[0][1])
+                       if eng.sweep_supported else "direct",
                        "l2": "inputs larger than L2 (COO+CSR %.0f MB per GPU)" % (h2d / 1e6),
                        "parallelism": "entries sharded x%d, all-reduce of row accumulators" % world},
             "roofline": roofline, "cpu_baseline": cpu,

@@ -159,6 +159,26 @@ int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t*
                     const int64_t* entry_ids, const int64_t* rows, const double* w_state,
                     double* partial_out, void* stream);
 
+/* ---- The sample-table path for full sweeps (slot-major; SSVI_TF_d, full covariance, rank <= 32, k1 % 8 == 0,
+ * k1 <= 64, order <= 4).  Same mathematics and the same outputs as ssvi_accumulate, organised so that the sample
+ * X(j, s) = m_j + L_j Z(s, jj) of sample_vjs_batch (SSVI_TF_interface.py:732-750) is evaluated once per (other-mode
+ * row j, noise slot s) instead of once per (entry, mode): with P pool slots a sweep asks for each pair nnz / (n_j P)
+ * times.  The caller runs a sweep as a sequence of calls over slot groups [slot_lo, slot_lo + n_slots); each call
+ * first fills the table workspace (n_slots * sum_{d != dim} dims[d] records) and then processes the chunks of those
+ * slots.  A chunk here is a run of entries of ONE row that all read ONE noise slot:
+ *   chunk_slot[c]   int32  that slot (must lie inside the call's slot group)
+ *   chunk_out[c]    int64  index of the chunk's record inside partial_out (any order; lets the caller keep the
+ *                          records row-major for ssvi_reduce_chunks while the launch order is slot-major)
+ * chunk_row / chunk_start / chunk_len / entry_ids / rows / partial_out as for ssvi_accumulate.
+ * table_ws: device workspace of at least ssvi_sweep_table_bytes(h, dim, n_slots) bytes, 16-byte aligned. */
+int ssvi_sweep_supported(const SsviHandle* h);                                   /* 1 if this path applies to h's config */
+int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int32_t n_slots);
+int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo, int32_t n_slots, int64_t n_chunks,
+                          const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
+                          const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
+                          const int64_t* rows, void* table_ws, int64_t table_ws_bytes, double* partial_out,
+                          void* stream);
+
 /* Deterministic in-order sum of the chunk records of each row:
  *   acc_out[r] = sum_{c = row_chunk_ptr[r] .. row_chunk_ptr[r+1]-1} partial[c]
  * acc_out double [n_rows][ssvi_acc_len] is the payload of the multi-GPU all-reduce. */

@@ -29,7 +29,7 @@ class SSVI_TF(object):
                  unstable_cov=False, k1=64, k2=64, batch_size=128,
                  eta=1, cov_eta=1, sigma_eta=1, randstart=True,
                  device=None, noise_dtype=torch.float32, noise_slots=None, noise_seed=319,
-                 chunk_entries=16, process_group=None):
+                 chunk_entries=16, process_group=None, engine_kwargs=None):
         self.tensor = tensor
         self.dims = list(tensor.dims)
         self.datatype = tensor.datatype
@@ -99,7 +99,7 @@ class SSVI_TF(object):
         if device is None:
             device = "cuda:%d" % torch.cuda.current_device() if torch.cuda.is_available() else "cuda"
         self.engine = Engine(cfg, self.dims, tensor.train_entries, tensor.train_vals, device=device,
-                             noise_dtype=noise_dtype, chunk_entries=chunk_entries)
+                             noise_dtype=noise_dtype, chunk_entries=chunk_entries, **(engine_kwargs or {}))
         eng = self.engine
         for d, p in enumerate(self.posterior.initial_values()):
             eng.params[d].copy_(torch.as_tensor(p))
@@ -223,10 +223,15 @@ class SSVI_TF(object):
 
     def sweep(self, dim):
         """One Jacobi sweep over mode `dim`: every observed entry of every row (scale = 1)."""
-        rp = self.engine.rowptr_h[dim]
+        eng = self.engine
+        rp = eng.rowptr_h[dim]
         rows = np.arange(self.dims[dim], dtype=np.int64)
         off, n_obs = self._shard_info(dim, rows, rp[1:] - rp[:-1])
-        self._run_plan(self.engine.plan_full(dim, None, off), n_obs)
+        if eng.noise is None:
+            self.fresh_noise()
+        # SSVI_TF_d + full covariance: the slot-major sample-table kernels; otherwise the direct kernels
+        plan = eng.plan_sweep(dim, off) if eng.sweep_supported else eng.plan_full(dim, None, off)
+        self._run_plan(plan, n_obs)
 
     def update_hyper_parameter(self, dim):
         """pSigma[dim] = sum_rows (tr S + m.m) / (n_dim D)  (:146-160), as a device reduction."""

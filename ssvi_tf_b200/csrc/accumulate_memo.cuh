@@ -1,0 +1,363 @@
+// Stages 1-3 for FULL SWEEPS of SSVI_TF_d, full covariance, D <= 32, k1 % 8 == 0, k1 <= 64: the sample-table path.
+//
+// In a sweep, entry b of a row's list reads noise slot (b mod P).  The Monte-Carlo sample of a gathered other-mode row
+//       X(j, s) = m_j + L_j Z(s, jj)            (D x k1, sample_vjs_batch, SSVI_TF_interface.py:732-750)
+// depends on (row j, slot s) only, and a sweep asks for each pair nnz / (n_j P) times (62 times at BASELINE config 2).
+// The direct kernel (accumulate_mma.cuh) re-evaluates the D x D x k1 product for every (entry, mode): 3/4 of its FP64
+// tensor-pipe time.  Here the sweep runs slot-major instead:
+//   sample_table_kernel      X(j, s) for every row of every other mode and a group of slots -> table (L2-resident);
+//                            the same DMMA sequence as the direct kernel, so the samples are bit-identical
+//   accumulate_memo_kernel   one CTA per (row, slot) group of entries; per entry it gathers N-1 table records (coalesced
+//                            512-byte fragment tiles, prefetched one k-tile ahead), forms V = Hadamard product, the
+//                            predictive mean f_k = u_k . v_k against the own-row sample U(row, slot) (evaluated ONCE per
+//                            CTA), the averaged log-likelihood derivatives (SSVI_TF_d.py:31-57, quirk Q3) and
+//                            G += w V V^T by DMMA straight from the V registers.
+// What is left per entry on the FP64 pipe is the contraction (NP*2*k1/8 DMMAs) + 3 D*k1 element-wise passes.
+//
+// Fragment layout (m8n8k4, g = lane>>2, q = lane&3): tile (i, t) of a sample holds x[n = 8i+g][k = 8t+2q+{0,1}] as one
+// double2 per lane, i.e. a table record is [NT][KT][32] double2 and a warp reads a tile as 512 contiguous bytes.
+#pragma once
+#include "accumulate_mma.cuh"
+
+#define SSVI_MEMO_MAX_OTH 3
+
+struct MemoView {
+  int32_t n_oth;                          // N - 1
+  int32_t rec_len;                        // doubles per table record = NT * KT * 64
+  int32_t slot_lo, n_slots;               // slots [slot_lo, slot_lo + n_slots) are in the table
+  int32_t od[SSVI_MEMO_MAX_OTH];          // other modes, ascending
+  int64_t n_rows[SSVI_MEMO_MAX_OTH];      // rows of each other mode
+  int64_t rec_base[SSVI_MEMO_MAX_OTH + 1];// first record of each other mode's block; [n_oth] = total records
+  double* tab;
+};
+
+__host__ __device__ inline int memo_rec_len(int D, int k1) { return smp_nt(D) * (k1 >> 3) * 64; }
+// record of (local slot sl, other-mode ordinal jj, row j)
+__device__ __forceinline__ int64_t memo_rec(const MemoView& mv, int jj, int sl, int64_t j) {
+  return mv.rec_base[jj] + (int64_t)sl * mv.n_rows[jj] + j;
+}
+
+__host__ __device__ inline int memo_stage_bytes(int D, int k1, int zsize) {
+  return smp_row_len(D, false) * 8 + ((smp_zblk(D, k1, false) * zsize + 15) / 16) * 16;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// One warp per table record.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int NT, typename ZT>
+__global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView mv, const ZT* __restrict__ z_other) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int g = lane >> 2;
+  const int64_t rec = (int64_t)blockIdx.x * wpb + warp;
+  if (rec >= mv.rec_base[mv.n_oth]) return;
+  const int D = v.D, k1 = v.k1, KT = k1 >> 3, NS = smp_ns(D);
+  int jj = 0;
+#pragma unroll
+  for (int a = 1; a < SSVI_MEMO_MAX_OTH; ++a)
+    if (a < mv.n_oth && rec >= mv.rec_base[a]) jj = a;
+  const int64_t local = rec - mv.rec_base[jj];
+  const int sl = (int)(local / mv.n_rows[jj]);
+  const int64_t j = local - (int64_t)sl * mv.n_rows[jj];
+  const int slot = mv.slot_lo + sl;
+
+  const int stage = memo_stage_bytes(D, k1, (int)sizeof(ZT));
+  double* S = reinterpret_cast<double*>(smem_raw + (size_t)warp * stage);
+  ZT* zs = reinterpret_cast<ZT*>(S + v.srow_len);
+  {
+    const double2* src = reinterpret_cast<const double2*>(v.sampler[mv.od[jj]] + j * (int64_t)v.srow_len);
+    double2* dst = reinterpret_cast<double2*>(S);
+    for (int i = lane; i < (v.srow_len >> 1); i += 32) dst[i] = src[i];
+    const ZT* zsrc = z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
+    for (int i = lane; i < v.zblk; i += 32) zs[i] = zsrc[i];
+  }
+  __syncwarp();
+  double vv[NT][8][2];
+  double fp[8][2];
+  mma_sample_mode<NT, ZT, false>(S, zs, NS, KT, lane, g, true, vv, fp);
+  double2* out = reinterpret_cast<double2*>(mv.tab + rec * (int64_t)mv.rec_len);
+#pragma unroll
+  for (int i = 0; i < NT; ++i) {
+    if (8 * i + g < D) {
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (t < KT) out[(i * KT + t) * 32 + lane] = make_double2(vv[i][t][0], vv[i][t][1]);
+    }
+  }
+}
+
+// x = m + L z for row-tile i and k-tile t only (own-row sample of the memo kernel's prologue)
+template <typename ZT>
+__device__ __forceinline__ void mma_sample_tile(const double* __restrict__ S, const ZT* __restrict__ z, int NT, int NS,
+                                                int lane, int g, int i, int t, double& c0, double& c1) {
+  c0 = c1 = S[8 * i + g];
+  const double* At = S + 8 * NT + 32 * (i * (i + 1)) + lane;
+  const int nj = min(2 * (i + 1), NS);
+  for (int j = 0; j < nj; ++j) dmma_m8n8k4(c0, c1, At[32 * j], zfrag(z, (t * NS + j) * 32 + lane));
+}
+
+// Shared memory of one CTA (4 warps), bytes: one region reused as {staging | U | reduction} + per-warp G.
+__host__ __device__ inline int memo_cta_smem(int NT, int D, int k1, int zsize) {
+  const int KT = k1 >> 3, NP = NT * (NT + 1) / 2;
+  int a = memo_stage_bytes(D, k1, zsize);
+  const int us = NT * KT * 32 * 16;
+  const int red = 4 * (NT * 8) * 8;
+  if (us > a) a = us;
+  if (red > a) a = red;
+  return a + 4 * NP * 64 * 8;
+}
+
+__device__ __forceinline__ double2 ld_tab(const double2* p) { return __ldcg(p); }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int NT, int NOTH, typename ZT>
+__global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
+    DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
+    const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
+    const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
+    const int64_t* __restrict__ entry_ids, const int64_t* __restrict__ rows, const ZT* __restrict__ z_own,
+    double* __restrict__ partial_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int NP = NT * (NT + 1) / 2;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, q = lane & 3;
+  const int64_t c = blockIdx.x;
+  if (c >= n_chunks) return;
+  const int N = v.N, D = v.D, k1 = v.k1, KT = k1 >> 3, NS = smp_ns(D);
+  const int64_t row = rows[chunk_row[c]];
+  const int64_t start = chunk_start[c];
+  const int len = chunk_len[c], slot = chunk_slot[c];
+  const int sl = slot - mv.slot_lo;
+
+  const int region = memo_cta_smem(NT, D, k1, (int)sizeof(ZT)) - 4 * NP * 64 * 8;
+  double* S = reinterpret_cast<double*>(smem_raw);
+  ZT* zs = reinterpret_cast<ZT*>(S + v.srow_len);
+  double2* Us = reinterpret_cast<double2*>(smem_raw);
+  double* red = reinterpret_cast<double*>(smem_raw);
+  double2* Gs = reinterpret_cast<double2*>(smem_raw + region) + warp * (NP * 32);
+
+  // ---- prologue: U(row, slot) = m + L z_own, once per CTA (ui samples, SSVI_TF_interface.py:251-254) --------------------
+  {
+    const double2* src = reinterpret_cast<const double2*>(v.sampler[v.dim] + row * (int64_t)v.srow_len);
+    double2* dst = reinterpret_cast<double2*>(S);
+    for (int i = tid; i < (v.srow_len >> 1); i += 128) dst[i] = src[i];
+    const ZT* zsrc = z_own + (int64_t)slot * v.zblk;
+    for (int i = tid; i < v.zblk; i += 128) zs[i] = zsrc[i];
+  }
+#pragma unroll
+  for (int p = 0; p < NP; ++p) Gs[p * 32 + lane] = make_double2(0.0, 0.0);
+  __syncthreads();
+  double uc[NT][2][2];                                  // warp w: k-tiles t = w and w + 4
+#pragma unroll
+  for (int i = 0; i < NT; ++i)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int t = warp + 4 * h;
+      uc[i][h][0] = uc[i][h][1] = 0.0;
+      if (t < KT) mma_sample_tile<ZT>(S, zs, NT, NS, lane, g, i, t, uc[i][h][0], uc[i][h][1]);
+    }
+  __syncthreads();                                      // staging is dead: the region becomes U
+#pragma unroll
+  for (int i = 0; i < NT; ++i)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int t = warp + 4 * h;
+      if (t < KT) Us[(i * KT + t) * 32 + lane] = make_double2(uc[i][h][0], uc[i][h][1]);
+    }
+  __syncthreads();
+
+  // ---- main loop: warp w takes entries w, w+4, ... of the chunk ----------------------------------------------------------
+  const int my_cnt = (len - warp + 3) >> 2;             // entries of this warp (len >= 1; may be 0 for high warps)
+  double gp[NT];
+#pragma unroll
+  for (int i = 0; i < NT; ++i) gp[i] = 0.0;
+  const double2* tab2 = reinterpret_cast<const double2*>(mv.tab);
+  const int rec2 = mv.rec_len >> 1;                     // double2 per record
+  // lanes holding padding rows (n >= D) never load
+  bool act[NT];
+#pragma unroll
+  for (int i = 0; i < NT; ++i) act[i] = (8 * i + g) < D;
+
+  for (int b0 = 0; b0 < my_cnt; b0 += 32) {
+    // lane-parallel fetch of up to 32 entries' value and table records
+    const int nb = min(32, my_cnt - b0);
+    double my_y = 0.0;
+    int32_t my_rec[NOTH];
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = 0;
+    if (lane < nb) {
+      const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
+      my_y = v.vals[eid];
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj)
+        my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
+    }
+    double2 cur[NOTH][NT];
+    {
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) {
+        const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
+#pragma unroll
+        for (int i = 0; i < NT; ++i) cur[jj][i] = act[i] ? ld_tab(p + (i * KT) * 32) : make_double2(0.0, 0.0);
+      }
+    }
+    for (int el = 0; el < nb; ++el) {
+      const double y = __shfl_sync(0xffffffffu, my_y, el);
+      const double2* pc[NOTH];
+      const double2* pn[NOTH];
+      const bool more = el + 1 < nb;
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) {
+        pc[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], el) * rec2 + lane;
+        pn[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], more ? el + 1 : el) * rec2 + lane;
+      }
+      double acc[NP][2];
+#pragma unroll
+      for (int p = 0; p < NP; ++p) acc[p][0] = acc[p][1] = 0.0;
+      double fp[8][2];
+      double rs[NT];
+#pragma unroll
+      for (int i = 0; i < NT; ++i) rs[i] = 0.0;
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        fp[t][0] = fp[t][1] = 0.0;
+        if (t < KT) {
+          double2 nxt[NOTH][NT];
+          const bool in_entry = t + 1 < KT;
+          if (in_entry || more) {
+#pragma unroll
+            for (int jj = 0; jj < NOTH; ++jj) {
+              const double2* p = in_entry ? pc[jj] + (t + 1) * 32 : pn[jj];
+#pragma unroll
+              for (int i = 0; i < NT; ++i) nxt[jj][i] = act[i] ? ld_tab(p + (i * KT) * 32) : make_double2(0.0, 0.0);
+            }
+          } else {
+#pragma unroll
+            for (int jj = 0; jj < NOTH; ++jj)
+#pragma unroll
+              for (int i = 0; i < NT; ++i) nxt[jj][i] = make_double2(0.0, 0.0);
+          }
+          double2 vv[NT];
+#pragma unroll
+          for (int i = 0; i < NT; ++i) {
+            vv[i] = cur[0][i];
+#pragma unroll
+            for (int jj = 1; jj < NOTH; ++jj) {
+              vv[i].x *= cur[jj][i].x;
+              vv[i].y *= cur[jj][i].y;
+            }
+            const double2 u = Us[(i * KT + t) * 32 + lane];
+            fp[t][0] += u.x * vv[i].x;
+            fp[t][1] += u.y * vv[i].y;
+            rs[i] += vv[i].x + vv[i].y;
+          }
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            int p = 0;
+#pragma unroll
+            for (int i1 = 0; i1 < NT; ++i1)
+#pragma unroll
+              for (int i2 = 0; i2 <= i1; ++i2) {
+                dmma_m8n8k4(acc[p][0], acc[p][1], s ? vv[i1].y : vv[i1].x, s ? vv[i2].y : vv[i2].x);
+                ++p;
+              }
+          }
+#pragma unroll
+          for (int jj = 0; jj < NOTH; ++jj)
+#pragma unroll
+            for (int i = 0; i < NT; ++i) cur[jj][i] = nxt[jj][i];
+        }
+      }
+      // ---- f_k = u_k . v_k: transposing reduction over the 8 row groups; lane (g, q) ends with k = 8g + 2q + {0,1} ----
+      double r1[4][2], r2[2][2], f[2];
+      {
+        const bool h2 = (g & 4) != 0, h1 = (g & 2) != 0, h0 = (g & 1) != 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            const double give = h2 ? fp[j][s] : fp[j + 4][s], keep = h2 ? fp[j + 4][s] : fp[j][s];
+            r1[j][s] = keep + __shfl_xor_sync(0xffffffffu, give, 16);
+          }
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int s = 0; s < 2; ++s) {
+            const double give = h1 ? r1[j][s] : r1[j + 2][s], keep = h1 ? r1[j + 2][s] : r1[j][s];
+            r2[j][s] = keep + __shfl_xor_sync(0xffffffffu, give, 8);
+          }
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          const double give = h0 ? r2[0][s] : r2[1][s], keep = h0 ? r2[1][s] : r2[0][s];
+          f[s] = keep + __shfl_xor_sync(0xffffffffu, give, 4);
+        }
+      }
+      // ---- SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1, then broadcast -------------------------------------
+      double sum_a = 0.0, sum_d = 0.0;
+      if (g < KT) {
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          double a, b;
+          log_pdf_derivs(v.lik, y, f[s], v.lik_param, a, b);
+          sum_a += a;
+          sum_d += b;
+        }
+      }
+      sum_a = warp_sum(sum_a) / (double)k1;
+      sum_d = warp_sum(sum_d) / (double)k1;
+      const double aw = sum_a / (double)k1, dw = 0.5 * sum_d / (double)k1;
+#pragma unroll
+      for (int i = 0; i < NT; ++i) gp[i] += aw * rs[i];
+#pragma unroll
+      for (int p = 0; p < NP; ++p) {
+        double2 o = Gs[p * 32 + lane];
+        o.x += dw * acc[p][0];
+        o.y += dw * acc[p][1];
+        Gs[p * 32 + lane] = o;
+      }
+    }
+  }
+
+  // ---- CTA reduction (fixed warp order => deterministic) and the chunk record [di | Di | si_sum | count] ------------
+#pragma unroll
+  for (int i = 0; i < NT; ++i) {
+    double x = gp[i];
+    x += __shfl_xor_sync(0xffffffffu, x, 1);
+    x += __shfl_xor_sync(0xffffffffu, x, 2);
+    gp[i] = x;
+  }
+  __syncthreads();                                      // every warp is done reading U
+  if (q == 0) {
+#pragma unroll
+    for (int i = 0; i < NT; ++i) red[warp * (NT * 8) + 8 * i + g] = gp[i];
+  }
+  __syncthreads();
+  double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;
+  for (int n = tid; n < D; n += 128)
+    out[n] = ((red[n] + red[NT * 8 + n]) + red[2 * NT * 8 + n]) + red[3 * NT * 8 + n];
+  const double2* Gall = reinterpret_cast<const double2*>(smem_raw + region);
+  for (int idx = tid; idx < NP * 32; idx += 128) {
+    const int p = idx >> 5, l = idx & 31;
+    const double2 a0 = Gall[idx], a1 = Gall[NP * 32 + idx], a2 = Gall[2 * NP * 32 + idx], a3 = Gall[3 * NP * 32 + idx];
+    const double x0 = ((a0.x + a1.x) + a2.x) + a3.x, x1 = ((a0.y + a1.y) + a2.y) + a3.y;
+    // unrank p -> (i1 >= i2)
+    int i1 = 0;
+    while ((i1 + 1) * (i1 + 2) / 2 <= p) ++i1;
+    const int i2 = p - i1 * (i1 + 1) / 2;
+    const int n1 = 8 * i1 + (l >> 2), n2 = 8 * i2 + 2 * (l & 3);
+    if (n1 < D && n2 <= n1) {                           // lower triangle incl. diagonal, mirrored: exactly symmetric
+      out[D + n1 * D + n2] = x0;
+      out[D + n2 * D + n1] = x0;
+    }
+    if (n1 < D && n2 + 1 <= n1) {
+      out[D + n1 * D + n2 + 1] = x1;
+      out[D + (n2 + 1) * D + n1] = x1;
+    }
+  }
+  if (tid == 0) {
+    out[D + D * D] = 0.0;
+    out[D + D * D + 1] = (double)len;
+  }
+}

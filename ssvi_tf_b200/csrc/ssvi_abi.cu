@@ -3,7 +3,7 @@
 #include <string.h>
 #include <new>
 
-#include "accumulate_mma.cuh"
+#include "accumulate_memo.cuh"
 #include "row_update.cuh"
 
 #define SSVI_VERSION_STR "ssvi_b200 0.1 sm_100a"
@@ -267,6 +267,109 @@ extern "C" int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, con
   if (h->cfg.noise_dtype == SSVI_NOISE_F32)
     return dispatch_accumulate<float>(h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st);
   return dispatch_accumulate<double>(h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows, w_state, partial_out, st);
+}
+
+// ---- sample-table ("memoised") sweep path: accumulate_memo.cuh ------------------------------------------------------
+static bool sweep_ok(const SsviConfig& c) {
+  return c.cov_kind == SSVI_COV_FULL && c.model == SSVI_MODEL_D && c.rank <= 32 && (c.k1 % 8) == 0 && c.k1 <= 64 &&
+         c.order >= 2 && c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
+}
+
+extern "C" int ssvi_sweep_supported(const SsviHandle* h) { return (h && sweep_ok(h->cfg)) ? 1 : 0; }
+
+extern "C" int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int32_t n_slots) {
+  if (!h || !sweep_ok(h->cfg) || dim < 0 || dim >= h->cfg.order || n_slots < 1) return 0;
+  int64_t recs = 0;
+  for (int d = 0; d < h->cfg.order; ++d)
+    if (d != dim) recs += h->cfg.dims[d] * (int64_t)n_slots;
+  return recs * memo_rec_len(h->cfg.rank, h->cfg.k1) * (int64_t)sizeof(double);
+}
+
+template <int NT, typename ZT>
+static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int64_t n_chunks, const int32_t* chunk_row,
+                        const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
+                        const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, double* partial_out,
+                        cudaStream_t st) {
+  {
+    const int wpb = 8;
+    const size_t smem = (size_t)memo_stage_bytes(v.D, v.k1, (int)sizeof(ZT)) * wpb;
+    auto kern = sample_table_kernel<NT, ZT>;
+    CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t recs = mv.rec_base[mv.n_oth];
+    kern<<<(unsigned)((recs + wpb - 1) / wpb), wpb * 32, smem, st>>>(v, mv, (const ZT*)h->z_other);
+    CUDA_TRY(h, cudaGetLastError());
+  }
+  if (n_chunks == 0) return SSVI_OK;
+  const size_t smem = (size_t)memo_cta_smem(NT, v.D, v.k1, (int)sizeof(ZT));
+#define SSVI_MEMO_LAUNCH(NOTH)                                                                                     \
+  do {                                                                                                             \
+    auto kern = accumulate_memo_kernel<NT, NOTH, ZT>;                                                              \
+    CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));               \
+    kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot,    \
+                                                chunk_out, entry_ids, rows, (const ZT*)h->z_own, partial_out);     \
+  } while (0)
+  switch (mv.n_oth) {
+    case 1: SSVI_MEMO_LAUNCH(1); break;
+    case 2: SSVI_MEMO_LAUNCH(2); break;
+    default: SSVI_MEMO_LAUNCH(3); break;
+  }
+#undef SSVI_MEMO_LAUNCH
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo, int32_t n_slots, int64_t n_chunks,
+                                     const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
+                                     const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
+                                     const int64_t* rows, void* table_ws, int64_t table_ws_bytes, double* partial_out,
+                                     void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (!h->data_bound || !h->state_bound || !h->noise_bound) return fail(h, SSVI_E_STATE, "sweep_accumulate: bind data, state and noise first%s");
+  if (!sweep_ok(h->cfg)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: configuration not supported by the sample-table path (see ssvi_sweep_supported)%s");
+  if (dim < 0 || dim >= h->cfg.order) return fail(h, SSVI_E_INVALID, "sweep_accumulate: bad dim%s");
+  if (n_slots < 1 || slot_lo < 0 || slot_lo + n_slots > h->pool_slots) return fail(h, SSVI_E_INVALID, "sweep_accumulate: slot range outside the noise pool%s");
+  if (n_chunks < 0 || !table_ws) return fail(h, SSVI_E_INVALID, "sweep_accumulate: null workspace%s");
+  if (n_chunks > 0 && (!chunk_row || !chunk_start || !chunk_len || !chunk_slot || !chunk_out || !entry_ids || !rows || !partial_out))
+    return fail(h, SSVI_E_INVALID, "sweep_accumulate: null pointer%s");
+  if (table_ws_bytes < ssvi_sweep_table_bytes(h, dim, n_slots)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: table workspace too small%s");
+  const DevView v = make_view(h, dim);
+  MemoView mv;
+  memset(&mv, 0, sizeof(mv));
+  mv.n_oth = h->cfg.order - 1;
+  mv.rec_len = memo_rec_len(h->cfg.rank, h->cfg.k1);
+  mv.slot_lo = slot_lo;
+  mv.n_slots = n_slots;
+  mv.tab = (double*)table_ws;
+  int jj = 0;
+  int64_t base = 0;
+  for (int d = 0; d < h->cfg.order; ++d) {
+    if (d == dim) continue;
+    mv.od[jj] = d;
+    mv.n_rows[jj] = h->cfg.dims[d];
+    mv.rec_base[jj] = base;
+    base += h->cfg.dims[d] * (int64_t)n_slots;
+    ++jj;
+  }
+  mv.rec_base[jj] = base;
+  if (base >= ((int64_t)1 << 31)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: too many table records; use fewer slots per call%s");
+  cudaStream_t st = (cudaStream_t)stream;
+#define SSVI_SWEEP_ARGS h, v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, partial_out, st
+  const int nt = (v.D + 7) / 8;
+  if (h->cfg.noise_dtype == SSVI_NOISE_F32) {
+    switch (nt) {
+      case 1: return launch_sweep<1, float>(SSVI_SWEEP_ARGS);
+      case 2: return launch_sweep<2, float>(SSVI_SWEEP_ARGS);
+      case 3: return launch_sweep<3, float>(SSVI_SWEEP_ARGS);
+      default: return launch_sweep<4, float>(SSVI_SWEEP_ARGS);
+    }
+  }
+  switch (nt) {
+    case 1: return launch_sweep<1, double>(SSVI_SWEEP_ARGS);
+    case 2: return launch_sweep<2, double>(SSVI_SWEEP_ARGS);
+    case 3: return launch_sweep<3, double>(SSVI_SWEEP_ARGS);
+    default: return launch_sweep<4, double>(SSVI_SWEEP_ARGS);
+  }
+#undef SSVI_SWEEP_ARGS
 }
 
 // acc_out[r][i] = sum over the row's chunk records, in chunk order (deterministic)

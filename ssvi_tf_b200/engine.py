@@ -119,11 +119,33 @@ class SweepPlan(object):
         self.n_entries = int(batch_sizes.sum())
 
 
+class SlotSweepPlan(object):
+    """Slot-major chunk tables for ssvi_sweep_accumulate (the sample-table path of a full sweep).
+
+    Chunks are sorted by (slot, row, segment) -- the launch order -- and carry the index of their record
+    in a row-major partial buffer (chunk_out), so ssvi_reduce_chunks still sums each row's records in
+    one contiguous, fixed-order run.  groups: [(slot_lo, n_slots, chunk_lo, chunk_hi)]."""
+
+    def __init__(self, dim, rows, n_obs, entry_ids, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
+                 row_chunk_ptr, batch_sizes, groups, table_bytes):
+        self.dim = dim
+        self.rows, self.n_obs, self.entry_ids = rows, n_obs, entry_ids
+        self.chunk_row, self.chunk_start, self.chunk_len = chunk_row, chunk_start, chunk_len
+        self.chunk_slot, self.chunk_out = chunk_slot, chunk_out
+        self.row_chunk_ptr = row_chunk_ptr
+        self.n_rows = int(rows.numel())
+        self.n_chunks = int(chunk_row.numel())
+        self.batch_sizes = batch_sizes
+        self.n_entries = int(batch_sizes.sum())
+        self.groups = groups
+        self.table_bytes = int(table_bytes)
+
+
 class Engine(object):
     """One GPU's view of the problem: COO shard + CSR index + posterior state + noise pool."""
 
     def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16,
-                 kernel_path=0):
+                 kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64):
         """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
         cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
         if not torch.cuda.is_available():
@@ -136,6 +158,8 @@ class Engine(object):
         self.diag = bool(cfg["diag"])
         self.device = torch.device(device)
         self.chunk_entries = int(chunk_entries)
+        self.table_budget_bytes = int(table_budget_bytes)      # L2-resident sample table of the sweep path
+        self.sweep_chunk_entries = int(sweep_chunk_entries)
         self.noise_dtype = noise_dtype
         if cfg["mean_update"] not in UPDATE_IDS or cfg["cov_update"] not in UPDATE_IDS:
             raise Exception("Unidentified update formula for covariance param")   # SSVI_TF_interface.py:612, 632
@@ -210,6 +234,8 @@ class Engine(object):
         self._bind_state()
         self.noise = None
         self._full_plans = {}
+        self._sweep_plans = {}
+        self.sweep_supported = bool(self.lib.ssvi_sweep_supported(self.h))
         self._scratch = {}
         self.launches = 0          # kernels of libssvi_b200 launched through this engine
         self.profile_events = None  # set to a list to time every ssvi_accumulate launch with CUDA events
@@ -339,6 +365,82 @@ class Engine(object):
         return SweepPlan(dim, torch.as_tensor(rows_h).to(self.device), torch.as_tensor(lens).to(self.device),
                          entry_ids, tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
 
+    def plan_sweep(self, dim, slot_offset=None):
+        """Full sweep of mode `dim` (every observed entry of every row, scale = 1) for the sample-table
+        path: entries regrouped by the noise slot they read (entry b of a row reads slot (b + offset) mod P),
+        one chunk per (slot, row[, segment]).  Needs the noise pool (P) to be set."""
+        assert self.noise is not None, "set_noise() first"
+        assert self.sweep_supported, "configuration not supported by the sample-table path"
+        P = int(self.noise.slots)
+        key = (dim, P, None if slot_offset is None else hash(np.asarray(slot_offset).tobytes()))
+        if key in self._sweep_plans:
+            return self._sweep_plans[key]
+        n = self.dims[dim]
+        dev = self.device
+        rp = self.rowptr_h[dim]
+        lens = rp[1:] - rp[:-1]
+        off = np.zeros(n, dtype=np.int64) if slot_offset is None else np.asarray(slot_offset, dtype=np.int64) % P
+        # ---- slot-major permutation of the mode's CSR entry list (device) ----
+        lens_d = torch.as_tensor(lens).to(dev)
+        row_of = torch.repeat_interleave(torch.arange(n, device=dev, dtype=torch.int64), lens_d)
+        b = torch.arange(int(rp[-1]), device=dev, dtype=torch.int64) - torch.as_tensor(rp[:-1]).to(dev)[row_of]
+        slot = (b + torch.as_tensor(off).to(dev)[row_of]) % P
+        del b, row_of
+        order = torch.sort(slot, stable=True).indices           # (slot, row, b): stable keeps (row, b)
+        del slot
+        entry_ids = self.perm[dim][order].contiguous()
+        del order
+        # ---- per (slot, row) counts and chunk tables (host) ----
+        s_idx = np.arange(P, dtype=np.int64)[:, None]
+        b0 = (s_idx - off[None, :]) % P                          # first position of row r that reads slot s
+        cnt = np.where(lens[None, :] > b0, (lens[None, :] - b0 + P - 1) // P, 0)      # [P, n]
+        W = self.sweep_chunk_entries
+        nseg = (cnt + W - 1) // W                                # [P, n]
+        flat_cnt, flat_seg = cnt.reshape(-1), nseg.reshape(-1)   # (slot, row) order == launch order
+        pair_start = np.zeros(P * n + 1, dtype=np.int64)
+        np.cumsum(flat_cnt, out=pair_start[1:])
+        pair_chunk = np.zeros(P * n + 1, dtype=np.int64)
+        np.cumsum(flat_seg, out=pair_chunk[1:])
+        total = int(pair_chunk[-1])
+        pair_of = np.repeat(np.arange(P * n, dtype=np.int64), flat_seg)
+        seg = np.arange(total, dtype=np.int64) - pair_chunk[pair_of]
+        c_cnt, c_nseg = flat_cnt[pair_of], flat_seg[pair_of]
+        base, rem = c_cnt // c_nseg, c_cnt % c_nseg              # segments differ by at most one entry
+        chunk_len = base + (seg < rem)
+        chunk_start = pair_start[pair_of] + seg * base + np.minimum(seg, rem)
+        chunk_slot = pair_of // n
+        chunk_row = pair_of % n
+        # record index in row-major (row, slot, segment) order
+        rm_chunk = np.zeros(n * P + 1, dtype=np.int64)
+        np.cumsum(nseg.T.reshape(-1), out=rm_chunk[1:])
+        chunk_out = rm_chunk[chunk_row * P + chunk_slot] + seg
+        row_chunk_ptr = rm_chunk[::P].copy()
+        # ---- slot groups: as many slots per call as the table budget holds ----
+        per_slot = int(self.lib.ssvi_sweep_table_bytes(self.h, dim, 1))
+        gs = max(1, min(P, self.table_budget_bytes // max(per_slot, 1)))
+        slot_chunk = pair_chunk[::n]                             # first chunk of each slot (+ total)
+        groups = [(s0, min(gs, P - s0), int(slot_chunk[s0]), int(slot_chunk[min(s0 + gs, P)]))
+                  for s0 in range(0, P, gs)]
+        t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a.astype(dt))).to(dev)      # noqa: E731
+        plan = SlotSweepPlan(dim, torch.arange(n, device=dev, dtype=torch.int64), lens_d, entry_ids,
+                             t(chunk_row, np.int32), t(chunk_start, np.int64), t(chunk_len, np.int32),
+                             t(chunk_slot, np.int32), t(chunk_out, np.int64), t(row_chunk_ptr, np.int64), lens,
+                             groups, per_slot * gs)
+        self._sweep_plans[key] = plan
+        return plan
+
+    def _accumulate_sweep(self, plan, partial, st):
+        tab = self._buf("sweep_table", (plan.table_bytes + 7) // 8)
+
+        def at(tensor, i):
+            return ctypes.c_void_p(tensor.data_ptr() + i * tensor.element_size())
+        for (s0, ns, c0, c1) in plan.groups:
+            self._call(self.lib.ssvi_sweep_accumulate, plan.dim, s0, ns, c1 - c0, at(plan.chunk_row, c0),
+                       at(plan.chunk_start, c0), at(plan.chunk_len, c0), at(plan.chunk_slot, c0),
+                       at(plan.chunk_out, c0), _ptr(plan.entry_ids), _ptr(plan.rows), _ptr(tab),
+                       tab.numel() * 8, _ptr(partial), st)
+            self.launches += 2 if c1 > c0 else 1
+
     # -------------------------------------------------------------------------------------------
     def _buf(self, name, numel):
         t = self._scratch.get(name)
@@ -357,14 +459,18 @@ class Engine(object):
         if self.profile_events is not None:
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             ev[0].record()
-        self._call(self.lib.ssvi_accumulate, plan.dim, plan.n_chunks, _ptr(plan.chunk_row), _ptr(plan.chunk_start),
-                   _ptr(plan.chunk_len), _ptr(plan.chunk_slot0), _ptr(plan.entry_ids), _ptr(plan.rows),
-                   _ptr(self.w_state), _ptr(partial), st)
+        if isinstance(plan, SlotSweepPlan):
+            self._accumulate_sweep(plan, partial, st)
+        else:
+            self._call(self.lib.ssvi_accumulate, plan.dim, plan.n_chunks, _ptr(plan.chunk_row),
+                       _ptr(plan.chunk_start), _ptr(plan.chunk_len), _ptr(plan.chunk_slot0), _ptr(plan.entry_ids),
+                       _ptr(plan.rows), _ptr(self.w_state), _ptr(partial), st)
+            self.launches += 1 if plan.n_chunks else 0
         if ev is not None:
             ev[1].record()
             self.profile_events.append((ev[0], ev[1], plan.n_entries))
         self._call(self.lib.ssvi_reduce_chunks, plan.n_rows, _ptr(plan.row_chunk_ptr), _ptr(partial), _ptr(acc), st)
-        self.launches += 2 if plan.n_chunks else 0
+        self.launches += 1 if plan.n_chunks else 0
         return acc[:plan.n_rows * self.acc_len].view(plan.n_rows, self.acc_len)
 
     def row_update(self, plan, acc, fixed_covariance=False, n_obs=None):

@@ -177,3 +177,62 @@ def test_mma_path_matches_oracle_and_generic(D, k1, model, lik):
     # Di block of the accumulator record is exactly symmetric
     Di = results[0][0][:, D:D + D * D].reshape(-1, D, D)
     np.testing.assert_array_equal(Di, np.transpose(Di, (0, 2, 1)))
+
+
+@pytest.mark.parametrize("dims,D,k1,lik,P,W,offs", [
+    ([6, 5, 4], 20, 64, "bernoulli", 4, 64, False),      # BASELINE config 2's kernel instance (NT=3, two other modes)
+    ([6, 5, 4], 12, 24, "normal", 3, 2, True),           # segments of 2 entries, shifted slots (multi-GPU shard)
+    ([5, 4, 4], 32, 64, "normal", 5, 3, False),          # NT=4 (config 5)
+    ([5, 4, 4], 30, 40, "poisson", 4, 64, True),
+    ([7, 9], 7, 16, "bernoulli", 2, 4, False),           # matrix: one other mode
+    ([4, 3, 3, 3], 10, 64, "normal", 3, 64, False),      # 4-way: three other modes (config 1's NT=2)
+])
+def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W, offs):
+    """Full sweep through the slot-major sample-table kernels == the direct DMMA kernel == the generic CUDA-core
+    kernel (same accumulators to summation order) == the oracle's rows_step on the same pooled noise."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(D * 1000 + k1 + P)
+    N = len(dims)
+    cfg = so.make_config("d", lik, D, diag=False, k1=k1, k2=4, batch_size=10 ** 9)
+    nnz = int(0.8 * np.prod(dims))
+    coords, vals = random_problem(rng, lik, dims, nnz)
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    pool = so.make_tape(rng, cfg, N, P)
+    for dim in range(N):
+        n = dims[dim]
+        off = rng.integers(0, 50, size=n) if offs else None
+        accs, states = [], []
+        for path, sweep in ((0, True), (0, False), (1, False)):
+            eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, chunk_entries=3,
+                         kernel_path=path, sweep_chunk_entries=W, table_budget_bytes=1)   # 1 slot per call
+            eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=False))
+            engine_load_state(eng, st0)
+            assert eng.sweep_supported == (path == 0)
+            plan = eng.plan_sweep(dim, off) if sweep else eng.plan_full(dim, None, off)
+            if sweep:
+                assert len(plan.groups) == P
+                np.testing.assert_array_equal(np.sort(plan.entry_ids.cpu().numpy()), np.sort(perm[dim]))
+            acc = eng.accumulate(plan).cpu().numpy().copy()
+            eng.row_update(plan, eng.accumulate(plan))
+            eng.check_flags()
+            accs.append(acc)
+            states.append(engine_dump_state(eng, st0))
+            eng.close()
+        scale = np.abs(accs[2]).max()
+        np.testing.assert_allclose(accs[0], accs[2], rtol=1e-9, atol=1e-12 * scale)
+        np.testing.assert_allclose(accs[1], accs[2], rtol=1e-9, atol=1e-12 * scale)
+        np.testing.assert_array_equal(accs[0][:, -1], np.diff(rowptr[dim]))        # counts: bit-exact
+        Di = accs[0][:, D:D + D * D].reshape(-1, D, D)
+        np.testing.assert_array_equal(Di, np.transpose(Di, (0, 2, 1)))
+        # oracle: entry b of a row reads pool slot (b + offset) mod P
+        entries, tapes = [], []
+        for row in range(n):
+            ids = perm[dim][rowptr[dim][row]:rowptr[dim][row + 1]]
+            sl = (np.arange(len(ids)) + (0 if off is None else int(off[row]))) % P
+            tapes.append(so.Tape(pool.z_other[sl], pool.z_own[sl], pool.r_w[sl], pool.z_f[sl]))
+            entries.append((coords[ids], vals[ids]))
+        want = so.copy_state(st0)
+        so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
+        for got in states:
+            assert_state_close(got, want, cfg, RTOL, what="dims=%s mode %d" % (dims, dim))
