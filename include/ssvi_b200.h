@@ -159,8 +159,8 @@ int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t*
                     const int64_t* entry_ids, const int64_t* rows, const double* w_state,
                     double* partial_out, void* stream);
 
-/* ---- The sample-table path for full sweeps (slot-major; SSVI_TF_d, full covariance, rank <= 32, k1 % 8 == 0,
- * k1 <= 64, order <= 4).  Same mathematics and the same outputs as ssvi_accumulate, organised so that the sample
+/* ---- The sample-table path for full sweeps (slot-major; SSVI_TF_d, full covariance, rank <= 32, k1 == 64 -- the
+ * reference's default, SSVI_TF_interface.py:23 -- and order <= 4).  Same mathematics and the same outputs as ssvi_accumulate, organised so that the sample
  * X(j, s) = m_j + L_j Z(s, jj) of sample_vjs_batch (SSVI_TF_interface.py:732-750) is evaluated once per (other-mode
  * row j, noise slot s) instead of once per (entry, mode): with P pool slots a sweep asks for each pair nnz / (n_j P)
  * times.  The caller runs a sweep as a sequence of calls over slot groups [slot_lo, slot_lo + n_slots); each call

@@ -1,4 +1,4 @@
-// Stages 1-3 for FULL SWEEPS of SSVI_TF_d, full covariance, D <= 32, k1 % 8 == 0, k1 <= 64: the sample-table path.
+// Stages 1-3 for FULL SWEEPS of SSVI_TF_d, full covariance, D <= 32, k1 == 64: the sample-table path.
 //
 // In a sweep, entry b of a row's list reads noise slot (b mod P).  The Monte-Carlo sample of a gathered other-mode row
 //       X(j, s) = m_j + L_j Z(s, jj)            (D x k1, sample_vjs_batch, SSVI_TF_interface.py:732-750)
@@ -75,76 +75,102 @@ __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView m
   double vv[NT][8][2];
   double fp[8][2];
   mma_sample_mode<NT, ZT, false>(S, zs, NS, KT, lane, g, true, vv, fp);
+  // Padding rows (n >= D) come out as exact zeros (zero mean, zero factor rows); row n == D is set to ONE so that the
+  // contraction V V^T of the accumulate kernel also delivers the row sums sum_k V[n][k] (its row D) for free.
   double2* out = reinterpret_cast<double2*>(mv.tab + rec * (int64_t)mv.rec_len);
 #pragma unroll
   for (int i = 0; i < NT; ++i) {
-    if (8 * i + g < D) {
+    const bool one = (8 * i + g) == D;
 #pragma unroll
-      for (int t = 0; t < 8; ++t)
-        if (t < KT) out[(i * KT + t) * 32 + lane] = make_double2(vv[i][t][0], vv[i][t][1]);
-    }
+    for (int t = 0; t < 8; ++t)
+      if (t < KT) out[(i * KT + t) * 32 + lane] = one ? make_double2(1.0, 1.0) : make_double2(vv[i][t][0], vv[i][t][1]);
   }
 }
 
-// x = m + L z for row-tile i and k-tile t only (own-row sample of the memo kernel's prologue)
-template <typename ZT>
-__device__ __forceinline__ void mma_sample_tile(const double* __restrict__ S, const ZT* __restrict__ z, int NT, int NS,
-                                                int lane, int g, int i, int t, double& c0, double& c1) {
+// x = m + L z for row-tile i and k-tile t only (own-row sample of the memo kernel's prologue; z staged as double)
+__device__ __forceinline__ void mma_sample_tile(const double* __restrict__ S, const double* __restrict__ z, int NT,
+                                                int NS, int lane, int g, int i, int t, double& c0, double& c1) {
   c0 = c1 = S[8 * i + g];
   const double* At = S + 8 * NT + 32 * (i * (i + 1)) + lane;
   const int nj = min(2 * (i + 1), NS);
-  for (int j = 0; j < nj; ++j) dmma_m8n8k4(c0, c1, At[32 * j], zfrag(z, (t * NS + j) * 32 + lane));
+  for (int j = 0; j < nj; ++j) dmma_m8n8k4(c0, c1, At[32 * j], z[(t * NS + j) * 32 + lane]);
 }
 
+#define SSVI_MEMO_KT 8                                  // the sample-table path is specialised for k1 == 64
 // Shared memory of one CTA (4 warps), bytes: one region reused as {staging | U | reduction} + per-warp G.
-__host__ __device__ inline int memo_cta_smem(int NT, int D, int k1, int zsize) {
-  const int KT = k1 >> 3, NP = NT * (NT + 1) / 2;
-  int a = memo_stage_bytes(D, k1, zsize);
-  const int us = NT * KT * 32 * 16;
+__host__ __device__ inline int memo_region_bytes(int NT, int D) {
+  int a = smp_row_len(D, false) * 8 + smp_zblk(D, 8 * SSVI_MEMO_KT, false) * 8;      // staging: row + z (as double)
+  const int us = NT * SSVI_MEMO_KT * 32 * 16;
   const int red = 4 * (NT * 8) * 8;
   if (us > a) a = us;
   if (red > a) a = red;
-  return a + 4 * NP * 64 * 8;
+  return a;
+}
+__host__ __device__ inline int memo_cta_smem(int NT, int D) {
+  return memo_region_bytes(NT, D) + 4 * (NT * (NT + 1) / 2) * 64 * 8;
 }
 
 __device__ __forceinline__ double2 ld_tab(const double2* p) { return __ldcg(p); }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.
+//   ONES: D % 8 != 0, the table carries a row of ones at n == D and di comes out of the contraction (row D of V V^T);
+//         otherwise the row sums are accumulated with DADDs.
 // ---------------------------------------------------------------------------------------------------------------------
-template <int NT, int NOTH, typename ZT>
+template <int NT, int NOTH, bool ONES>
 __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
     DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
     const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
     const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
-    const int64_t* __restrict__ entry_ids, const int64_t* __restrict__ rows, const ZT* __restrict__ z_own,
-    double* __restrict__ partial_out) {
+    const int64_t* __restrict__ entry_ids, const int64_t* __restrict__ rows, const void* __restrict__ z_own,
+    int z_f32, double* __restrict__ partial_out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  constexpr int NP = NT * (NT + 1) / 2;
+  constexpr int NP = NT * (NT + 1) / 2, KT = SSVI_MEMO_KT, PL = NT * (NT - 1) / 2;   // PL: first pair of tile-row NT-1
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, q = lane & 3;
   const int64_t c = blockIdx.x;
   if (c >= n_chunks) return;
-  const int N = v.N, D = v.D, k1 = v.k1, KT = k1 >> 3, NS = smp_ns(D);
+  const int N = v.N, D = v.D, NS = smp_ns(D);
   const int64_t row = rows[chunk_row[c]];
   const int64_t start = chunk_start[c];
   const int len = chunk_len[c], slot = chunk_slot[c];
   const int sl = slot - mv.slot_lo;
 
-  const int region = memo_cta_smem(NT, D, k1, (int)sizeof(ZT)) - 4 * NP * 64 * 8;
+  const int region = memo_region_bytes(NT, D);
   double* S = reinterpret_cast<double*>(smem_raw);
-  ZT* zs = reinterpret_cast<ZT*>(S + v.srow_len);
+  double* zs = S + v.srow_len;
   double2* Us = reinterpret_cast<double2*>(smem_raw);
   double* red = reinterpret_cast<double*>(smem_raw);
   double2* Gs = reinterpret_cast<double2*>(smem_raw + region) + warp * (NP * 32);
+
+  // ---- this warp's entries (w, w+4, ...): value and table records, fetched lane-parallel before the prologue so the
+  //      index -> coordinate -> table chain of loads overlaps the own-row sampling ------------------------------------
+  const int my_cnt = (len - warp + 3) >> 2;             // may be 0 for high warps of a short chunk
+  const double2* tab2 = reinterpret_cast<const double2*>(mv.tab);
+  const int rec2 = mv.rec_len >> 1;                     // double2 per record
+  double my_y = 0.0;
+  int32_t my_rec[NOTH];
+#pragma unroll
+  for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = 0;
+  if (lane < my_cnt) {
+    const int64_t eid = entry_ids[start + (int64_t)lane * 4 + warp];
+    my_y = v.vals[eid];
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
+  }
 
   // ---- prologue: U(row, slot) = m + L z_own, once per CTA (ui samples, SSVI_TF_interface.py:251-254) --------------------
   {
     const double2* src = reinterpret_cast<const double2*>(v.sampler[v.dim] + row * (int64_t)v.srow_len);
     double2* dst = reinterpret_cast<double2*>(S);
     for (int i = tid; i < (v.srow_len >> 1); i += 128) dst[i] = src[i];
-    const ZT* zsrc = z_own + (int64_t)slot * v.zblk;
-    for (int i = tid; i < v.zblk; i += 128) zs[i] = zsrc[i];
+    if (z_f32) {
+      const float* zsrc = reinterpret_cast<const float*>(z_own) + (int64_t)slot * v.zblk;
+      for (int i = tid; i < v.zblk; i += 128) zs[i] = (double)zsrc[i];
+    } else {
+      const double* zsrc = reinterpret_cast<const double*>(z_own) + (int64_t)slot * v.zblk;
+      for (int i = tid; i < v.zblk; i += 128) zs[i] = zsrc[i];
+    }
   }
 #pragma unroll
   for (int p = 0; p < NP; ++p) Gs[p * 32 + lane] = make_double2(0.0, 0.0);
@@ -153,122 +179,102 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
 #pragma unroll
   for (int i = 0; i < NT; ++i)
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int t = warp + 4 * h;
-      uc[i][h][0] = uc[i][h][1] = 0.0;
-      if (t < KT) mma_sample_tile<ZT>(S, zs, NT, NS, lane, g, i, t, uc[i][h][0], uc[i][h][1]);
-    }
+    for (int h = 0; h < 2; ++h)
+      mma_sample_tile(S, zs, NT, NS, lane, g, i, warp + 4 * h, uc[i][h][0], uc[i][h][1]);
   __syncthreads();                                      // staging is dead: the region becomes U
 #pragma unroll
   for (int i = 0; i < NT; ++i)
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int t = warp + 4 * h;
-      if (t < KT) Us[(i * KT + t) * 32 + lane] = make_double2(uc[i][h][0], uc[i][h][1]);
-    }
+    for (int h = 0; h < 2; ++h)
+      Us[(i * KT + warp + 4 * h) * 32 + lane] = make_double2(uc[i][h][0], uc[i][h][1]);
   __syncthreads();
 
-  // ---- main loop: warp w takes entries w, w+4, ... of the chunk ----------------------------------------------------------
-  const int my_cnt = (len - warp + 3) >> 2;             // entries of this warp (len >= 1; may be 0 for high warps)
-  double gp[NT];
+  // ---- main loop -----------------------------------------------------------------------------------------------------
+  double2 ga[NT];                                       // ONES: sum_b aw_b * (row D of V V^T) ; else sum_b aw_b * row sums
 #pragma unroll
-  for (int i = 0; i < NT; ++i) gp[i] = 0.0;
-  const double2* tab2 = reinterpret_cast<const double2*>(mv.tab);
-  const int rec2 = mv.rec_len >> 1;                     // double2 per record
-  // lanes holding padding rows (n >= D) never load
-  bool act[NT];
-#pragma unroll
-  for (int i = 0; i < NT; ++i) act[i] = (8 * i + g) < D;
+  for (int i = 0; i < NT; ++i) ga[i] = make_double2(0.0, 0.0);
+  const double inv_k1 = 1.0 / (double)(8 * KT);
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
-    // lane-parallel fetch of up to 32 entries' value and table records
     const int nb = min(32, my_cnt - b0);
-    double my_y = 0.0;
-    int32_t my_rec[NOTH];
+    if (b0 > 0) {                                       // chunks longer than 128 entries: next 32 of this warp
+      my_y = 0.0;
 #pragma unroll
-    for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = 0;
-    if (lane < nb) {
-      const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
-      my_y = v.vals[eid];
+      for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = 0;
+      if (lane < nb) {
+        const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
+        my_y = v.vals[eid];
 #pragma unroll
-      for (int jj = 0; jj < NOTH; ++jj)
-        my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
+        for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
+      }
     }
     double2 cur[NOTH][NT];
-    {
 #pragma unroll
-      for (int jj = 0; jj < NOTH; ++jj) {
-        const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
+    for (int jj = 0; jj < NOTH; ++jj) {
+      const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
 #pragma unroll
-        for (int i = 0; i < NT; ++i) cur[jj][i] = act[i] ? ld_tab(p + (i * KT) * 32) : make_double2(0.0, 0.0);
-      }
+      for (int i = 0; i < NT; ++i) cur[jj][i] = ld_tab(p + (i * KT) * 32);
     }
     for (int el = 0; el < nb; ++el) {
       const double y = __shfl_sync(0xffffffffu, my_y, el);
+      const int eln = (el + 1 < nb) ? el + 1 : el;      // last entry: re-read its own first tiles (harmless)
       const double2* pc[NOTH];
       const double2* pn[NOTH];
-      const bool more = el + 1 < nb;
 #pragma unroll
       for (int jj = 0; jj < NOTH; ++jj) {
         pc[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], el) * rec2 + lane;
-        pn[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], more ? el + 1 : el) * rec2 + lane;
+        pn[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], eln) * rec2 + lane;
       }
       double acc[NP][2];
 #pragma unroll
       for (int p = 0; p < NP; ++p) acc[p][0] = acc[p][1] = 0.0;
-      double fp[8][2];
+      double fp[KT][2];
       double rs[NT];
 #pragma unroll
       for (int i = 0; i < NT; ++i) rs[i] = 0.0;
 #pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        fp[t][0] = fp[t][1] = 0.0;
-        if (t < KT) {
-          double2 nxt[NOTH][NT];
-          const bool in_entry = t + 1 < KT;
-          if (in_entry || more) {
+      for (int t = 0; t < KT; ++t) {
+        double2 nxt[NOTH][NT];                          // one k-tile ahead (the next entry's first tile at t == KT-1)
 #pragma unroll
-            for (int jj = 0; jj < NOTH; ++jj) {
-              const double2* p = in_entry ? pc[jj] + (t + 1) * 32 : pn[jj];
+        for (int jj = 0; jj < NOTH; ++jj) {
+          const double2* p = (t + 1 < KT) ? pc[jj] + (t + 1) * 32 : pn[jj];
 #pragma unroll
-              for (int i = 0; i < NT; ++i) nxt[jj][i] = act[i] ? ld_tab(p + (i * KT) * 32) : make_double2(0.0, 0.0);
-            }
-          } else {
+          for (int i = 0; i < NT; ++i) nxt[jj][i] = ld_tab(p + (i * KT) * 32);
+        }
+        double2 vv[NT];
 #pragma unroll
-            for (int jj = 0; jj < NOTH; ++jj)
+        for (int i = 0; i < NT; ++i) {
+          vv[i] = cur[0][i];
 #pragma unroll
-              for (int i = 0; i < NT; ++i) nxt[jj][i] = make_double2(0.0, 0.0);
+          for (int jj = 1; jj < NOTH; ++jj) {
+            vv[i].x *= cur[jj][i].x;
+            vv[i].y *= cur[jj][i].y;
           }
-          double2 vv[NT];
-#pragma unroll
-          for (int i = 0; i < NT; ++i) {
-            vv[i] = cur[0][i];
-#pragma unroll
-            for (int jj = 1; jj < NOTH; ++jj) {
-              vv[i].x *= cur[jj][i].x;
-              vv[i].y *= cur[jj][i].y;
-            }
-            const double2 u = Us[(i * KT + t) * 32 + lane];
+          const double2 u = Us[(i * KT + t) * 32 + lane];
+          if (i == 0) {
+            fp[t][0] = u.x * vv[i].x;
+            fp[t][1] = u.y * vv[i].y;
+          } else {
             fp[t][0] += u.x * vv[i].x;
             fp[t][1] += u.y * vv[i].y;
-            rs[i] += vv[i].x + vv[i].y;
           }
-#pragma unroll
-          for (int s = 0; s < 2; ++s) {
-            int p = 0;
-#pragma unroll
-            for (int i1 = 0; i1 < NT; ++i1)
-#pragma unroll
-              for (int i2 = 0; i2 <= i1; ++i2) {
-                dmma_m8n8k4(acc[p][0], acc[p][1], s ? vv[i1].y : vv[i1].x, s ? vv[i2].y : vv[i2].x);
-                ++p;
-              }
-          }
-#pragma unroll
-          for (int jj = 0; jj < NOTH; ++jj)
-#pragma unroll
-            for (int i = 0; i < NT; ++i) cur[jj][i] = nxt[jj][i];
+          if (!ONES) rs[i] += vv[i].x + vv[i].y;
         }
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          int p = 0;
+#pragma unroll
+          for (int i1 = 0; i1 < NT; ++i1)
+#pragma unroll
+            for (int i2 = 0; i2 <= i1; ++i2) {
+              dmma_m8n8k4(acc[p][0], acc[p][1], s ? vv[i1].y : vv[i1].x, s ? vv[i2].y : vv[i2].x);
+              ++p;
+            }
+        }
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj)
+#pragma unroll
+          for (int i = 0; i < NT; ++i) cur[jj][i] = nxt[jj][i];
       }
       // ---- f_k = u_k . v_k: transposing reduction over the 8 row groups; lane (g, q) ends with k = 8g + 2q + {0,1} ----
       double r1[4][2], r2[2][2], f[2];
@@ -296,20 +302,25 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
       }
       // ---- SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1, then broadcast -------------------------------------
       double sum_a = 0.0, sum_d = 0.0;
-      if (g < KT) {
 #pragma unroll
-        for (int s = 0; s < 2; ++s) {
-          double a, b;
-          log_pdf_derivs(v.lik, y, f[s], v.lik_param, a, b);
-          sum_a += a;
-          sum_d += b;
+      for (int s = 0; s < 2; ++s) {
+        double a, b;
+        log_pdf_derivs(v.lik, y, f[s], v.lik_param, a, b);
+        sum_a += a;
+        sum_d += b;
+      }
+      sum_a = warp_sum(sum_a) * inv_k1;
+      sum_d = warp_sum(sum_d) * inv_k1;
+      const double aw = sum_a * inv_k1, dw = 0.5 * sum_d * inv_k1;
+#pragma unroll
+      for (int i = 0; i < NT; ++i) {
+        if (ONES) {
+          ga[i].x += aw * acc[PL + i][0];
+          ga[i].y += aw * acc[PL + i][1];
+        } else {
+          ga[i].x += aw * rs[i];
         }
       }
-      sum_a = warp_sum(sum_a) / (double)k1;
-      sum_d = warp_sum(sum_d) / (double)k1;
-      const double aw = sum_a / (double)k1, dw = 0.5 * sum_d / (double)k1;
-#pragma unroll
-      for (int i = 0; i < NT; ++i) gp[i] += aw * rs[i];
 #pragma unroll
       for (int p = 0; p < NP; ++p) {
         double2 o = Gs[p * 32 + lane];
@@ -321,17 +332,21 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
   }
 
   // ---- CTA reduction (fixed warp order => deterministic) and the chunk record [di | Di | si_sum | count] ------------
-#pragma unroll
-  for (int i = 0; i < NT; ++i) {
-    double x = gp[i];
-    x += __shfl_xor_sync(0xffffffffu, x, 1);
-    x += __shfl_xor_sync(0xffffffffu, x, 2);
-    gp[i] = x;
-  }
   __syncthreads();                                      // every warp is done reading U
-  if (q == 0) {
+  if (ONES) {                                           // lanes of row group g == D % 8 hold di[8 i2 + 2q + {0,1}]
+    if (g == (D & 7)) {
 #pragma unroll
-    for (int i = 0; i < NT; ++i) red[warp * (NT * 8) + 8 * i + g] = gp[i];
+      for (int i = 0; i < NT; ++i)
+        *reinterpret_cast<double2*>(&red[warp * (NT * 8) + 8 * i + 2 * q]) = ga[i];
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < NT; ++i) {
+      double x = ga[i].x;
+      x += __shfl_xor_sync(0xffffffffu, x, 1);
+      x += __shfl_xor_sync(0xffffffffu, x, 2);
+      if (q == 0) red[warp * (NT * 8) + 8 * i + g] = x;
+    }
   }
   __syncthreads();
   double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;
@@ -342,8 +357,7 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
     const int p = idx >> 5, l = idx & 31;
     const double2 a0 = Gall[idx], a1 = Gall[NP * 32 + idx], a2 = Gall[2 * NP * 32 + idx], a3 = Gall[3 * NP * 32 + idx];
     const double x0 = ((a0.x + a1.x) + a2.x) + a3.x, x1 = ((a0.y + a1.y) + a2.y) + a3.y;
-    // unrank p -> (i1 >= i2)
-    int i1 = 0;
+    int i1 = 0;                                         // unrank p -> (i1 >= i2)
     while ((i1 + 1) * (i1 + 2) / 2 <= p) ++i1;
     const int i2 = p - i1 * (i1 + 1) / 2;
     const int n1 = 8 * i1 + (l >> 2), n2 = 8 * i2 + 2 * (l & 3);

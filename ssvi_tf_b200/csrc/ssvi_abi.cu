@@ -271,7 +271,7 @@ extern "C" int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, con
 
 // ---- sample-table ("memoised") sweep path: accumulate_memo.cuh ------------------------------------------------------
 static bool sweep_ok(const SsviConfig& c) {
-  return c.cov_kind == SSVI_COV_FULL && c.model == SSVI_MODEL_D && c.rank <= 32 && (c.k1 % 8) == 0 && c.k1 <= 64 &&
+  return c.cov_kind == SSVI_COV_FULL && c.model == SSVI_MODEL_D && c.rank <= 32 && c.k1 == 8 * SSVI_MEMO_KT &&
          c.order >= 2 && c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
 }
 
@@ -300,18 +300,23 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
     CUDA_TRY(h, cudaGetLastError());
   }
   if (n_chunks == 0) return SSVI_OK;
-  const size_t smem = (size_t)memo_cta_smem(NT, v.D, v.k1, (int)sizeof(ZT));
-#define SSVI_MEMO_LAUNCH(NOTH)                                                                                     \
+  const size_t smem = (size_t)memo_cta_smem(NT, v.D);
+  const int z_f32 = sizeof(ZT) == 4;
+#define SSVI_MEMO_LAUNCH(NOTH, ONES)                                                                               \
   do {                                                                                                             \
-    auto kern = accumulate_memo_kernel<NT, NOTH, ZT>;                                                              \
+    auto kern = accumulate_memo_kernel<NT, NOTH, ONES>;                                                            \
     CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));               \
     kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot,    \
-                                                chunk_out, entry_ids, rows, (const ZT*)h->z_own, partial_out);     \
+                                                chunk_out, entry_ids, rows, h->z_own, z_f32, partial_out);         \
   } while (0)
-  switch (mv.n_oth) {
-    case 1: SSVI_MEMO_LAUNCH(1); break;
-    case 2: SSVI_MEMO_LAUNCH(2); break;
-    default: SSVI_MEMO_LAUNCH(3); break;
+  const bool ones = (v.D & 7) != 0;
+  switch (mv.n_oth * 2 + (ones ? 1 : 0)) {
+    case 2: SSVI_MEMO_LAUNCH(1, false); break;
+    case 3: SSVI_MEMO_LAUNCH(1, true); break;
+    case 4: SSVI_MEMO_LAUNCH(2, false); break;
+    case 5: SSVI_MEMO_LAUNCH(2, true); break;
+    case 6: SSVI_MEMO_LAUNCH(3, false); break;
+    default: SSVI_MEMO_LAUNCH(3, true); break;
   }
 #undef SSVI_MEMO_LAUNCH
   CUDA_TRY(h, cudaGetLastError());

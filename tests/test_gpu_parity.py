@@ -181,11 +181,13 @@ def test_mma_path_matches_oracle_and_generic(D, k1, model, lik):
 
 @pytest.mark.parametrize("dims,D,k1,lik,P,W,offs", [
     ([6, 5, 4], 20, 64, "bernoulli", 4, 64, False),      # BASELINE config 2's kernel instance (NT=3, two other modes)
-    ([6, 5, 4], 12, 24, "normal", 3, 2, True),           # segments of 2 entries, shifted slots (multi-GPU shard)
-    ([5, 4, 4], 32, 64, "normal", 5, 3, False),          # NT=4 (config 5)
-    ([5, 4, 4], 30, 40, "poisson", 4, 64, True),
-    ([7, 9], 7, 16, "bernoulli", 2, 4, False),           # matrix: one other mode
+    ([6, 5, 4], 12, 64, "normal", 3, 2, True),           # segments of 2 entries, shifted slots (multi-GPU shard)
+    ([5, 4, 4], 32, 64, "normal", 5, 3, False),          # NT=4, D % 8 == 0 (config 5): row sums by DADD
+    ([5, 4, 4], 30, 64, "poisson", 4, 64, True),
+    ([5, 4, 4], 16, 64, "bernoulli", 2, 5, False),       # D % 8 == 0, NT=2
+    ([7, 9], 7, 64, "bernoulli", 2, 4, False),           # matrix: one other mode
     ([4, 3, 3, 3], 10, 64, "normal", 3, 64, False),      # 4-way: three other modes (config 1's NT=2)
+    ([40, 3, 3], 20, 64, "normal", 1, 200, False),       # one slot, chunks longer than 128 entries
 ])
 def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W, offs):
     """Full sweep through the slot-major sample-table kernels == the direct DMMA kernel == the generic CUDA-core
