@@ -255,6 +255,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--table-mb", type=float, default=48.0, help="sample-table budget per call (L2-resident)")
     ap.add_argument("--sweep-chunk", type=int, default=64, help="max entries of one (row, slot) chunk")
+    ap.add_argument("--sweep-streams", type=int, default=2, help="side streams the slot groups alternate between")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     c = CONFIGS[args.config]
@@ -276,7 +277,8 @@ def main():
         group = dist.group.WORLD
     data = DeviceTensorData(c, device, seed=319 + int(args.config[1:]) + 1000 * rank, scale=args.scale)
     model = build_model(c, data, device, group, args.chunk_entries, args.noise_slots,
-                        dict(table_budget_bytes=int(args.table_mb * (1 << 20)), sweep_chunk_entries=args.sweep_chunk))
+                        dict(table_budget_bytes=int(args.table_mb * (1 << 20)), sweep_chunk_entries=args.sweep_chunk,
+                             sweep_streams=args.sweep_streams))
     eng = model.engine
     N = model.order
     nnz_train = eng.nnz

@@ -159,6 +159,14 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
     for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
   }
 
+  double2 cur[NOTH][NT];                                // first k-tile of the first entry: in flight during the prologue
+#pragma unroll
+  for (int jj = 0; jj < NOTH; ++jj) {
+    const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
+#pragma unroll
+    for (int i = 0; i < NT; ++i) cur[jj][i] = ld_tab(p + (i * KT) * 32);
+  }
+
   // ---- prologue: U(row, slot) = m + L z_own, once per CTA (ui samples, SSVI_TF_interface.py:251-254) --------------------
   {
     const double2* src = reinterpret_cast<const double2*>(v.sampler[v.dim] + row * (int64_t)v.srow_len);
@@ -208,12 +216,13 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
         for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
       }
     }
-    double2 cur[NOTH][NT];
+    if (b0 > 0) {
 #pragma unroll
-    for (int jj = 0; jj < NOTH; ++jj) {
-      const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
+      for (int jj = 0; jj < NOTH; ++jj) {
+        const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
 #pragma unroll
-      for (int i = 0; i < NT; ++i) cur[jj][i] = ld_tab(p + (i * KT) * 32);
+        for (int i = 0; i < NT; ++i) cur[jj][i] = ld_tab(p + (i * KT) * 32);
+      }
     }
     for (int el = 0; el < nb; ++el) {
       const double y = __shfl_sync(0xffffffffu, my_y, el);

@@ -44,8 +44,15 @@ __device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, doub
     fst = is2 * (y - f);
     snd = -is2;
   } else if (lik == SSVI_LIK_BERNOULLI) {
-    double yf = y * f;
-    double sp = sigmoid_ref(yf, 0.0), sm = sigmoid_ref(-yf, 0.0);
+    // sigmoid(yf) and sigmoid(-yf) (bernoulli.py:40-51) from ONE exponential: with e = exp(-|yf|) in (0, 1],
+    // sigmoid(|yf|) = 1/(1+e) and sigmoid(-|yf|) = e/(1+e); equal to the reference's two evaluations to 2 ulp, and
+    // saturating to {1, 0} exactly where 1/(1+exp(-x)) does.
+    const double yf = y * f;
+    const double e = exp(-fabs(yf));
+    const double hi = 1.0 / (1.0 + e), lo = e * hi;
+    const bool pos = yf >= 0.0;
+    double sp = pos ? hi : lo, sm = pos ? lo : hi;
+    if (isnan(yf)) sp = sm = 0.0;                      // nan_to_num(sigmoid(nan)) = 0 (ProbFun.py:24)
     fst = y * sm;
     snd = -sp * sm;
   } else {

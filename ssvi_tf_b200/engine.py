@@ -145,7 +145,7 @@ class Engine(object):
     """One GPU's view of the problem: COO shard + CSR index + posterior state + noise pool."""
 
     def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16,
-                 kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64):
+                 kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64, sweep_streams=2):
         """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
         cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
         if not torch.cuda.is_available():
@@ -160,6 +160,8 @@ class Engine(object):
         self.chunk_entries = int(chunk_entries)
         self.table_budget_bytes = int(table_budget_bytes)      # L2-resident sample table of the sweep path
         self.sweep_chunk_entries = int(sweep_chunk_entries)
+        self.sweep_streams = int(sweep_streams)
+        self._side_streams = []
         self.noise_dtype = noise_dtype
         if cfg["mean_update"] not in UPDATE_IDS or cfg["cov_update"] not in UPDATE_IDS:
             raise Exception("Unidentified update formula for covariance param")   # SSVI_TF_interface.py:612, 632
@@ -430,16 +432,34 @@ class Engine(object):
         return plan
 
     def _accumulate_sweep(self, plan, partial, st):
-        tab = self._buf("sweep_table", (plan.table_bytes + 7) // 8)
+        """Slot groups alternate between `sweep_streams` side streams, each with its own table, so the tail of one
+        group's launch overlaps the next group's sampling and ramp-up; joined back into the caller's stream."""
+        ns = max(1, min(self.sweep_streams, len(plan.groups)))
+        tabs = [self._buf("sweep_table%d" % i, (plan.table_bytes + 7) // 8) for i in range(ns)]
 
         def at(tensor, i):
             return ctypes.c_void_p(tensor.data_ptr() + i * tensor.element_size())
-        for (s0, ns, c0, c1) in plan.groups:
-            self._call(self.lib.ssvi_sweep_accumulate, plan.dim, s0, ns, c1 - c0, at(plan.chunk_row, c0),
+        main = torch.cuda.current_stream(self.device)
+        if ns > 1:
+            if len(self._side_streams) < ns:
+                self._side_streams = [torch.cuda.Stream(device=self.device) for _ in range(ns)]
+            fork = torch.cuda.Event()
+            fork.record(main)
+            for s_ in self._side_streams[:ns]:
+                s_.wait_event(fork)
+        for k, (s0, nsl, c0, c1) in enumerate(plan.groups):
+            stream = ctypes.c_void_p(self._side_streams[k % ns].cuda_stream) if ns > 1 else st
+            tab = tabs[k % ns]
+            self._call(self.lib.ssvi_sweep_accumulate, plan.dim, s0, nsl, c1 - c0, at(plan.chunk_row, c0),
                        at(plan.chunk_start, c0), at(plan.chunk_len, c0), at(plan.chunk_slot, c0),
                        at(plan.chunk_out, c0), _ptr(plan.entry_ids), _ptr(plan.rows), _ptr(tab),
-                       tab.numel() * 8, _ptr(partial), st)
+                       tab.numel() * 8, _ptr(partial), stream)
             self.launches += 2 if c1 > c0 else 1
+        if ns > 1:
+            for s_ in self._side_streams[:ns]:
+                join = torch.cuda.Event()
+                join.record(s_)
+                main.wait_event(join)
 
     # -------------------------------------------------------------------------------------------
     def _buf(self, name, numel):
