@@ -163,10 +163,25 @@ def build_model(c, data, device, group, chunk_entries, noise_slots, engine_kwarg
                noise_slots=noise_slots, chunk_entries=chunk_entries, process_group=group, engine_kwargs=engine_kwargs)
 
 
-def one_step(model):
+def one_step(model, flush=None):
+    if flush is not None:
+        flush.zero_()                     # inputs smaller than L2: evict them between iterations
     for dim in range(model.order):
         model.sweep(dim)
         model.update_hyper_parameter(dim)
+
+
+def fp64_pipe_stats(c, units_per_s):
+    """Issued DMMA work of the sample-table path per unit: NP*16 contraction DMMAs per entry
+    (+ the once-per-chunk own-row sample, ignored), 512 FLOP each, against the measured FP64-pipe peak."""
+    if c["diag"] or c["model"] != "d" or c["D"] > 32 or c["k1"] != 64:
+        return None
+    nt = (c["D"] + 7) // 8
+    dmma = nt * (nt + 1) // 2 * 2 * (c["k1"] // 8)
+    peak = 37.1                           # TFLOP/s, profiles/r01_microbench_fp64_pipes.txt (mma.sync m8n8k4 f64)
+    ach = units_per_s * dmma * 512 / 1e12
+    return {"dmma_per_unit": dmma, "achieved_tflops": ach, "peak_tflops": peak, "frac": ach / peak,
+            "note": "issued DMMA FLOP only; the other FP64 instructions of a unit add ~30 % pipe time"}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -290,9 +305,15 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    in_bytes = eng.coords.numel() * 4 + eng.vals.numel() * 8 + 8 * N * nnz_train
+    flush = None
+    if in_bytes < 256 << 20:
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+    l2_note = ("L2 flushed between iterations (256 MB memset; inputs are %.0f MB)" % (in_bytes / 1e6)) if flush is not None \
+        else "inputs larger than L2 (COO+CSR %.0f MB per GPU)" % (in_bytes / 1e6)
     # ---- device-resident arm: `value` ------------------------------------------------------------
     for _ in range(args.warmup):
-        one_step(model)
+        one_step(model, flush)
     eng.check_flags()
     barrier()
     sampler = ClockSampler(local)
@@ -304,7 +325,7 @@ def main():
     barrier()
     e0.record()
     for _ in range(args.steps):
-        one_step(model)
+        one_step(model, flush)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -333,7 +354,14 @@ def main():
                 "traffic": None, "kernel": "accumulate (stages 1-3)", "peak_source": peak_src,
                 "algorithmic_bytes_per_unit": bpu, "kernel_ms_per_launch": float(np.mean(acc_ms)),
                 "kernel_share_of_step": sum(acc_ms) / ms,
-                "note": "fp64 work is bounded by the FP64 pipe (36 TFLOP/s measured), see DESIGN.md"}
+                "fp64_pipe": fp64_pipe_stats(c, sum(acc_units) / (sum(acc_ms) * 1e-3)),
+                "note": "fp64 contract: the FP64 pipe (37 TFLOP/s measured), not HBM, bounds this kernel; see DESIGN.md 3.1"}
+    tr_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr_path):          # DRAM bytes per unit from the committed ncu capture of this kernel
+        tr = json.load(open(tr_path)).get(args.config)
+        if tr:
+            roofline["traffic"] = tr["dram_bytes_per_unit"] * float(np.mean(acc_units))
+            roofline["traffic_source"] = tr["source"]
 
     # ---- end-to-end arm: host buffers in, host result out, every step ----------------------------
     pin = lambda x: x.cpu().pin_memory()                                      # noqa: E731
@@ -356,7 +384,7 @@ def main():
             dp.copy_(hp, non_blocking=True)
         for dn, hn in zip(d_noise, h_noise):
             dn.copy_(hn, non_blocking=True)
-        one_step(model)
+        one_step(model, flush)
         for ho, p in zip(h_out, eng.params):
             ho.copy_(p, non_blocking=True)
 
@@ -389,7 +417,7 @@ def main():
                        "noise": "f32 pool, %d slots" % eng.noise.slots, "chunk_entries": args.chunk_entries,
                        "path": ("sample-table sweep (slot-major), %d slots/call" % eng.plan_sweep(0).groups[0][1])
                        if eng.sweep_supported else "direct",
-                       "l2": "inputs larger than L2 (COO+CSR %.0f MB per GPU)" % (h2d / 1e6),
+                       "l2": l2_note,
                        "parallelism": "entries sharded x%d, all-reduce of row accumulators" % world},
             "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},

@@ -60,7 +60,7 @@ __device__ void jacobi_eigh(double* A, double* Vm, int D, double* scratch, int32
   double* red = scratch + 4 * (np + 1);
   for (int i = tid; i < D * D; i += nt) Vm[i] = (i / D == i % D) ? 1.0 : 0.0;
   __syncthreads();
-  const int max_sweeps = 30;
+  const int max_sweeps = 40;
   int sweep = 0;
   for (; sweep < max_sweeps; ++sweep) {
     double off = 0.0, tot = 0.0;
@@ -71,7 +71,8 @@ __device__ void jacobi_eigh(double* A, double* Vm, int D, double* scratch, int32
     }
     off = block_sum(off, red);
     tot = block_sum(tot, red);
-    if (off <= 1e-30 * tot || tot == 0.0) break;
+    // converged: off-diagonal Frobenius mass at the rounding floor (about D eps^2 of the total after a sweep)
+    if (off <= 1e-27 * tot || tot == 0.0) break;
     for (int r = 0; r < n - 1; ++r) {
       // tournament pairing of round r: player n-1 fixed, the others rotate
       if (tid < np) {
