@@ -28,10 +28,40 @@ __device__ __forceinline__ double factorial_ref(double y) {
   return r;
 }
 
+// A^y for the integral counts y of count data (np.power(A, y), poisson.py:23): binary powering, <= 8 squarings for
+// y <= 170; a few ulp from the libm pow, and it overflows / underflows where pow does.
+__device__ __forceinline__ double ipow_ref(double a, double y) {
+  int n = (int)y;
+  double r = 1.0;
+  while (n > 0) {
+    if (n & 1) r *= a;
+    a *= a;
+    n >>= 1;
+  }
+  return r;
+}
+
+// One exponential serves sigmoid(f) and poisson_link(f) (ProbFun.py:22-28, 52-55): with E = exp(f),
+//   poisson_link = max(nan_to_num(log(1 + E)), 1e-8),  sigmoid = 1/(1 + exp(-f)) = E/(1 + E)  (1 when E overflows).
+struct PoissonTerms {
+  double E1;    // 1 + exp(f)
+  double A;     // poisson_link(f)
+  double sg;    // sigmoid(f)
+};
+__device__ __forceinline__ PoissonTerms poisson_terms(double f) {
+  PoissonTerms t;
+  const double E = exp(f);
+  t.E1 = 1.0 + E;
+  t.A = fmax(nan_to_num(log(t.E1)), 1e-8);
+  t.sg = (E > 1e300) ? 1.0 : E / t.E1;
+  if (isnan(f)) t.sg = 0.0;                           // nan_to_num(sigmoid(nan)) = 0
+  return t;
+}
+
 // poisson.py:19-27  pdf(y, m) = max(A^y / (1+e^m) / y!, 1e-8), A = poisson_link(m)
 __device__ __forceinline__ double poisson_pdf_ref(double y, double m, double yfact) {
   double A = poisson_link_ref(m);
-  double r = pow(A, y) / (1.0 + exp(m)) / yfact;
+  double r = ipow_ref(A, y) / (1.0 + exp(m)) / yfact;
   return fmax(r, 1e-8);
 }
 
@@ -56,8 +86,8 @@ __device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, doub
     fst = y * sm;
     snd = -sp * sm;
   } else {
-    double sg = sigmoid_ref(f, 0.0);
-    double A = poisson_link_ref(f);
+    const PoissonTerms pt = poisson_terms(f);
+    const double sg = pt.sg, A = pt.A;
     double t = y / A - 1.0;
     fst = nan_to_num(sg * t);
     snd = nan_to_num(sg * (1.0 - sg) * t - y * (sg * sg) / (A * A));
@@ -79,10 +109,10 @@ __device__ __forceinline__ void pdf_derivs(int lik, double y, double f, double s
     p1 = (y * sg) * (1.0 - sg);
     p2 = sg * (1.0 - sg) * (1.0 - 2.0 * sg);
   } else {
-    double A = poisson_link_ref(f);
-    double sg = sigmoid_ref(f, 0.0);
+    const PoissonTerms pt = poisson_terms(f);
+    const double A = pt.A, sg = pt.sg;
     double t = y / A - 1.0;
-    p = poisson_pdf_ref(y, f, yfact);
+    p = fmax(ipow_ref(A, y) / pt.E1 / yfact, 1e-8);   // pdf(y, f), poisson.py:19-27
     p1 = p * (sg * t);
     double pl = poisson_pdf_ref(y, A, yfact);         // Q7: pdf(y, poisson_link(m))
     double temp = -(y / (A * A)) * (sg * sg) + t * (sg * (1.0 - sg));
