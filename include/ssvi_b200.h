@@ -170,14 +170,19 @@ int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t*
  *   chunk_out[c]    int64  index of the chunk's record inside partial_out (any order; lets the caller keep the
  *                          records row-major for ssvi_reduce_chunks while the launch order is slot-major)
  * chunk_row / chunk_start / chunk_len / entry_ids / rows / partial_out as for ssvi_accumulate.
- * table_ws: device workspace of at least ssvi_sweep_table_bytes(h, dim, n_slots) bytes, 16-byte aligned. */
+ * table_ws: device workspace of at least ssvi_sweep_table_bytes(h, dim, n_slots) bytes, 16-byte aligned.
+ *
+ * Diagonal covariance (every model, rank <= 64, k1 % 16 == 0, k1 <= 64, order <= 4) takes the same slot-major chunk
+ * tables: samples are element-wise there, so nothing is tabulated (ssvi_sweep_table_bytes == 0, table_ws may be NULL,
+ * any slot range in one call); each CTA stages its chunk's noise blocks in shared memory once instead.
+ * w_state as for ssvi_accumulate (simple / robust; may be NULL for SSVI_TF_d). */
 int ssvi_sweep_supported(const SsviHandle* h);                                   /* 1 if this path applies to h's config */
 int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int32_t n_slots);
 int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo, int32_t n_slots, int64_t n_chunks,
                           const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
                           const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
-                          const int64_t* rows, void* table_ws, int64_t table_ws_bytes, double* partial_out,
-                          void* stream);
+                          const int64_t* rows, const double* w_state, void* table_ws, int64_t table_ws_bytes,
+                          double* partial_out, void* stream);
 
 /* Deterministic in-order sum of the chunk records of each row:
  *   acc_out[r] = sum_{c = row_chunk_ptr[r] .. row_chunk_ptr[r+1]-1} partial[c]

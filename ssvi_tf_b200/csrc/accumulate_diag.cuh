@@ -1,0 +1,281 @@
+// Stages 1-3 for FULL SWEEPS with a DIAGONAL covariance (every model, D <= 64, k1 % 16 == 0, k1 <= 64), slot-major.
+//
+// With a diagonal covariance a sample is element-wise, x[n][k] = m[n] + sqrt(S)[n] * z[n][k]
+// (Posterior_Diag_Covariance, Model/TF_Models.py:72-93; sample_vjs_batch, SSVI_TF_interface.py:732-750), so there is no
+// dense contraction and nothing worth memoising: re-evaluating a sample costs D*k1 FMAs against 8*D*k1 bytes to read it
+// back.  What IS shared is the noise: in a sweep all entries of a chunk (one row, one noise slot) read the same N noise
+// blocks, so one CTA stages them in shared memory ONCE (as doubles: an F2F.F64.F32 costs four DFMAs on this part) and its
+// 4 warps stream the chunk's entries against them.  Per entry only the N-1 gathered (mean, sqrt S) rows come from global
+// memory -- the algorithmic bytes of SURVEY.md 8(d).
+//
+// Lanes run over components: lane l owns n = 2l, 2l+1, so the per-row accumulators g[n], G[n] (di, Di) live in
+// registers across the whole chunk and need no reduction.  The predictive mean f_k = sum_n u[n][k] v[n][k] is reduced
+// over lanes 16 samples at a time with a transposing shuffle reduction (16 shuffles per 16 samples), after which every
+// lane owns two samples' f and evaluates their likelihood weights (the k2 second-layer loop for SSVI_TF_simple /
+// SSVI_TF_robust).  SSVI_TF_d (weights uniform in k, SSVI_TF_d.py:31-57 quirk Q3) needs one pass; simple / robust
+// re-evaluate v in a second pass once the per-sample weights are known.
+#pragma once
+#include "accumulate_generic.cuh"
+
+__host__ __device__ inline int diag_dp(int D) { return (D + 1) & ~1; }          // components padded to even
+// shared memory of one CTA (4 warps): N noise blocks [k][DP] as doubles | per-warp weights [k1] double2 | reduction
+__host__ __device__ inline size_t diag_cta_smem(int N, int D, int k1) {
+  return (size_t)N * k1 * diag_dp(D) * 8 + (size_t)4 * k1 * 16 + (size_t)4 * (2 * diag_dp(D) + 2) * 8;
+}
+
+// sum over the 32 lanes of p[0..15]; on return lane l holds the total of sample (l >> 1) (both lanes of a pair)
+__device__ __forceinline__ double transpose_reduce16(double (&p)[16], int lane) {
+  const bool b4 = (lane & 16) != 0, b3 = (lane & 8) != 0, b2 = (lane & 4) != 0, b1 = (lane & 2) != 0;
+  double r8[8], r4[4], r2[2];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const double give = b4 ? p[j] : p[j + 8], keep = b4 ? p[j + 8] : p[j];
+    r8[j] = keep + __shfl_xor_sync(0xffffffffu, give, 16);
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const double give = b3 ? r8[j] : r8[j + 4], keep = b3 ? r8[j + 4] : r8[j];
+    r4[j] = keep + __shfl_xor_sync(0xffffffffu, give, 8);
+  }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const double give = b2 ? r4[j] : r4[j + 2], keep = b2 ? r4[j + 2] : r4[j];
+    r2[j] = keep + __shfl_xor_sync(0xffffffffu, give, 4);
+  }
+  const double give = b1 ? r2[0] : r2[1], keep = b1 ? r2[1] : r2[0];
+  double r = keep + __shfl_xor_sync(0xffffffffu, give, 2);
+  r += __shfl_xor_sync(0xffffffffu, r, 1);
+  return r;                                             // sample index 8*b4 + 4*b3 + 2*b2 + b1 = lane >> 1
+}
+
+// v[0..1] = prod_jj (m + s z) for this lane's two components at sample k; z blocks staged as [blk][k][DP]
+template <int NOTH>
+__device__ __forceinline__ void diag_v(const double* __restrict__ zs, int blk_stride, int k, int DP, int zoff,
+                                       const double (&m)[NOTH][2], const double (&s)[NOTH][2], double& v0,
+                                       double& v1) {
+#pragma unroll
+  for (int jj = 0; jj < NOTH; ++jj) {
+    const double2 z = *reinterpret_cast<const double2*>(zs + (size_t)jj * blk_stride + k * DP + zoff);
+    const double x0 = fma(s[jj][0], z.x, m[jj][0]), x1 = fma(s[jj][1], z.y, m[jj][1]);
+    if (jj == 0) {
+      v0 = x0;
+      v1 = x1;
+    } else {
+      v0 *= x0;
+      v1 *= x1;
+    }
+  }
+}
+
+// One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.
+template <int NOTH, typename ZT, bool SECOND>
+__global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
+    DevView v, int64_t n_chunks, const int32_t* __restrict__ chunk_row, const int64_t* __restrict__ chunk_start,
+    const int32_t* __restrict__ chunk_len, const int32_t* __restrict__ chunk_slot,
+    const int64_t* __restrict__ chunk_out, const int64_t* __restrict__ entry_ids, const int64_t* __restrict__ rows,
+    const double* __restrict__ w_state, const ZT* __restrict__ z_other, const ZT* __restrict__ z_own,
+    const ZT* __restrict__ r_w, const ZT* __restrict__ z_f, double* __restrict__ partial_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t c = blockIdx.x;
+  if (c >= n_chunks) return;
+  const int N = v.N, D = v.D, k1 = v.k1, DP = diag_dp(D), dim = v.dim;
+  const int blk_stride = k1 * DP;
+  double* zs = reinterpret_cast<double*>(smem_raw);                      // [N][k1][DP]: other modes, then own
+  double2* AW = reinterpret_cast<double2*>(zs + (size_t)N * blk_stride) + warp * k1;
+  double* red = reinterpret_cast<double*>(zs + (size_t)N * blk_stride) + 4 * k1 * 2;
+
+  const int64_t row = rows[chunk_row[c]];
+  const int64_t start = chunk_start[c];
+  const int len = chunk_len[c], slot = chunk_slot[c];
+  const double w_sigma = SECOND ? w_state[0] : 1.0;
+
+  int od[NOTH];
+  {
+    int jj = 0;
+#pragma unroll
+    for (int d = 0; d < SSVI_MAX_ORDER; ++d)
+      if (d < N && d != dim && jj < NOTH) od[jj++] = d;
+  }
+
+  // ---- this warp's entries (w, w+4, ...): ids, values and gathered-row offsets fetched lane-parallel -----------------
+  const int my_cnt = (len - warp + 3) >> 2;
+  double my_y = 0.0;
+  int32_t my_col[NOTH];
+#pragma unroll
+  for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
+  if (lane < my_cnt) {
+    const int64_t eid = entry_ids[start + (int64_t)lane * 4 + warp];
+    my_y = v.vals[eid];
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
+  }
+
+  // ---- stage the slot's noise blocks as doubles, [blk][k][c] (pool layout is [c][k]) ----------------------------------
+  for (int b = 0; b < N; ++b) {
+    const ZT* src = (b < N - 1) ? z_other + ((int64_t)slot * (N - 1) + b) * v.zblk : z_own + (int64_t)slot * v.zblk;
+    double* dst = zs + (size_t)b * blk_stride;
+    for (int idx = tid; idx < D * k1; idx += 128) {
+      const int cc = idx / k1, k = idx - cc * k1;
+      dst[k * DP + cc] = (double)src[idx];
+    }
+    if (DP != D)
+      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
+  }
+  // own row: lane l owns components 2l, 2l+1 (zero beyond D: they then contribute exact zeros everywhere)
+  const int n0 = 2 * lane, n1 = 2 * lane + 1;
+  const int zoff = n0 < DP ? n0 : 0;                    // idle lanes (n0 >= D) read valid noise against m = s = 0
+  double mo[2], so[2];
+  {
+    const double* src = v.sampler[dim] + row * (int64_t)v.srow_len;
+    mo[0] = n0 < D ? src[n0] : 0.0;
+    mo[1] = n1 < D ? src[n1] : 0.0;
+    so[0] = n0 < D ? src[D + n0] : 0.0;
+    so[1] = n1 < D ? src[D + n1] : 0.0;
+  }
+  __syncthreads();
+
+  double g0 = 0.0, g1 = 0.0, G0 = 0.0, G1 = 0.0, si_part = 0.0;
+  bool bad = false;
+  const double inv_k1 = 1.0 / (double)k1;
+  const double* zo = zs + (size_t)(N - 1) * blk_stride;
+
+  for (int b0 = 0; b0 < my_cnt; b0 += 32) {
+    const int nb = min(32, my_cnt - b0);
+    if (b0 > 0) {
+      my_y = 0.0;
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
+      if (lane < nb) {
+        const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
+        my_y = v.vals[eid];
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
+      }
+    }
+    // gathered rows of the first entry
+    double mn[NOTH][2], sn[NOTH][2];
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) {
+      const double* src = v.sampler[od[jj]] + (int64_t)__shfl_sync(0xffffffffu, my_col[jj], 0) * v.srow_len;
+      mn[jj][0] = n0 < D ? src[n0] : 0.0;
+      mn[jj][1] = n1 < D ? src[n1] : 0.0;
+      sn[jj][0] = n0 < D ? src[D + n0] : 0.0;
+      sn[jj][1] = n1 < D ? src[D + n1] : 0.0;
+    }
+    for (int el = 0; el < nb; ++el) {
+      const double y = __shfl_sync(0xffffffffu, my_y, el);
+      double m[NOTH][2], s[NOTH][2];
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) {
+        m[jj][0] = mn[jj][0];
+        m[jj][1] = mn[jj][1];
+        s[jj][0] = sn[jj][0];
+        s[jj][1] = sn[jj][1];
+      }
+      {                                                  // prefetch the next entry's rows (last entry: its own again)
+        const int eln = (el + 1 < nb) ? el + 1 : el;
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj) {
+          const double* src = v.sampler[od[jj]] + (int64_t)__shfl_sync(0xffffffffu, my_col[jj], eln) * v.srow_len;
+          mn[jj][0] = n0 < D ? src[n0] : 0.0;
+          mn[jj][1] = n1 < D ? src[n1] : 0.0;
+          sn[jj][0] = n0 < D ? src[D + n0] : 0.0;
+          sn[jj][1] = n1 < D ? src[D + n1] : 0.0;
+        }
+      }
+      // ---- pass 1: f_k, and for SSVI_TF_d the plain sums over k ---------------------------------------------------
+      double sv0 = 0.0, sv1 = 0.0, sq0 = 0.0, sq1 = 0.0;
+      double fk[2] = {0.0, 0.0};                         // lane owns samples 16*(2a + (lane&1)) + (lane>>1), a = 0, 1
+      for (int tile = 0; tile < (k1 >> 4); ++tile) {
+        double p[16];
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) {
+          const int k = tile * 16 + kk;
+          double v0, v1;
+          diag_v<NOTH>(zs, blk_stride, k, DP, zoff, m, s, v0, v1);
+          const double2 z = *reinterpret_cast<const double2*>(zo + k * DP + zoff);
+          const double u0 = fma(so[0], z.x, mo[0]), u1 = fma(so[1], z.y, mo[1]);
+          p[kk] = fma(u1, v1, u0 * v0);
+          if (!SECOND) {
+            sv0 += v0;
+            sv1 += v1;
+            sq0 = fma(v0, v0, sq0);
+            sq1 = fma(v1, v1, sq1);
+          }
+        }
+        const double f = transpose_reduce16(p, lane);
+        if ((tile & 1) == (lane & 1)) {
+          if (tile < 2) fk[0] = f; else fk[1] = f;
+        }
+      }
+      if (!SECOND) {
+        // SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1, then broadcast
+        double sum_a = 0.0, sum_d = 0.0;
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          const int k = 16 * (2 * a + (lane & 1)) + (lane >> 1);
+          if (k < k1) {
+            double fa, fb;
+            log_pdf_derivs(v.lik, y, fk[a], v.lik_param, fa, fb);
+            sum_a += fa;
+            sum_d += fb;
+          }
+        }
+        sum_a = warp_sum(sum_a) * inv_k1;
+        sum_d = warp_sum(sum_d) * inv_k1;
+        const double aw = sum_a * inv_k1, dw = 0.5 * sum_d * inv_k1;
+        g0 = fma(aw, sv0, g0);
+        g1 = fma(aw, sv1, g1);
+        G0 = fma(dw, sq0, G0);
+        G1 = fma(dw, sq1, G1);
+      } else {
+        // simple / robust: per-sample weights (second-layer k2 loop), then pass 2 re-evaluates v
+        const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? factorial_ref(y) : 1.0;
+        __syncwarp();
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+          const int k = 16 * (2 * a + (lane & 1)) + (lane >> 1);
+          const bool active = k < k1;
+          double aw, dw;
+          likelihood_weights<ZT>(v, r_w, z_f, slot, k, active, y, yfact, fk[a], w_sigma, aw, dw, si_part, bad);
+          if (active) AW[k] = make_double2(aw, dw);
+        }
+        __syncwarp();
+#pragma unroll 4
+        for (int k = 0; k < k1; ++k) {
+          double v0, v1;
+          diag_v<NOTH>(zs, blk_stride, k, DP, zoff, m, s, v0, v1);
+          const double2 w = AW[k];
+          g0 = fma(w.x, v0, g0);
+          g1 = fma(w.x, v1, g1);
+          G0 = fma(w.y * v0, v0, G0);
+          G1 = fma(w.y * v1, v1, G1);
+        }
+      }
+    }
+  }
+
+  // ---- CTA reduction in fixed warp order; chunk record [di (D) | Di (D) | si_sum | count] -----------------------------
+  si_part = warp_sum(si_part);
+  const unsigned anybad = __ballot_sync(0xffffffffu, bad);
+  double* rw = red + warp * (2 * DP + 2);
+  if (n0 < DP) {
+    rw[n0] = g0;
+    rw[n1] = g1;
+    rw[DP + n0] = G0;
+    rw[DP + n1] = G1;
+  }
+  if (lane == 0) {
+    rw[2 * DP] = si_part;
+    if (anybad) atomicOr(v.flags, SSVI_FLAG_PHI_ZERO);
+  }
+  __syncthreads();
+  double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;
+  const int rs = 2 * DP + 2;
+  for (int i = tid; i < 2 * D + 1; i += 128) {
+    const int src = i < D ? i : (i < 2 * D ? DP + (i - D) : 2 * DP);
+    out[i] = ((red[src] + red[rs + src]) + red[2 * rs + src]) + red[3 * rs + src];
+  }
+  if (tid == 0) out[2 * D + 1] = (double)len;
+}

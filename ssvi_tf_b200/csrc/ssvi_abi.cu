@@ -4,6 +4,7 @@
 #include <new>
 
 #include "accumulate_memo.cuh"
+#include "accumulate_diag.cuh"
 #include "row_update.cuh"
 
 #define SSVI_VERSION_STR "ssvi_b200 0.1 sm_100a"
@@ -270,15 +271,21 @@ extern "C" int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, con
 }
 
 // ---- sample-table ("memoised") sweep path: accumulate_memo.cuh ------------------------------------------------------
-static bool sweep_ok(const SsviConfig& c) {
+static bool sweep_diag_ok(const SsviConfig& c, int max_smem) {
+  return c.cov_kind == SSVI_COV_DIAG && c.rank <= 64 && (c.k1 % 16) == 0 && c.k1 <= 64 && c.order >= 2 &&
+         c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1 &&
+         diag_cta_smem(c.order, c.rank, c.k1) <= (size_t)max_smem;
+}
+static bool sweep_full_ok(const SsviConfig& c) {
   return c.cov_kind == SSVI_COV_FULL && c.model == SSVI_MODEL_D && c.rank <= 32 && c.k1 == 8 * SSVI_MEMO_KT &&
          c.order >= 2 && c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
 }
+static bool sweep_ok(const SsviHandle* h) { return sweep_full_ok(h->cfg) || sweep_diag_ok(h->cfg, h->max_smem_optin); }
 
-extern "C" int ssvi_sweep_supported(const SsviHandle* h) { return (h && sweep_ok(h->cfg)) ? 1 : 0; }
+extern "C" int ssvi_sweep_supported(const SsviHandle* h) { return (h && sweep_ok(h)) ? 1 : 0; }
 
 extern "C" int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int32_t n_slots) {
-  if (!h || !sweep_ok(h->cfg) || dim < 0 || dim >= h->cfg.order || n_slots < 1) return 0;
+  if (!h || !sweep_full_ok(h->cfg) || dim < 0 || dim >= h->cfg.order || n_slots < 1) return 0;   // diagonal: no table
   int64_t recs = 0;
   for (int d = 0; d < h->cfg.order; ++d)
     if (d != dim) recs += h->cfg.dims[d] * (int64_t)n_slots;
@@ -323,17 +330,60 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
   return SSVI_OK;
 }
 
+template <int NOTH, typename ZT, bool SECOND>
+static int launch_sweep_diag(SsviHandle* h, const DevView& v, int64_t n_chunks, const int32_t* chunk_row,
+                             const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
+                             const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows,
+                             const double* w_state, double* partial_out, cudaStream_t st) {
+  const size_t smem = diag_cta_smem(v.N, v.D, v.k1);
+  auto kern = accumulate_diag_kernel<NOTH, ZT, SECOND>;
+  CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
+                                              entry_ids, rows, w_state, (const ZT*)h->z_other, (const ZT*)h->z_own,
+                                              (const ZT*)h->r_w, (const ZT*)h->z_f, partial_out);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+static int sweep_diag(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t* chunk_row, const int64_t* chunk_start,
+                      const int32_t* chunk_len, const int32_t* chunk_slot, const int64_t* chunk_out,
+                      const int64_t* entry_ids, const int64_t* rows, const double* w_state, double* partial_out,
+                      cudaStream_t st) {
+  if (n_chunks == 0) return SSVI_OK;
+  if (!chunk_row || !chunk_start || !chunk_len || !chunk_slot || !chunk_out || !entry_ids || !rows || !partial_out)
+    return fail(h, SSVI_E_INVALID, "sweep_accumulate: null pointer%s");
+  const bool second = h->cfg.model != SSVI_MODEL_D;
+  if (second && !w_state) return fail(h, SSVI_E_INVALID, "sweep_accumulate: w_state required for simple/robust%s");
+  const DevView v = make_view(h, dim);
+#define SSVI_DIAG_ARGS h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, w_state, partial_out, st
+#define SSVI_DIAG_CASE(NOTH)                                                                              \
+  if (h->cfg.noise_dtype == SSVI_NOISE_F32)                                                               \
+    return second ? launch_sweep_diag<NOTH, float, true>(SSVI_DIAG_ARGS) : launch_sweep_diag<NOTH, float, false>(SSVI_DIAG_ARGS); \
+  return second ? launch_sweep_diag<NOTH, double, true>(SSVI_DIAG_ARGS) : launch_sweep_diag<NOTH, double, false>(SSVI_DIAG_ARGS);
+  switch (h->cfg.order - 1) {
+    case 1: SSVI_DIAG_CASE(1)
+    case 2: SSVI_DIAG_CASE(2)
+    default: SSVI_DIAG_CASE(3)
+  }
+#undef SSVI_DIAG_CASE
+#undef SSVI_DIAG_ARGS
+}
+
 extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo, int32_t n_slots, int64_t n_chunks,
                                      const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
                                      const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
-                                     const int64_t* rows, void* table_ws, int64_t table_ws_bytes, double* partial_out,
-                                     void* stream) {
+                                     const int64_t* rows, const double* w_state, void* table_ws,
+                                     int64_t table_ws_bytes, double* partial_out, void* stream) {
   if (!h) return SSVI_E_INVALID;
   if (!h->data_bound || !h->state_bound || !h->noise_bound) return fail(h, SSVI_E_STATE, "sweep_accumulate: bind data, state and noise first%s");
-  if (!sweep_ok(h->cfg)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: configuration not supported by the sample-table path (see ssvi_sweep_supported)%s");
+  if (!sweep_ok(h)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: configuration not supported by the sample-table path (see ssvi_sweep_supported)%s");
   if (dim < 0 || dim >= h->cfg.order) return fail(h, SSVI_E_INVALID, "sweep_accumulate: bad dim%s");
   if (n_slots < 1 || slot_lo < 0 || slot_lo + n_slots > h->pool_slots) return fail(h, SSVI_E_INVALID, "sweep_accumulate: slot range outside the noise pool%s");
-  if (n_chunks < 0 || !table_ws) return fail(h, SSVI_E_INVALID, "sweep_accumulate: null workspace%s");
+  if (n_chunks < 0) return fail(h, SSVI_E_INVALID, "sweep_accumulate: negative chunk count%s");
+  if (h->cfg.cov_kind == SSVI_COV_DIAG)
+    return sweep_diag(h, dim, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows,
+                      w_state, partial_out, (cudaStream_t)stream);
+  if (!table_ws) return fail(h, SSVI_E_INVALID, "sweep_accumulate: null workspace%s");
   if (n_chunks > 0 && (!chunk_row || !chunk_start || !chunk_len || !chunk_slot || !chunk_out || !entry_ids || !rows || !partial_out))
     return fail(h, SSVI_E_INVALID, "sweep_accumulate: null pointer%s");
   if (table_ws_bytes < ssvi_sweep_table_bytes(h, dim, n_slots)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: table workspace too small%s");

@@ -396,7 +396,7 @@ class Engine(object):
         s_idx = np.arange(P, dtype=np.int64)[:, None]
         b0 = (s_idx - off[None, :]) % P                          # first position of row r that reads slot s
         cnt = np.where(lens[None, :] > b0, (lens[None, :] - b0 + P - 1) // P, 0)      # [P, n]
-        W = self.sweep_chunk_entries
+        W = self.sweep_chunk_entries * (4 if self.diag else 1)   # diagonal: a CTA stages N noise blocks per chunk
         nseg = (cnt + W - 1) // W                                # [P, n]
         flat_cnt, flat_seg = cnt.reshape(-1), nseg.reshape(-1)   # (slot, row) order == launch order
         pair_start = np.zeros(P * n + 1, dtype=np.int64)
@@ -452,9 +452,9 @@ class Engine(object):
             tab = tabs[k % ns]
             self._call(self.lib.ssvi_sweep_accumulate, plan.dim, s0, nsl, c1 - c0, at(plan.chunk_row, c0),
                        at(plan.chunk_start, c0), at(plan.chunk_len, c0), at(plan.chunk_slot, c0),
-                       at(plan.chunk_out, c0), _ptr(plan.entry_ids), _ptr(plan.rows), _ptr(tab),
+                       at(plan.chunk_out, c0), _ptr(plan.entry_ids), _ptr(plan.rows), _ptr(self.w_state), _ptr(tab),
                        tab.numel() * 8, _ptr(partial), stream)
-            self.launches += 2 if c1 > c0 else 1
+            self.launches += (1 if self.diag else 2) if c1 > c0 else (0 if self.diag else 1)
         if ns > 1:
             for s_ in self._side_streams[:ns]:
                 join = torch.cuda.Event()

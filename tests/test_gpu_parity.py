@@ -238,3 +238,55 @@ def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W
         so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
         for got in states:
             assert_state_close(got, want, cfg, RTOL, what="dims=%s mode %d" % (dims, dim))
+
+
+@pytest.mark.parametrize("dims,D,k1,model,lik,P,W,offs", [
+    ([6, 5, 4], 50, 64, "simple", "normal", 4, 64, False),       # BASELINE config 4's kernel instance (3-way slice)
+    ([4, 3, 3, 3], 50, 64, "simple", "normal", 3, 64, False),    # config 4: 4-way, three other modes
+    ([6, 5, 4], 7, 16, "d", "bernoulli", 3, 1, True),            # odd D, one k-tile, segments of 4, shifted slots
+    ([6, 5, 4], 33, 32, "d", "poisson", 2, 64, False),
+    ([5, 4, 4], 20, 64, "robust", "poisson", 4, 2, True),
+    ([5, 4, 4], 64, 48, "robust", "bernoulli", 2, 64, False),    # D = 64: every lane busy
+    ([7, 9], 12, 64, "simple", "poisson", 3, 64, False),         # matrix
+])
+def test_sweep_diag_path_matches_generic_and_oracle(dims, D, k1, model, lik, P, W, offs):
+    """Diagonal covariance, full sweep through the slot-major shared-noise kernel == the generic kernel == the oracle."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(D * 1000 + k1 + P)
+    N = len(dims)
+    cfg = so.make_config(model, lik, D, diag=True, k1=k1, k2=6, batch_size=10 ** 9)
+    nnz = int(0.8 * np.prod(dims))
+    coords, vals = random_problem(rng, lik, dims, nnz)
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    pool = so.make_tape(rng, cfg, N, P)
+    for dim in range(N):
+        n = dims[dim]
+        off = rng.integers(0, 50, size=n) if offs else None
+        accs, states = [], []
+        for path, sweep in ((0, True), (1, False)):
+            eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, chunk_entries=3,
+                         kernel_path=path, sweep_chunk_entries=W)
+            eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=True))
+            engine_load_state(eng, st0)
+            assert eng.sweep_supported == (path == 0)
+            plan = eng.plan_sweep(dim, off) if sweep else eng.plan_full(dim, None, off)
+            acc = eng.accumulate(plan).cpu().numpy().copy()
+            eng.row_update(plan, eng.accumulate(plan))
+            eng.check_flags()
+            accs.append(acc)
+            states.append(engine_dump_state(eng, st0))
+            eng.close()
+        scale = np.abs(accs[1]).max()
+        np.testing.assert_allclose(accs[0], accs[1], rtol=1e-9, atol=1e-12 * scale)
+        np.testing.assert_array_equal(accs[0][:, -1], np.diff(rowptr[dim]))
+        entries, tapes = [], []
+        for row in range(n):
+            ids = perm[dim][rowptr[dim][row]:rowptr[dim][row + 1]]
+            sl = (np.arange(len(ids)) + (0 if off is None else int(off[row]))) % P
+            tapes.append(so.Tape(pool.z_other[sl], pool.z_own[sl], pool.r_w[sl], pool.z_f[sl]))
+            entries.append((coords[ids], vals[ids]))
+        want = so.copy_state(st0)
+        so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
+        for got in states:
+            assert_state_close(got, want, cfg, RTOL, what="dims=%s mode %d" % (dims, dim))
