@@ -135,6 +135,29 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
   }
   __syncthreads();
 
+  // SSVI_TF_simple + normal likelihood: d log p / df is linear in f, so the k2 mean of SSVI_TF_simple.py:35-38 is
+  // (y - f - ws * mean_i z_f[i][k]) / s^2, and both ws and that mean are constants of the chunk (one slot).
+  const bool lin = SECOND && v.model == SSVI_MODEL_SIMPLE && v.lik == SSVI_LIK_NORMAL;
+  double zbar[2] = {0.0, 0.0}, wsl[2] = {0.0, 0.0};
+  if (lin) {
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      const int k = 16 * (2 * a + (lane & 1)) + (lane >> 1);
+      if (k < k1) {
+        const ZT* zf = z_f + (int64_t)slot * v.k2 * k1 + k;
+        double t = 0.0;
+        for (int i0 = 0; i0 < v.k2; i0 += 8) {
+          double zz[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) zz[j] = (i0 + j < v.k2) ? ldz(zf, (int64_t)(i0 + j) * k1) : 0.0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) t += zz[j];
+        }
+        zbar[a] = t / (double)v.k2;
+        wsl[a] = (w_sigma * w_sigma) * ldz(r_w, (int64_t)slot * k1 + k);
+      }
+    }
+  }
   double g0 = 0.0, g1 = 0.0, G0 = 0.0, G1 = 0.0, si_part = 0.0;
   bool bad = false;
   const double inv_k1 = 1.0 / (double)k1;
@@ -238,7 +261,14 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
           const int k = 16 * (2 * a + (lane & 1)) + (lane >> 1);
           const bool active = k < k1;
           double aw, dw;
-          likelihood_weights<ZT>(v, r_w, z_f, slot, k, active, y, yfact, fk[a], w_sigma, aw, dw, si_part, bad);
+          if (lin) {
+            const double is2 = 1.0 / (v.lik_param * v.lik_param);
+            aw = is2 * (y - fk[a] - wsl[a] * zbar[a]) * inv_k1;
+            dw = -0.5 * is2 * inv_k1;
+            if (active) si_part -= is2 * wsl[a];
+          } else {
+            likelihood_weights<ZT>(v, r_w, z_f, slot, k, active, y, yfact, fk[a], w_sigma, aw, dw, si_part, bad);
+          }
           if (active) AW[k] = make_double2(aw, dw);
         }
         __syncwarp();

@@ -36,14 +36,23 @@ __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* _
   if (!active) return;
   const double ws = (w_sigma * w_sigma) * ldz(r_w, (int64_t)slot * k1 + k);   // rayleigh(scale=w_sigma^2)
   const ZT* zf = z_f + (int64_t)slot * k2 * k1 + k;
+  // second-layer samples fs = f + ws * z_f (Q2: the Rayleigh draw is the standard deviation); the k2 variates are
+  // fetched 8 at a time so the loads are in flight together instead of one L2 round trip per sample
   if (v.model == SSVI_MODEL_SIMPLE) {
     double sf = 0.0, ss = 0.0;
-    for (int i2 = 0; i2 < k2; ++i2) {
-      double fs = f + ws * ldz(zf, (int64_t)i2 * k1);                        // Q2: scale = var(0) + ws
-      double a, b;
-      log_pdf_derivs(v.lik, y, fs, s, a, b);
-      sf += a;
-      ss += b;
+    for (int i0 = 0; i0 < k2; i0 += 8) {
+      double zz[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) zz[j] = (i0 + j < k2) ? ldz(zf, (int64_t)(i0 + j) * k1) : 0.0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (i0 + j < k2) {
+          double a, b;
+          log_pdf_derivs(v.lik, y, f + ws * zz[j], s, a, b);
+          sf += a;
+          ss += b;
+        }
+      }
     }
     sf /= (double)k2;
     ss /= (double)k2;
@@ -52,7 +61,7 @@ __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* _
     si_part += ss * ws;
   } else {
     double p = 0.0, p1 = 0.0, p2 = 0.0;
-    for (int i2 = 0; i2 < k2; ++i2) {
+    for (int i2 = 0; i2 < k2; ++i2) {                  // (the pdf terms are too large a body to unroll profitably)
       double fs = f + ws * ldz(zf, (int64_t)i2 * k1);
       double a, b, c;
       pdf_derivs(v.lik, y, fs, s, yfact, a, b, c);
