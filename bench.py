@@ -268,9 +268,9 @@ def main():
     ap.add_argument("--chunk-entries", type=int, default=16)
     ap.add_argument("--noise-slots", type=int, default=128)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
-    ap.add_argument("--table-mb", type=float, default=48.0, help="sample-table budget per call (L2-resident)")
+    ap.add_argument("--table-mb", type=float, default=96.0, help="sample-table budget per call (L2-resident)")
     ap.add_argument("--sweep-chunk", type=int, default=64, help="max entries of one (row, slot) chunk")
-    ap.add_argument("--sweep-streams", type=int, default=2, help="side streams the slot groups alternate between")
+    ap.add_argument("--sweep-streams", type=int, default=3, help="side streams the slot groups alternate between")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     c = CONFIGS[args.config]
@@ -364,37 +364,72 @@ def main():
             roofline["traffic_source"] = tr["source"]
 
     # ---- end-to-end arm: host buffers in, host result out, every step ----------------------------
+    # Every step's inputs (COO entries, values, the per-mode entry lists the sweep kernels read, the noise pool) are
+    # copied from pinned host memory and the posterior is copied back.  Two device input sets: the copy of step k+1
+    # runs on a copy stream while step k computes (all K copies are inside the timed region).
+    from ssvi_tf_b200.engine import NoisePool, _ptr
     pin = lambda x: x.cpu().pin_memory()                                      # noqa: E731
-    h_coords, h_vals = pin(eng.coords), pin(eng.vals)
-    # per-mode entry lists the sweep kernels read: the slot-major lists of the sample-table path where it applies
-    d_perm = [eng.plan_sweep(d).entry_ids if eng.sweep_supported else eng.perm[d] for d in range(N)]
-    h_perm = [pin(p) for p in d_perm]
+    plans = [model.sweep_plan(d)[0] for d in range(N)]
     nz = eng.noise
-    h_noise = [pin(x) for x in (nz.z_other, nz.z_own, nz.r_w, nz.z_f) if x is not None]
-    d_noise = [x for x in (nz.z_other, nz.z_own, nz.r_w, nz.z_f) if x is not None]
+    noise_names = [n for n in ("z_other", "z_own", "r_w", "z_f") if getattr(nz, n) is not None]
+    dev_sets = [dict(coords=eng.coords, vals=eng.vals, perm=[pl.entry_ids for pl in plans],
+                     noise=[getattr(nz, n) for n in noise_names])]
+    dev_sets.append(dict(coords=torch.empty_like(eng.coords), vals=torch.empty_like(eng.vals),
+                         perm=[torch.empty_like(pl.entry_ids) for pl in plans],
+                         noise=[torch.empty_like(x) for x in dev_sets[0]["noise"]]))
+    host = dict(coords=pin(eng.coords), vals=pin(eng.vals), perm=[pin(x) for x in dev_sets[0]["perm"]],
+                noise=[pin(x) for x in dev_sets[0]["noise"]])
     h_out = [torch.empty(p.shape, dtype=p.dtype).pin_memory() for p in eng.params]
-    h2d = (h_coords.numel() * 4 + h_vals.numel() * 8 + sum(p.numel() * 8 for p in h_perm)
-           + sum(x.numel() * x.element_size() for x in h_noise))
+    h2d = (host["coords"].numel() * 4 + host["vals"].numel() * 8 + sum(x.numel() * 8 for x in host["perm"])
+           + sum(x.numel() * x.element_size() for x in host["noise"]))
     d2h = sum(p.numel() * 8 for p in h_out)
+    main_stream = torch.cuda.current_stream()
+    copy_stream = torch.cuda.Stream()
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    free = [torch.cuda.Event(), torch.cuda.Event()]
 
-    def e2e_step():
-        eng.coords.copy_(h_coords, non_blocking=True)
-        eng.vals.copy_(h_vals, non_blocking=True)
-        for dp, hp in zip(d_perm, h_perm):
-            dp.copy_(hp, non_blocking=True)
-        for dn, hn in zip(d_noise, h_noise):
-            dn.copy_(hn, non_blocking=True)
-        one_step(model, flush)
-        for ho, p in zip(h_out, eng.params):
-            ho.copy_(p, non_blocking=True)
+    def stage(k):                       # H2D of step k's inputs into set k % 2
+        ds = dev_sets[k % 2]
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(free[k % 2])
+            ds["coords"].copy_(host["coords"], non_blocking=True)
+            ds["vals"].copy_(host["vals"], non_blocking=True)
+            for dp, hp in zip(ds["perm"], host["perm"]):
+                dp.copy_(hp, non_blocking=True)
+            for dn, hn in zip(ds["noise"], host["noise"]):
+                dn.copy_(hn, non_blocking=True)
+            ready[k % 2].record(copy_stream)
 
-    e2e_step()
+    def bind(k):                        # point the library at set k % 2 (host-side pointer swaps only)
+        ds = dev_sets[k % 2]
+        eng.coords, eng.vals = ds["coords"], ds["vals"]
+        eng._call(eng.lib.ssvi_bind_data, _ptr(eng.coords), _ptr(eng.vals), eng.nnz)
+        for pl, t_ in zip(plans, ds["perm"]):
+            pl.entry_ids = t_
+        kw = dict(zip(noise_names, ds["noise"]))
+        eng.set_noise(NoisePool(kw.get("z_other"), kw.get("z_own"), kw.get("r_w"), kw.get("z_f")))
+
+    def e2e_run(steps):
+        for e in free:
+            e.record(main_stream)
+        stage(0)
+        for k in range(steps):
+            if k + 1 < steps:
+                stage(k + 1)
+            main_stream.wait_event(ready[k % 2])
+            bind(k)
+            one_step(model, flush)
+            free[k % 2].record(main_stream)
+            for ho, p in zip(h_out, eng.params):
+                ho.copy_(p, non_blocking=True)
+
+    e2e_run(2)
     barrier()
     e0.record()
-    for _ in range(args.steps):
-        e2e_step()
+    e2e_run(args.steps)
     e1.record()
     barrier()
+    bind(0)
     t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -415,7 +450,7 @@ def main():
             "config": {"workload": c["desc"], "config_id": args.config, "nnz_train_per_gpu": nnz_train,
                        "units_per_step_per_gpu": units_per_step, "sweep": "full rows (scale=1), all modes",
                        "noise": "f32 pool, %d slots" % eng.noise.slots, "chunk_entries": args.chunk_entries,
-                       "path": ("sample-table sweep (slot-major), %d slots/call" % eng.plan_sweep(0).groups[0][1])
+                       "path": ("slot-major sweep kernels, %d slots/call" % model.sweep_plan(0)[0].groups[0][1])
                        if eng.sweep_supported else "direct",
                        "l2": l2_note,
                        "parallelism": "entries sharded x%d, all-reduce of row accumulators" % world},

@@ -221,16 +221,22 @@ class SSVI_TF(object):
         if self.noise_added:
             self.w_changes = abs(self.w_sigma - w_before)                            # :209
 
-    def sweep(self, dim):
-        """One Jacobi sweep over mode `dim`: every observed entry of every row (scale = 1)."""
+    def sweep_plan(self, dim):
+        """(plan, n_obs) of a full sweep over mode `dim`: every observed entry of every row (scale = 1).
+        SSVI_TF_d + full covariance and every diagonal-covariance model take the slot-major sweep kernels; the rest
+        the direct kernels."""
         eng = self.engine
         rp = eng.rowptr_h[dim]
         rows = np.arange(self.dims[dim], dtype=np.int64)
         off, n_obs = self._shard_info(dim, rows, rp[1:] - rp[:-1])
         if eng.noise is None:
             self.fresh_noise()
-        # SSVI_TF_d + full covariance: the slot-major sample-table kernels; otherwise the direct kernels
         plan = eng.plan_sweep(dim, off) if eng.sweep_supported else eng.plan_full(dim, None, off)
+        return plan, n_obs
+
+    def sweep(self, dim):
+        """One Jacobi sweep over mode `dim`."""
+        plan, n_obs = self.sweep_plan(dim)
         self._run_plan(plan, n_obs)
 
     def update_hyper_parameter(self, dim):

@@ -60,8 +60,9 @@ __device__ __forceinline__ PoissonTerms poisson_terms(double f) {
 
 // poisson.py:19-27  pdf(y, m) = max(A^y / (1+e^m) / y!, 1e-8), A = poisson_link(m)
 __device__ __forceinline__ double poisson_pdf_ref(double y, double m, double yfact) {
-  double A = poisson_link_ref(m);
-  double r = ipow_ref(A, y) / (1.0 + exp(m)) / yfact;
+  const double E1 = 1.0 + exp(m);                     // one exponential for the link and the denominator
+  const double A = fmax(nan_to_num(log(E1)), 1e-8);
+  double r = ipow_ref(A, y) / E1 / yfact;
   return fmax(r, 1e-8);
 }
 
