@@ -7,7 +7,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libssvi_b200.so")
+LIB_PATH = os.environ.get("SSVI_B200_LIB", os.path.join(_HERE, "libssvi_b200.so"))   # override: kernel A/B builds
 
 MAX_ORDER = 8
 MAX_RANK = 64

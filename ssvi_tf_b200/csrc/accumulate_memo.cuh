@@ -106,9 +106,9 @@ __host__ __device__ inline int memo_region_bytes(int NT, int D) {
   if (red > a) a = red;
   return a;
 }
-__host__ __device__ inline int memo_cta_smem(int NT, int D) {
-  return memo_region_bytes(NT, D) + 4 * (NT * (NT + 1) / 2) * 64 * 8;
-}
+// + per warp: G [NP][32] double2, di accumulator [NT][32] double2, f partials [8][32] double2
+__host__ __device__ inline int memo_warp_bytes(int NT) { return ((NT * (NT + 1) / 2) + NT + SSVI_MEMO_KT) * 512; }
+__host__ __device__ inline int memo_cta_smem(int NT, int D) { return memo_region_bytes(NT, D) + 4 * memo_warp_bytes(NT); }
 
 __device__ __forceinline__ double2 ld_tab(const double2* p) { return __ldcg(p); }
 
@@ -118,7 +118,7 @@ __device__ __forceinline__ double2 ld_tab(const double2* p) { return __ldcg(p); 
 //         otherwise the row sums are accumulated with DADDs.
 // ---------------------------------------------------------------------------------------------------------------------
 template <int NT, int NOTH, bool ONES>
-__global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
+__global__ void __launch_bounds__(128, (NT <= 3 ? 4 : 3)) accumulate_memo_kernel(
     DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
     const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
     const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
@@ -141,7 +141,9 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
   double* zs = S + v.srow_len;
   double2* Us = reinterpret_cast<double2*>(smem_raw);
   double* red = reinterpret_cast<double*>(smem_raw);
-  double2* Gs = reinterpret_cast<double2*>(smem_raw + region) + warp * (NP * 32);
+  double2* Gs = reinterpret_cast<double2*>(smem_raw + region + warp * memo_warp_bytes(NT));   // [NP][32]
+  double2* Ga = Gs + NP * 32;                                                                  // [NT][32]
+  double2* FP = Ga + NT * 32;                                                                  // [KT][32], swizzled
 
   // ---- this warp's entries (w, w+4, ...): value and table records, fetched lane-parallel before the prologue so the
   //      index -> coordinate -> table chain of loads overlaps the own-row sampling ------------------------------------
@@ -181,7 +183,7 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
     }
   }
 #pragma unroll
-  for (int p = 0; p < NP; ++p) Gs[p * 32 + lane] = make_double2(0.0, 0.0);
+  for (int p = 0; p < NP + NT; ++p) Gs[p * 32 + lane] = make_double2(0.0, 0.0);   // G and the di accumulator
   __syncthreads();
   double uc[NT][2][2];                                  // warp w: k-tiles t = w and w + 4
 #pragma unroll
@@ -198,9 +200,6 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
   __syncthreads();
 
   // ---- main loop -----------------------------------------------------------------------------------------------------
-  double2 ga[NT];                                       // ONES: sum_b aw_b * (row D of V V^T) ; else sum_b aw_b * row sums
-#pragma unroll
-  for (int i = 0; i < NT; ++i) ga[i] = make_double2(0.0, 0.0);
   const double inv_k1 = 1.0 / (double)(8 * KT);
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
@@ -237,7 +236,6 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
       double acc[NP][2];
 #pragma unroll
       for (int p = 0; p < NP; ++p) acc[p][0] = acc[p][1] = 0.0;
-      double fp[KT][2];
       double rs[NT];
 #pragma unroll
       for (int i = 0; i < NT; ++i) rs[i] = 0.0;
@@ -250,7 +248,7 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
 #pragma unroll
           for (int i = 0; i < NT; ++i) nxt[jj][i] = ld_tab(p + (i * KT) * 32);
         }
-        double2 vv[NT];
+        double2 vv[NT], fpt;
 #pragma unroll
         for (int i = 0; i < NT; ++i) {
           vv[i] = cur[0][i];
@@ -261,14 +259,15 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
           }
           const double2 u = Us[(i * KT + t) * 32 + lane];
           if (i == 0) {
-            fp[t][0] = u.x * vv[i].x;
-            fp[t][1] = u.y * vv[i].y;
+            fpt.x = u.x * vv[i].x;
+            fpt.y = u.y * vv[i].y;
           } else {
-            fp[t][0] += u.x * vv[i].x;
-            fp[t][1] += u.y * vv[i].y;
+            fpt.x += u.x * vv[i].x;
+            fpt.y += u.y * vv[i].y;
           }
           if (!ONES) rs[i] += vv[i].x + vv[i].y;
         }
+        FP[t * 32 + (lane ^ (t << 2))] = fpt;           // row-group index XOR-swizzled: the read below is conflict-free
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           int p = 0;
@@ -285,30 +284,22 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
 #pragma unroll
           for (int i = 0; i < NT; ++i) cur[jj][i] = nxt[jj][i];
       }
-      // ---- f_k = u_k . v_k: transposing reduction over the 8 row groups; lane (g, q) ends with k = 8g + 2q + {0,1} ----
-      double r1[4][2], r2[2][2], f[2];
+      // ---- f_k = u_k . v_k: sum over the 8 row groups through shared memory; lane (g, q) ends with the samples
+      //      k = 8g + 2q + {0,1}, i.e. it reads the partials of k-tile t = g held by the lanes (g', q), g' = 0..7 -----------
+      double f[2];
+      __syncwarp();
       {
-        const bool h2 = (g & 4) != 0, h1 = (g & 2) != 0, h0 = (g & 1) != 0;
+        double2 a = FP[g * 32 + (((0 ^ g) << 2) | q)];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-#pragma unroll
-          for (int s = 0; s < 2; ++s) {
-            const double give = h2 ? fp[j][s] : fp[j + 4][s], keep = h2 ? fp[j + 4][s] : fp[j][s];
-            r1[j][s] = keep + __shfl_xor_sync(0xffffffffu, give, 16);
-          }
-#pragma unroll
-        for (int j = 0; j < 2; ++j)
-#pragma unroll
-          for (int s = 0; s < 2; ++s) {
-            const double give = h1 ? r1[j][s] : r1[j + 2][s], keep = h1 ? r1[j + 2][s] : r1[j][s];
-            r2[j][s] = keep + __shfl_xor_sync(0xffffffffu, give, 8);
-          }
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-          const double give = h0 ? r2[0][s] : r2[1][s], keep = h0 ? r2[1][s] : r2[0][s];
-          f[s] = keep + __shfl_xor_sync(0xffffffffu, give, 4);
+        for (int gg = 1; gg < 8; ++gg) {
+          const double2 b = FP[g * 32 + (((gg ^ g) << 2) | q)];
+          a.x += b.x;
+          a.y += b.y;
         }
+        f[0] = a.x;
+        f[1] = a.y;
       }
+      __syncwarp();
       // ---- SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1, then broadcast -------------------------------------
       double sum_a = 0.0, sum_d = 0.0;
 #pragma unroll
@@ -322,13 +313,15 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
       sum_d = warp_sum(sum_d) * inv_k1;
       const double aw = sum_a * inv_k1, dw = 0.5 * sum_d * inv_k1;
 #pragma unroll
-      for (int i = 0; i < NT; ++i) {
+      for (int i = 0; i < NT; ++i) {                    // ONES: sum_b aw_b * (row D of V V^T); else sum_b aw_b * row sums
+        double2 o = Ga[i * 32 + lane];
         if (ONES) {
-          ga[i].x += aw * acc[PL + i][0];
-          ga[i].y += aw * acc[PL + i][1];
+          o.x += aw * acc[PL + i][0];
+          o.y += aw * acc[PL + i][1];
         } else {
-          ga[i].x += aw * rs[i];
+          o.x += aw * rs[i];
         }
+        Ga[i * 32 + lane] = o;
       }
 #pragma unroll
       for (int p = 0; p < NP; ++p) {
@@ -346,12 +339,12 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
     if (g == (D & 7)) {
 #pragma unroll
       for (int i = 0; i < NT; ++i)
-        *reinterpret_cast<double2*>(&red[warp * (NT * 8) + 8 * i + 2 * q]) = ga[i];
+        *reinterpret_cast<double2*>(&red[warp * (NT * 8) + 8 * i + 2 * q]) = Ga[i * 32 + lane];
     }
   } else {
 #pragma unroll
     for (int i = 0; i < NT; ++i) {
-      double x = ga[i].x;
+      double x = Ga[i * 32 + lane].x;
       x += __shfl_xor_sync(0xffffffffu, x, 1);
       x += __shfl_xor_sync(0xffffffffu, x, 2);
       if (q == 0) red[warp * (NT * 8) + 8 * i + g] = x;
@@ -362,9 +355,10 @@ __global__ void __launch_bounds__(128, 3) accumulate_memo_kernel(
   for (int n = tid; n < D; n += 128)
     out[n] = ((red[n] + red[NT * 8 + n]) + red[2 * NT * 8 + n]) + red[3 * NT * 8 + n];
   const double2* Gall = reinterpret_cast<const double2*>(smem_raw + region);
+  constexpr int WS = ((NT * (NT + 1) / 2) + NT + SSVI_MEMO_KT) * 32;       // double2 per warp block (memo_warp_bytes)
   for (int idx = tid; idx < NP * 32; idx += 128) {
     const int p = idx >> 5, l = idx & 31;
-    const double2 a0 = Gall[idx], a1 = Gall[NP * 32 + idx], a2 = Gall[2 * NP * 32 + idx], a3 = Gall[3 * NP * 32 + idx];
+    const double2 a0 = Gall[idx], a1 = Gall[WS + idx], a2 = Gall[2 * WS + idx], a3 = Gall[3 * WS + idx];
     const double x0 = ((a0.x + a1.x) + a2.x) + a3.x, x1 = ((a0.y + a1.y) + a2.y) + a3.y;
     int i1 = 0;                                         // unrank p -> (i1 >= i2)
     while ((i1 + 1) * (i1 + 2) / 2 <= p) ++i1;
