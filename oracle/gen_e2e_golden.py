@@ -26,10 +26,12 @@ OUT_DIR = os.path.join(ROOT, "tests", "golden_e2e")
 
 CASES = [
     # name, datatype, model, diag, dims, D, k1, k2, batch, iterations, seeds
-    ("real_d_full", "real", "d", False, [20, 18, 16], 4, 16, 16, 32, 1200, 4),
-    ("binary_d_full", "binary", "d", False, [20, 18, 16], 4, 16, 16, 32, 1200, 4),
-    ("real_simple_diag", "real", "simple", True, [20, 18, 16], 4, 16, 8, 32, 1200, 4),
-    ("count_robust_full", "count", "robust", False, [14, 12, 10], 3, 8, 8, 24, 600, 4),
+    # every row fits in one minibatch (no subsampling) and the loop runs ~70 sweeps, so the seed-to-seed spread of the
+    # final metric is a few per cent instead of tens of per cent
+    ("real_d_full", "real", "d", False, [12, 10, 8], 3, 32, 8, 128, 800, 8),
+    ("binary_d_full", "binary", "d", False, [12, 10, 8], 3, 32, 8, 128, 800, 8),
+    ("real_simple_diag", "real", "simple", True, [12, 10, 8], 3, 32, 8, 128, 800, 8),
+    ("count_robust_full", "count", "robust", False, [12, 10, 8], 3, 16, 8, 128, 400, 8),
 ]
 
 

@@ -4,8 +4,9 @@ error must stay within 1 % of the reference").
 tests/golden_e2e/*.npz hold small synthetic tensors and the test RMSE / error rate the UNMODIFIED reference reached on
 them after its own factorize loop, for several NumPy seeds (oracle/gen_e2e_golden.py).  Here the B200 build's
 factorize runs the same schedule (one row per mode per iteration, SSVI_TF_interface.py:117-133) on the same data with
-the same hyper-parameters.  Both sides are stochastic (different noise streams), so the bar is 1 % of the reference's
-mean plus three of the reference's own seed-to-seed standard deviations."""
+the same hyper-parameters.  Both sides are stochastic (different noise streams; the reference's own seed-to-seed
+spread on these problems is several per cent), so the bar is: means over the seeds agree within 1 % of the reference
+plus three standard errors of the difference."""
 import glob
 import os
 
@@ -41,7 +42,7 @@ def test_factorize_metrics_within_one_percent_of_reference(name):
     cls = {"d": pkg.SSVI_TF_d, "simple": pkg.SSVI_TF_simple, "robust": pkg.SSVI_TF_robust}[str(z["model"])]
     mean0 = np.ones(D) if t.datatype == "real" else np.zeros(D)
     rs, er = [], []
-    for seed in (319, 320, 321):
+    for seed in range(319, 325):
         np.random.seed(seed)
         m = cls(t, D, diag=bool(z["diag"]), mean0=mean0, cov0=np.eye(D) * 0.1, k1=k1, k2=k2, batch_size=B,
                 randstart=True, noise_dtype=torch.float64, noise_seed=seed)
@@ -49,9 +50,14 @@ def test_factorize_metrics_within_one_percent_of_reference(name):
         r, e = m.evaluate_test_error()
         rs.append(r)
         er.append(e)
+    rs, er = np.array(rs), np.array(er)
     ref_r, ref_e = z["ref_rsme"], z["ref_err"]
-    tol_r = 0.01 * np.median(ref_r) + 3.0 * max(ref_r.std(), 1e-3 * ref_r.mean())
-    assert abs(np.median(rs) - np.median(ref_r)) <= tol_r, (name, rs, list(ref_r))
-    if t.datatype == "binary":                         # error rate: 1 % absolute
-        tol_e = 0.01 + 3.0 * ref_e.std()
-        assert abs(np.median(er) - np.median(ref_e)) <= tol_e, (name, er, list(ref_e))
+
+    def close(ours, ref, floor):
+        # 1 % of the reference + three standard errors of the difference of the two sample means
+        se = np.sqrt(ref.var() / len(ref) + ours.var() / len(ours))
+        return abs(ours.mean() - ref.mean()) <= 0.01 * max(abs(ref.mean()), floor) + 3.0 * se
+
+    assert close(rs, ref_r, 0.0), (name, list(rs), list(ref_r))
+    if t.datatype == "binary":
+        assert close(er, ref_e, 1.0), (name, list(er), list(ref_e))       # error rate: 1 % absolute
