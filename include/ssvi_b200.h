@@ -159,7 +159,7 @@ int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t*
                     const int64_t* entry_ids, const int64_t* rows, const double* w_state,
                     double* partial_out, void* stream);
 
-/* ---- The sample-table path for full sweeps (slot-major; SSVI_TF_d, full covariance, rank <= 32, k1 == 64 -- the
+/* ---- The sample-table path for full sweeps (slot-major; full covariance, rank <= 32, k1 == 64 -- the
  * reference's default, SSVI_TF_interface.py:23 -- and order <= 4).  Same mathematics and the same outputs as ssvi_accumulate, organised so that the sample
  * X(j, s) = m_j + L_j Z(s, jj) of sample_vjs_batch (SSVI_TF_interface.py:732-750) is evaluated once per (other-mode
  * row j, noise slot s) instead of once per (entry, mode): with P pool slots a sweep asks for each pair nnz / (n_j P)
@@ -175,13 +175,21 @@ int ssvi_accumulate(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t*
  * Diagonal covariance (every model, rank <= 64, k1 % 16 == 0, k1 <= 64, order <= 4) takes the same slot-major chunk
  * tables: samples are element-wise there, so nothing is tabulated (ssvi_sweep_table_bytes == 0, table_ws may be NULL,
  * any slot range in one call); each CTA stages its chunk's noise blocks in shared memory once instead.
- * w_state as for ssvi_accumulate (simple / robust; may be NULL for SSVI_TF_d). */
+ * w_state as for ssvi_accumulate (simple / robust; may be NULL for SSVI_TF_d).
+ *
+ * SSVI_TF_simple / SSVI_TF_robust with a full covariance run a slot group in three passes (predictive means F ->
+ * per-(entry, sample) likelihood weights at full occupancy -> contraction) and need a second workspace of
+ * ssvi_sweep_work_bytes(h, n_entries) bytes, where the call's chunks cover the n_entries consecutive positions
+ * [entry_lo, entry_lo + n_entries) of entry_ids (true by construction for slot-major chunk tables).  For SSVI_TF_d and
+ * for diagonal covariances work_ws may be NULL and entry_lo / n_entries are ignored. */
 int ssvi_sweep_supported(const SsviHandle* h);                                   /* 1 if this path applies to h's config */
 int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int32_t n_slots);
+int64_t ssvi_sweep_work_bytes(const SsviHandle* h, int64_t n_entries);           /* 0 unless simple/robust + full cov */
 int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo, int32_t n_slots, int64_t n_chunks,
                           const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
                           const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
                           const int64_t* rows, const double* w_state, void* table_ws, int64_t table_ws_bytes,
+                          void* work_ws, int64_t work_ws_bytes, int64_t entry_lo, int64_t n_entries,
                           double* partial_out, void* stream);
 
 /* Deterministic in-order sum of the chunk records of each row:

@@ -52,7 +52,8 @@ SIGNATURES = {
     "ssvi_accumulate": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "ssvi_sweep_supported": (ctypes.c_int, [_P]),
     "ssvi_sweep_table_bytes": (_I64, [_P, _I32, _I32]),
-    "ssvi_sweep_accumulate": (ctypes.c_int, [_P, _I32, _I32, _I32, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P]),
+    "ssvi_sweep_accumulate": (ctypes.c_int, [_P, _I32, _I32, _I32, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _I64, _I64, _I64, _P, _P]),
+    "ssvi_sweep_work_bytes": (_I64, [_P, _I64]),
     "ssvi_reduce_chunks": (ctypes.c_int, [_P, _I64, _P, _P, _P, _P]),
     "ssvi_row_update": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _I32, _I32, _P, _P]),
     "ssvi_sigma_update": (ctypes.c_int, [_P, _I64, _P, _P, _P, _P]),

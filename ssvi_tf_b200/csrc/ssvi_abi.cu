@@ -3,7 +3,7 @@
 #include <string.h>
 #include <new>
 
-#include "accumulate_memo.cuh"
+#include "accumulate_memo2.cuh"
 #include "accumulate_diag.cuh"
 #include "row_update.cuh"
 
@@ -277,8 +277,8 @@ static bool sweep_diag_ok(const SsviConfig& c, int max_smem) {
          diag_cta_smem(c.order, c.rank, c.k1) <= (size_t)max_smem;
 }
 static bool sweep_full_ok(const SsviConfig& c) {
-  return c.cov_kind == SSVI_COV_FULL && c.model == SSVI_MODEL_D && c.rank <= 32 && c.k1 == 8 * SSVI_MEMO_KT &&
-         c.order >= 2 && c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
+  return c.cov_kind == SSVI_COV_FULL && c.rank <= 32 && c.k1 == 8 * SSVI_MEMO_KT && c.order >= 2 &&
+         c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
 }
 static bool sweep_ok(const SsviHandle* h) { return sweep_full_ok(h->cfg) || sweep_diag_ok(h->cfg, h->max_smem_optin); }
 
@@ -292,11 +292,16 @@ extern "C" int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int3
   return recs * memo_rec_len(h->cfg.rank, h->cfg.k1) * (int64_t)sizeof(double);
 }
 
+extern "C" int64_t ssvi_sweep_work_bytes(const SsviHandle* h, int64_t n_entries) {
+  if (!h || n_entries < 0 || !sweep_full_ok(h->cfg) || h->cfg.model == SSVI_MODEL_D) return 0;
+  return memo_work_bytes(n_entries);
+}
+
 template <int NT, typename ZT>
 static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int64_t n_chunks, const int32_t* chunk_row,
                         const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
                         const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, double* partial_out,
-                        cudaStream_t st) {
+                        const double* w_state, const MemoWork& wk, cudaStream_t st) {
   {
     const int wpb = 8;
     const size_t smem = (size_t)memo_stage_bytes(v.D, v.k1, (int)sizeof(ZT)) * wpb;
@@ -307,8 +312,33 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
     CUDA_TRY(h, cudaGetLastError());
   }
   if (n_chunks == 0) return SSVI_OK;
-  const size_t smem = (size_t)memo_cta_smem(NT, v.D);
   const int z_f32 = sizeof(ZT) == 4;
+  if (h->cfg.model != SSVI_MODEL_D) {                   // simple / robust: F pass, weights, contraction pass
+    const size_t smf = (size_t)memo_f_smem(NT, v.D), smc = (size_t)memo_c_smem(NT, v.D);
+#define SSVI_MEMO2_LAUNCH(NOTH)                                                                                    \
+    do {                                                                                                           \
+      auto kf = memo_f_kernel<NT, NOTH>;                                                                           \
+      auto kc = memo_c_kernel<NT, NOTH>;                                                                           \
+      CUDA_TRY(h, cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smf));                \
+      CUDA_TRY(h, cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));                \
+      kf<<<(unsigned)n_chunks, 128, smf, st>>>(v, mv, wk, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, \
+                                               entry_ids, rows, h->z_own, z_f32);                                  \
+      memo_weights_kernel<ZT><<<(unsigned)((wk.n * 64 + 255) / 256), 256, 0, st>>>(v, wk, w_state,                 \
+                                                                                   (const ZT*)h->r_w,              \
+                                                                                   (const ZT*)h->z_f);             \
+      kc<<<(unsigned)n_chunks, 128, smc, st>>>(v, mv, wk, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, \
+                                               chunk_out, entry_ids, partial_out);                                 \
+    } while (0)
+    switch (mv.n_oth) {
+      case 1: SSVI_MEMO2_LAUNCH(1); break;
+      case 2: SSVI_MEMO2_LAUNCH(2); break;
+      default: SSVI_MEMO2_LAUNCH(3); break;
+    }
+#undef SSVI_MEMO2_LAUNCH
+    CUDA_TRY(h, cudaGetLastError());
+    return SSVI_OK;
+  }
+  const size_t smem = (size_t)memo_cta_smem(NT, v.D);
 #define SSVI_MEMO_LAUNCH(NOTH, ONES)                                                                               \
   do {                                                                                                             \
     auto kern = accumulate_memo_kernel<NT, NOTH, ONES>;                                                            \
@@ -373,7 +403,8 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
                                      const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
                                      const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
                                      const int64_t* rows, const double* w_state, void* table_ws,
-                                     int64_t table_ws_bytes, double* partial_out, void* stream) {
+                                     int64_t table_ws_bytes, void* work_ws, int64_t work_ws_bytes, int64_t entry_lo,
+                                     int64_t n_entries, double* partial_out, void* stream) {
   if (!h) return SSVI_E_INVALID;
   if (!h->data_bound || !h->state_bound || !h->noise_bound) return fail(h, SSVI_E_STATE, "sweep_accumulate: bind data, state and noise first%s");
   if (!sweep_ok(h)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: configuration not supported by the sample-table path (see ssvi_sweep_supported)%s");
@@ -407,8 +438,23 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
   }
   mv.rec_base[jj] = base;
   if (base >= ((int64_t)1 << 31)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: too many table records; use fewer slots per call%s");
+  MemoWork wk;
+  memset(&wk, 0, sizeof(wk));
+  if (h->cfg.model != SSVI_MODEL_D && n_chunks > 0) {
+    if (!w_state) return fail(h, SSVI_E_INVALID, "sweep_accumulate: w_state required for simple/robust%s");
+    if (n_entries < 0 || entry_lo < 0 || !work_ws || work_ws_bytes < memo_work_bytes(n_entries))
+      return fail(h, SSVI_E_INVALID, "sweep_accumulate: work workspace missing or too small (ssvi_sweep_work_bytes)%s");
+    unsigned char* b = (unsigned char*)work_ws;
+    wk.F = (double*)b;
+    wk.W = (double2*)(b + n_entries * 512);
+    wk.SI = (double*)(b + n_entries * 1536);
+    wk.Y = (double*)(b + n_entries * 2048);
+    wk.SL = (int32_t*)(b + n_entries * 2056);
+    wk.e_lo = entry_lo;
+    wk.n = n_entries;
+  }
   cudaStream_t st = (cudaStream_t)stream;
-#define SSVI_SWEEP_ARGS h, v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, partial_out, st
+#define SSVI_SWEEP_ARGS h, v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, partial_out, w_state, wk, st
   const int nt = (v.D + 7) / 8;
   if (h->cfg.noise_dtype == SSVI_NOISE_F32) {
     switch (nt) {

@@ -139,6 +139,7 @@ class SlotSweepPlan(object):
         self.n_entries = int(batch_sizes.sum())
         self.groups = groups
         self.table_bytes = int(table_bytes)
+        self.chunk_start_h = None           # host int64 [n_chunks + 1]: first entry position of every chunk (+ total)
 
 
 class Engine(object):
@@ -428,6 +429,7 @@ class Engine(object):
                              t(chunk_row, np.int32), t(chunk_start, np.int64), t(chunk_len, np.int32),
                              t(chunk_slot, np.int32), t(chunk_out, np.int64), t(row_chunk_ptr, np.int64), lens,
                              groups, per_slot * gs)
+        plan.chunk_start_h = np.concatenate([chunk_start, [int(pair_start[-1])]]).astype(np.int64)
         self._sweep_plans[key] = plan
         return plan
 
@@ -436,6 +438,11 @@ class Engine(object):
         group's launch overlaps the next group's sampling and ramp-up; joined back into the caller's stream."""
         ns = max(1, min(self.sweep_streams, len(plan.groups)))
         tabs = [self._buf("sweep_table%d" % i, (plan.table_bytes + 7) // 8) for i in range(ns)]
+        # simple / robust + full covariance: per-group work buffers (F, weights, si) of the three-pass path
+        e_pos = plan.chunk_start_h
+        max_n = max([int(e_pos[c1] - e_pos[c0]) for (_, _, c0, c1) in plan.groups] + [0])
+        work_bytes = int(self.lib.ssvi_sweep_work_bytes(self.h, max_n))
+        works = [self._buf("sweep_work%d" % i, (work_bytes + 7) // 8) for i in range(ns)] if work_bytes else None
 
         def at(tensor, i):
             return ctypes.c_void_p(tensor.data_ptr() + i * tensor.element_size())
@@ -453,7 +460,9 @@ class Engine(object):
             self._call(self.lib.ssvi_sweep_accumulate, plan.dim, s0, nsl, c1 - c0, at(plan.chunk_row, c0),
                        at(plan.chunk_start, c0), at(plan.chunk_len, c0), at(plan.chunk_slot, c0),
                        at(plan.chunk_out, c0), _ptr(plan.entry_ids), _ptr(plan.rows), _ptr(self.w_state), _ptr(tab),
-                       tab.numel() * 8, _ptr(partial), stream)
+                       tab.numel() * 8, _ptr(works[k % ns]) if works else ctypes.c_void_p(0),
+                       works[k % ns].numel() * 8 if works else 0, int(e_pos[c0]), int(e_pos[c1] - e_pos[c0]),
+                       _ptr(partial), stream)
             self.launches += (1 if self.diag else 2) if c1 > c0 else (0 if self.diag else 1)
         if ns > 1:
             for s_ in self._side_streams[:ns]:

@@ -179,23 +179,28 @@ def test_mma_path_matches_oracle_and_generic(D, k1, model, lik):
     np.testing.assert_array_equal(Di, np.transpose(Di, (0, 2, 1)))
 
 
-@pytest.mark.parametrize("dims,D,k1,lik,P,W,offs", [
-    ([6, 5, 4], 20, 64, "bernoulli", 4, 64, False),      # BASELINE config 2's kernel instance (NT=3, two other modes)
-    ([6, 5, 4], 12, 64, "normal", 3, 2, True),           # segments of 2 entries, shifted slots (multi-GPU shard)
-    ([5, 4, 4], 32, 64, "normal", 5, 3, False),          # NT=4, D % 8 == 0 (config 5): row sums by DADD
-    ([5, 4, 4], 30, 64, "poisson", 4, 64, True),
-    ([5, 4, 4], 16, 64, "bernoulli", 2, 5, False),       # D % 8 == 0, NT=2
-    ([7, 9], 7, 64, "bernoulli", 2, 4, False),           # matrix: one other mode
-    ([4, 3, 3, 3], 10, 64, "normal", 3, 64, False),      # 4-way: three other modes (config 1's NT=2)
-    ([40, 3, 3], 20, 64, "normal", 1, 200, False),       # one slot, chunks longer than 128 entries
+@pytest.mark.parametrize("dims,D,k1,lik,P,W,offs,model", [
+    ([6, 5, 4], 20, 64, "bernoulli", 4, 64, False, "d"),     # BASELINE config 2's kernel instance (NT=3, two other modes)
+    ([6, 5, 4], 12, 64, "normal", 3, 2, True, "d"),          # segments of 2 entries, shifted slots (multi-GPU shard)
+    ([5, 4, 4], 32, 64, "normal", 5, 3, False, "d"),         # NT=4, D % 8 == 0 (config 5): row sums by DADD
+    ([5, 4, 4], 30, 64, "poisson", 4, 64, True, "d"),
+    ([5, 4, 4], 16, 64, "bernoulli", 2, 5, False, "d"),      # D % 8 == 0, NT=2
+    ([7, 9], 7, 64, "bernoulli", 2, 4, False, "d"),          # matrix: one other mode
+    ([4, 3, 3, 3], 10, 64, "normal", 3, 64, False, "d"),     # 4-way: three other modes (config 1's NT=2)
+    ([40, 3, 3], 20, 64, "normal", 1, 200, False, "d"),      # one slot, chunks longer than 128 entries
+    ([5, 4, 4], 30, 64, "poisson", 4, 64, False, "robust"),  # BASELINE config 3's kernel instances (three-pass path)
+    ([6, 5, 4], 20, 64, "bernoulli", 3, 3, True, "robust"),
+    ([6, 5, 4], 12, 64, "normal", 2, 64, False, "simple"),
+    ([4, 3, 3, 3], 9, 64, "poisson", 3, 5, True, "simple"),
+    ([7, 9], 32, 64, "normal", 2, 64, False, "robust"),
 ])
-def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W, offs):
+def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W, offs, model):
     """Full sweep through the slot-major sample-table kernels == the direct DMMA kernel == the generic CUDA-core
     kernel (same accumulators to summation order) == the oracle's rows_step on the same pooled noise."""
     from ssvi_tf_b200.engine import Engine, NoisePool
     rng = np.random.default_rng(D * 1000 + k1 + P)
     N = len(dims)
-    cfg = so.make_config("d", lik, D, diag=False, k1=k1, k2=4, batch_size=10 ** 9)
+    cfg = so.make_config(model, lik, D, diag=False, k1=k1, k2=4, batch_size=10 ** 9)
     nnz = int(0.8 * np.prod(dims))
     coords, vals = random_problem(rng, lik, dims, nnz)
     st0 = random_state(rng, cfg, dims)
