@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
         G1 = fma(dw, sq1, G1);
       } else {
         // simple / robust: per-sample weights (second-layer k2 loop), then pass 2 re-evaluates v
-        const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? factorial_ref(y) : 1.0;
+        const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? 1.0 / factorial_ref(y) : 1.0;
         __syncwarp();
 #pragma unroll
         for (int a = 0; a < 2; ++a) {

@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(128) accumulate_generic_kernel(
     const int64_t eid = entry_ids[start + e];
     const int slot = (slot0 + e) % v.pool_slots;
     const double y = v.vals[eid];
-    const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? factorial_ref(y) : 1.0;
+    const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? 1.0 / factorial_ref(y) : 1.0;
     // ---- stage 1+2: other modes ------------------------------------------------------------
     int jj = 0;
     for (int d = 0; d < N; ++d) {

@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(256) memo_weights_kernel(DevView v, MemoWork w
   const int k = (int)(t & 63);
   const double y = wk.Y[loc];
   const int slot = wk.SL[loc];
-  const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? factorial_ref(y) : 1.0;
+  const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? 1.0 / factorial_ref(y) : 1.0;
   double aw, dw, si = 0.0;
   bool bad = false;
   likelihood_weights<ZT>(v, r_w, z_f, slot, k, true, y, yfact, wk.F[t], w_state[0], aw, dw, si, bad);

@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(256) accumulate_mma_kernel(
         if (jj < N - 1) col_n[jj] = v.coords[eid_n * N + od[jj]];
     }
     const double yfact =
-        (SECOND && v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? factorial_ref(y) : 1.0;
+        (SECOND && v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? 1.0 / factorial_ref(y) : 1.0;
     double vv[NT][8][2];
     double fp[8][2];
 #pragma unroll

@@ -58,14 +58,6 @@ __device__ __forceinline__ PoissonTerms poisson_terms(double f) {
   return t;
 }
 
-// poisson.py:19-27  pdf(y, m) = max(A^y / (1+e^m) / y!, 1e-8), A = poisson_link(m)
-__device__ __forceinline__ double poisson_pdf_ref(double y, double m, double yfact) {
-  const double E1 = 1.0 + exp(m);                     // one exponential for the link and the denominator
-  const double A = fmax(nan_to_num(log(E1)), 1e-8);
-  double r = ipow_ref(A, y) / E1 / yfact;
-  return fmax(r, 1e-8);
-}
-
 // d / simple models: first and second derivative of log p(y|f) w.r.t. f
 //   normal.py:32-36, bernoulli.py:40-51, poisson.py:70-87
 __device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, double s, double& fst,
@@ -97,6 +89,7 @@ __device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, doub
 
 // robust model: pdf and its first / second derivative w.r.t. f
 //   normal.py:16-27, bernoulli.py:16-36, poisson.py:19-57
+// (yfact: 1 / y! for the Poisson likelihood, unused otherwise)
 __device__ __forceinline__ void pdf_derivs(int lik, double y, double f, double s, double yfact, double& p,
                                            double& p1, double& p2) {
   if (lik == SSVI_LIK_NORMAL) {
@@ -110,13 +103,21 @@ __device__ __forceinline__ void pdf_derivs(int lik, double y, double f, double s
     p1 = (y * sg) * (1.0 - sg);
     p2 = sg * (1.0 - sg) * (1.0 - 2.0 * sg);
   } else {
-    const PoissonTerms pt = poisson_terms(f);
-    const double A = pt.A, sg = pt.sg;
-    double t = y / A - 1.0;
-    p = fmax(ipow_ref(A, y) / pt.E1 / yfact, 1e-8);   // pdf(y, f), poisson.py:19-27
+    // Divisions are the expensive part here (about 25 instructions each in fp64): one reciprocal each of 1+e^f, A and
+    // 1+e^A serves every quotient of poisson.py:19-57; yfact arrives as 1/y! (a few ulp from the reference's order).
+    const double E = exp(f);
+    const double E1 = 1.0 + E, rE1 = 1.0 / E1;
+    const double A = fmax(nan_to_num(log(E1)), 1e-8), rA = 1.0 / A;
+    double sg = (E > 1e300) ? 1.0 : E * rE1;
+    if (isnan(f)) sg = 0.0;
+    const double yA = y * rA;
+    double t = yA - 1.0;
+    p = fmax(ipow_ref(A, y) * rE1 * yfact, 1e-8);     // pdf(y, f)
     p1 = p * (sg * t);
-    double pl = poisson_pdf_ref(y, A, yfact);         // Q7: pdf(y, poisson_link(m))
-    double temp = -(y / (A * A)) * (sg * sg) + t * (sg * (1.0 - sg));
+    const double EA1 = 1.0 + exp(A);                  // Q7: pdf(y, poisson_link(m)) -- the link applied twice
+    const double A2 = fmax(nan_to_num(log(EA1)), 1e-8);
+    const double pl = fmax(ipow_ref(A2, y) / EA1 * yfact, 1e-8);
+    double temp = -(yA * rA) * (sg * sg) + t * (sg * (1.0 - sg));
     p2 = p1 * (sg * t) + pl * temp;
   }
 }
