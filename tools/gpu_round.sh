@@ -11,8 +11,9 @@ timeout 300 python -c 'import __graft_entry__ as g; g.smoke()' > $OUT/${TAG}_smo
 timeout 900 python bench.py "$@" > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?"
 cat $OUT/${TAG}_bench.json; tail -5 $OUT/${TAG}_bench.err
 if [ -s $OUT/${TAG}_bench.json ]; then
-  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/${TAG}_launches.csv \
-    python bench.py --scale 0.1 --steps 1 --warmup 1 --no-cpu-baseline "$@" > $OUT/${TAG}_ncu_list.log 2>&1; echo "ncu list rc=$?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:accumulate -s 3 -c 1 -o $OUT/${TAG}_accumulate -f \
-    python bench.py --scale 0.1 --steps 1 --warmup 1 --no-cpu-baseline "$@" > $OUT/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
+  # launch list of ONE timed step at full size (skip data generation + 3 warm-up steps + the timed region's first launches)
+  timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s 900 -c 260 --csv --log-file $OUT/${TAG}_launches.csv \
+    python bench.py --steps 1 --warmup 3 --no-cpu-baseline "$@" > $OUT/${TAG}_ncu_list.log 2>&1; echo "ncu list rc=$?"
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:accumulate_memo -s 40 -c 1 -o $OUT/${TAG}_accumulate -f \
+    python bench.py --steps 1 --warmup 3 --no-cpu-baseline "$@" > $OUT/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 fi
