@@ -28,6 +28,7 @@ struct MemoView {
   int32_t od[SSVI_MEMO_MAX_OTH];          // other modes, ascending
   int64_t n_rows[SSVI_MEMO_MAX_OTH];      // rows of each other mode
   int64_t rec_base[SSVI_MEMO_MAX_OTH + 1];// first record of each other mode's block; [n_oth] = total records
+  int64_t blk_base[SSVI_MEMO_MAX_OTH + 1];// sample_table_kernel: first CTA of each other mode (8 rows of one slot per CTA)
   double* tab;
 };
 
@@ -42,41 +43,49 @@ __host__ __device__ inline int memo_stage_bytes(int D, int k1, int zsize) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// One warp per table record.
+// One warp per table record; the 8 warps of a CTA take 8 consecutive rows of ONE (slot, other mode), so the noise block
+// is staged (and converted to double: an F2F.F64.F32 costs four DFMAs) once per CTA.
 // ---------------------------------------------------------------------------------------------------------------------
+__host__ __device__ inline int sample_table_smem(int D, int k1) {
+  return smp_zblk(D, k1, false) * 8 + 8 * smp_row_len(D, false) * 8;
+}
+
 template <int NT, typename ZT>
 __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView mv, const ZT* __restrict__ z_other) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2;
-  const int64_t rec = (int64_t)blockIdx.x * wpb + warp;
-  if (rec >= mv.rec_base[mv.n_oth]) return;
   const int D = v.D, k1 = v.k1, KT = k1 >> 3, NS = smp_ns(D);
   int jj = 0;
 #pragma unroll
   for (int a = 1; a < SSVI_MEMO_MAX_OTH; ++a)
-    if (a < mv.n_oth && rec >= mv.rec_base[a]) jj = a;
-  const int64_t local = rec - mv.rec_base[jj];
-  const int sl = (int)(local / mv.n_rows[jj]);
-  const int64_t j = local - (int64_t)sl * mv.n_rows[jj];
+    if (a < mv.n_oth && (int64_t)blockIdx.x >= mv.blk_base[a]) jj = a;
+  const int64_t nblk = (mv.n_rows[jj] + 7) >> 3;                        // CTAs per slot of this mode
+  const int64_t local = (int64_t)blockIdx.x - mv.blk_base[jj];
+  const int sl = (int)(local / nblk);
+  const int64_t j = (local - (int64_t)sl * nblk) * 8 + warp;
   const int slot = mv.slot_lo + sl;
 
-  const int stage = memo_stage_bytes(D, k1, (int)sizeof(ZT));
-  double* S = reinterpret_cast<double*>(smem_raw + (size_t)warp * stage);
-  ZT* zs = reinterpret_cast<ZT*>(S + v.srow_len);
+  double* zs = reinterpret_cast<double*>(smem_raw);
+  double* S = zs + v.zblk + (size_t)warp * v.srow_len;
   {
+    const ZT* zsrc = z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
+    for (int i = tid; i < v.zblk; i += 256) zs[i] = (double)zsrc[i];
+  }
+  const bool live = j < mv.n_rows[jj];
+  if (live) {
     const double2* src = reinterpret_cast<const double2*>(v.sampler[mv.od[jj]] + j * (int64_t)v.srow_len);
     double2* dst = reinterpret_cast<double2*>(S);
     for (int i = lane; i < (v.srow_len >> 1); i += 32) dst[i] = src[i];
-    const ZT* zsrc = z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
-    for (int i = lane; i < v.zblk; i += 32) zs[i] = zsrc[i];
   }
-  __syncwarp();
+  __syncthreads();
+  if (!live) return;
   double vv[NT][8][2];
   double fp[8][2];
-  mma_sample_mode<NT, ZT, false>(S, zs, NS, KT, lane, g, true, vv, fp);
+  mma_sample_mode<NT, double, false>(S, zs, NS, KT, lane, g, true, vv, fp);
   // Padding rows (n >= D) come out as exact zeros (zero mean, zero factor rows); row n == D is set to ONE so that the
   // contraction V V^T of the accumulate kernel also delivers the row sums sum_k V[n][k] (its row D) for free.
+  const int64_t rec = memo_rec(mv, jj, sl, j);
   double2* out = reinterpret_cast<double2*>(mv.tab + rec * (int64_t)mv.rec_len);
 #pragma unroll
   for (int i = 0; i < NT; ++i) {

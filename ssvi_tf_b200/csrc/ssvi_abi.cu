@@ -303,12 +303,10 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
                         const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, double* partial_out,
                         const double* w_state, const MemoWork& wk, cudaStream_t st) {
   {
-    const int wpb = 8;
-    const size_t smem = (size_t)memo_stage_bytes(v.D, v.k1, (int)sizeof(ZT)) * wpb;
+    const size_t smem = (size_t)sample_table_smem(v.D, v.k1);
     auto kern = sample_table_kernel<NT, ZT>;
     CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t recs = mv.rec_base[mv.n_oth];
-    kern<<<(unsigned)((recs + wpb - 1) / wpb), wpb * 32, smem, st>>>(v, mv, (const ZT*)h->z_other);
+    kern<<<(unsigned)mv.blk_base[mv.n_oth], 256, smem, st>>>(v, mv, (const ZT*)h->z_other);
     CUDA_TRY(h, cudaGetLastError());
   }
   if (n_chunks == 0) return SSVI_OK;
@@ -427,16 +425,19 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
   mv.n_slots = n_slots;
   mv.tab = (double*)table_ws;
   int jj = 0;
-  int64_t base = 0;
+  int64_t base = 0, blocks = 0;
   for (int d = 0; d < h->cfg.order; ++d) {
     if (d == dim) continue;
     mv.od[jj] = d;
     mv.n_rows[jj] = h->cfg.dims[d];
     mv.rec_base[jj] = base;
+    mv.blk_base[jj] = blocks;
     base += h->cfg.dims[d] * (int64_t)n_slots;
+    blocks += ((h->cfg.dims[d] + 7) / 8) * (int64_t)n_slots;
     ++jj;
   }
   mv.rec_base[jj] = base;
+  mv.blk_base[jj] = blocks;
   if (base >= ((int64_t)1 << 31)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: too many table records; use fewer slots per call%s");
   MemoWork wk;
   memset(&wk, 0, sizeof(wk));
