@@ -163,11 +163,11 @@ def build_model(c, data, device, group, chunk_entries, noise_slots, engine_kwarg
                noise_slots=noise_slots, chunk_entries=chunk_entries, process_group=group, engine_kwargs=engine_kwargs)
 
 
-def one_step(model, flush=None):
+def one_step(model, flush=None, batch_size=None):
     if flush is not None:
         flush.zero_()                     # inputs smaller than L2: evict them between iterations
     for dim in range(model.order):
-        model.sweep(dim)
+        model.sweep(dim, batch_size)
         model.update_hyper_parameter(dim)
 
 
@@ -271,6 +271,9 @@ def main():
     ap.add_argument("--table-mb", type=float, default=96.0, help="sample-table budget per call (L2-resident)")
     ap.add_argument("--sweep-chunk", type=int, default=64, help="max entries of one (row, slot) chunk")
     ap.add_argument("--sweep-streams", type=int, default=3, help="side streams the slot groups alternate between")
+    ap.add_argument("--batch-size", type=int, default=0,
+                    help="0: full-row sweeps (headline).  B > 0: reference-style subsampled sweeps, every row takes at "
+                         "most B entries drawn afresh each sweep (SSVI_TF_interface.py:170-174), scale = len / B")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     c = CONFIGS[args.config]
@@ -297,7 +300,12 @@ def main():
     eng = model.engine
     N = model.order
     nnz_train = eng.nnz
-    units_per_step = N * nnz_train                       # per rank
+    B = args.batch_size or None
+    if B is None:
+        units_per_step = N * nnz_train                   # per rank
+    else:
+        assert world == 1, "subsampled sweeps are single-shard"
+        units_per_step = int(sum(np.minimum(np.diff(eng.rowptr_h[d]), B).sum() for d in range(N)))
     model.fresh_noise()
 
     def barrier():
@@ -313,7 +321,7 @@ def main():
         else "inputs larger than L2 (COO+CSR %.0f MB per GPU)" % (in_bytes / 1e6)
     # ---- device-resident arm: `value` ------------------------------------------------------------
     for _ in range(args.warmup):
-        one_step(model, flush)
+        one_step(model, flush, B)
     eng.check_flags()
     barrier()
     sampler = ClockSampler(local)
@@ -325,7 +333,7 @@ def main():
     barrier()
     e0.record()
     for _ in range(args.steps):
-        one_step(model, flush)
+        one_step(model, flush, B)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -342,7 +350,7 @@ def main():
     # roofline of the dominant kernel (ssvi_accumulate), from CUDA events inside the timed region
     acc_ms = [a.elapsed_time(b) for a, b, _ in events]
     acc_units = [n for _, _, n in events]
-    mean_row = nnz_train * N / float(sum(c["dims"]))
+    mean_row = units_per_step / float(sum(c["dims"]))
     bpu = algorithmic_bytes_per_unit(c, mean_row)
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
@@ -354,7 +362,7 @@ def main():
                 "traffic": None, "kernel": "accumulate (stages 1-3)", "peak_source": peak_src,
                 "algorithmic_bytes_per_unit": bpu, "kernel_ms_per_launch": float(np.mean(acc_ms)),
                 "kernel_share_of_step": sum(acc_ms) / ms,
-                "fp64_pipe": fp64_pipe_stats(c, sum(acc_units) / (sum(acc_ms) * 1e-3)),
+                "fp64_pipe": fp64_pipe_stats(c, sum(acc_units) / (sum(acc_ms) * 1e-3)) if B is None else None,
                 "note": "fp64 contract: the FP64 pipe (37 TFLOP/s measured), not HBM, bounds this kernel; see DESIGN.md 3.1"}
     tr_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr_path):          # DRAM bytes per unit from the committed ncu capture of this kernel
@@ -369,13 +377,14 @@ def main():
     # runs on a copy stream while step k computes (all K copies are inside the timed region).
     from ssvi_tf_b200.engine import NoisePool, _ptr
     pin = lambda x: x.cpu().pin_memory()                                      # noqa: E731
-    plans = [model.sweep_plan(d)[0] for d in range(N)]
+    plans = [model.sweep_plan(d)[0] for d in range(N)] if B is None else [None] * N
     nz = eng.noise
     noise_names = [n for n in ("z_other", "z_own", "r_w", "z_f") if getattr(nz, n) is not None]
-    dev_sets = [dict(coords=eng.coords, vals=eng.vals, perm=[pl.entry_ids for pl in plans],
+    lists0 = [pl.entry_ids for pl in plans] if B is None else list(eng.perm)   # the per-mode entry lists the sweeps read
+    dev_sets = [dict(coords=eng.coords, vals=eng.vals, perm=lists0,
                      noise=[getattr(nz, n) for n in noise_names])]
     dev_sets.append(dict(coords=torch.empty_like(eng.coords), vals=torch.empty_like(eng.vals),
-                         perm=[torch.empty_like(pl.entry_ids) for pl in plans],
+                         perm=[torch.empty_like(x) for x in lists0],
                          noise=[torch.empty_like(x) for x in dev_sets[0]["noise"]]))
     host = dict(coords=pin(eng.coords), vals=pin(eng.vals), perm=[pin(x) for x in dev_sets[0]["perm"]],
                 noise=[pin(x) for x in dev_sets[0]["noise"]])
@@ -404,8 +413,11 @@ def main():
         ds = dev_sets[k % 2]
         eng.coords, eng.vals = ds["coords"], ds["vals"]
         eng._call(eng.lib.ssvi_bind_data, _ptr(eng.coords), _ptr(eng.vals), eng.nnz)
-        for pl, t_ in zip(plans, ds["perm"]):
-            pl.entry_ids = t_
+        for d_, (pl, t_) in enumerate(zip(plans, ds["perm"])):
+            if pl is None:
+                eng.perm[d_] = t_
+            else:
+                pl.entry_ids = t_
         kw = dict(zip(noise_names, ds["noise"]))
         eng.set_noise(NoisePool(kw.get("z_other"), kw.get("z_own"), kw.get("r_w"), kw.get("z_f")))
 
@@ -418,7 +430,7 @@ def main():
                 stage(k + 1)
             main_stream.wait_event(ready[k % 2])
             bind(k)
-            one_step(model, flush)
+            one_step(model, flush, B)
             free[k % 2].record(main_stream)
             for ho, p in zip(h_out, eng.params):
                 ho.copy_(p, non_blocking=True)
@@ -448,10 +460,13 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": c["desc"], "config_id": args.config, "nnz_train_per_gpu": nnz_train,
-                       "units_per_step_per_gpu": units_per_step, "sweep": "full rows (scale=1), all modes",
+                       "units_per_step_per_gpu": units_per_step,
+                       "sweep": "full rows (scale=1), all modes" if B is None else
+                       "reference-style minibatches: every row takes <= %d entries, drawn on the device each sweep "
+                       "(scale = len/B), all rows of all modes" % B,
                        "noise": "f32 pool, %d slots" % eng.noise.slots, "chunk_entries": args.chunk_entries,
                        "path": ("slot-major sweep kernels, %d slots/call" % model.sweep_plan(0)[0].groups[0][1])
-                       if eng.sweep_supported else "direct",
+                       if eng.sweep_supported and B is None else "direct (one warp per row-chunk)",
                        "l2": l2_note,
                        "parallelism": "entries sharded x%d, all-reduce of row accumulators" % world},
             "roofline": roofline, "cpu_baseline": cpu,

@@ -112,6 +112,8 @@ class SSVI_TF(object):
         self._noise_gen_seed = int(noise_seed)
         self._noise_draws = 0
         self._np_rng = np.random.default_rng(noise_seed)
+        self._sub_gen = torch.Generator(device=eng.device)
+        self._sub_gen.manual_seed(int(noise_seed) + 7919)
         self._n_obs_global = {}
 
     # ---------------------------------------------------------------------------------------------
@@ -234,10 +236,20 @@ class SSVI_TF(object):
         plan = eng.plan_sweep(dim, off) if eng.sweep_supported else eng.plan_full(dim, None, off)
         return plan, n_obs
 
-    def sweep(self, dim):
-        """One Jacobi sweep over mode `dim`."""
-        plan, n_obs = self.sweep_plan(dim)
+    def sweep(self, dim, batch_size=None):
+        """One Jacobi sweep over mode `dim`: every row updated from one state snapshot.  batch_size=None takes every
+        observed entry of every row (scale = 1); with a batch size each row takes the reference's minibatch
+        (:170-174: at most batch_size entries, drawn without replacement, scale = len / batch_size), all rows
+        subsampled in one device pass."""
+        if batch_size is None:
+            plan, n_obs = self.sweep_plan(dim)
+        else:
+            assert self.process_group is None, "subsampled sweeps are single-shard"
+            if self.engine.noise is None:
+                self.fresh_noise()
+            plan, n_obs = self.engine.plan_subsampled_sweep(dim, batch_size, self._sub_gen), None
         self._run_plan(plan, n_obs)
+        return plan
 
     def update_hyper_parameter(self, dim):
         """pSigma[dim] = sum_rows (tr S + m.m) / (n_dim D)  (:146-160), as a device reduction."""

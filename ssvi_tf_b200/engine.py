@@ -238,6 +238,7 @@ class Engine(object):
         self.noise = None
         self._full_plans = {}
         self._sweep_plans = {}
+        self._sub_plans = {}
         self.sweep_supported = bool(self.lib.ssvi_sweep_supported(self.h))
         self._scratch = {}
         self.launches = 0          # kernels of libssvi_b200 launched through this engine
@@ -367,6 +368,38 @@ class Engine(object):
         entry_ids = torch.as_tensor(np.concatenate(ids) if ids else np.zeros(0, np.int64)).to(self.device)
         return SweepPlan(dim, torch.as_tensor(rows_h).to(self.device), torch.as_tensor(lens).to(self.device),
                          entry_ids, tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
+
+    def plan_subsampled_sweep(self, dim, batch_size, generator=None):
+        """The reference's minibatch rule (SSVI_TF_interface.py:170-174) for EVERY row of mode `dim` at once, drawn on
+        the device: rows holding more than batch_size entries keep batch_size of them, chosen uniformly without
+        replacement (one sort of the mode's entry list by (row, uniform key)); shorter rows keep all.  The chunk
+        tables depend on (dim, batch_size) only and are cached; every call draws a fresh subsample.  Single shard."""
+        B = int(batch_size)
+        key = (dim, B)
+        c = self._sub_plans.get(key)
+        if c is None:
+            rp = self.rowptr_h[dim]
+            lens = rp[1:] - rp[:-1]
+            seg_len = np.minimum(lens, B)
+            seg_start = np.zeros(len(lens), dtype=np.int64)
+            np.cumsum(seg_len[:-1], out=seg_start[1:])
+            rows_h = np.arange(self.dims[dim], dtype=np.int64)
+            tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len)
+            row_of_pos = torch.repeat_interleave(torch.arange(self.dims[dim], device=self.device),
+                                                 torch.as_tensor(lens).to(self.device))
+            pos_in_row = torch.arange(self.nnz, device=self.device) - torch.as_tensor(rp[:-1]).to(self.device)[row_of_pos]
+            lens_d = torch.as_tensor(lens).to(self.device)
+            whole = lens_d[row_of_pos] <= B                # rows kept whole stay in append order (:170-174)
+            c = dict(tabs=tabs, seg_len=seg_len, rows=torch.as_tensor(rows_h).to(self.device),
+                     n_obs=lens_d, row_key=row_of_pos.double(), whole=whole,
+                     frac=pos_in_row.double() / (B + 1), keep=torch.nonzero(pos_in_row < B).squeeze(1))
+            self._sub_plans[key] = c
+        u = torch.rand(self.nnz, device=self.device, dtype=torch.float64, generator=generator)
+        u = torch.where(c["whole"], c["frac"], u)
+        order = torch.argsort(c["row_key"] + u)            # by row; subsampled rows uniformly shuffled inside
+        entry_ids = self.perm[dim][order[c["keep"]]]
+        t = c["tabs"]
+        return SweepPlan(dim, c["rows"], c["n_obs"], entry_ids, t[0], t[1], t[2], t[3], t[4], c["seg_len"])
 
     def plan_sweep(self, dim, slot_offset=None):
         """Full sweep of mode `dim` (every observed entry of every row, scale = 1) for the sample-table

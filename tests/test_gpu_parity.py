@@ -295,3 +295,56 @@ def test_sweep_diag_path_matches_generic_and_oracle(dims, D, k1, model, lik, P, 
         so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
         for got in states:
             assert_state_close(got, want, cfg, RTOL, what="dims=%s mode %d" % (dims, dim))
+
+
+def test_subsampled_sweep_draws_reference_minibatches_on_device():
+    """plan_subsampled_sweep: every row keeps min(len, B) DISTINCT entries of its own list (bit-exact ids / counts),
+    fresh picks per call, and the sweep equals the oracle's rows_step fed the same picks (SSVI_TF_interface.py:170-174)."""
+    from ssvi_tf_b200.engine import NoisePool
+    rng = np.random.default_rng(23)
+    dims, D, k1, k2, B = [6, 9, 5], 5, 16, 4, 8
+    cfg = so.make_config("d", "bernoulli", D, k1=k1, k2=k2, batch_size=B)
+    coords, vals = random_problem(rng, "bernoulli", dims, 200)
+    coords = coords[coords[:, 1] != 2]                 # an empty row in mode 1
+    vals = vals[:len(coords)]
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    eng = _engine(cfg, dims, coords, vals, chunk_entries=3)
+    pool = so.make_tape(rng, cfg, 3, B)
+    eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=False))
+    gen = torch.Generator(device=eng.device)
+    gen.manual_seed(5)
+    for dim in range(3):
+        engine_load_state(eng, st0)
+        plan = eng.plan_subsampled_sweep(dim, B, gen)
+        again = eng.plan_subsampled_sweep(dim, B, gen)
+        ids = plan.entry_ids.cpu().numpy()
+        lens = np.diff(rowptr[dim])
+        want_counts = np.minimum(lens, B)
+        np.testing.assert_array_equal(plan.batch_sizes, want_counts)
+        assert len(ids) == want_counts.sum()
+        assert not np.array_equal(ids, again.entry_ids.cpu().numpy())          # a fresh draw every sweep
+        rows = np.arange(dims[dim])
+        entries, tapes, pos = [], [], 0
+        for row in rows:
+            own = perm[dim][rowptr[dim][row]:rowptr[dim][row + 1]]
+            seg = ids[pos:pos + want_counts[row]]
+            pos += want_counts[row]
+            assert len(set(seg.tolist())) == len(seg) and set(seg.tolist()) <= set(own.tolist())
+            if lens[row] <= B:
+                np.testing.assert_array_equal(seg, own)       # kept whole, in append order
+            n = len(seg)
+            t = so.Tape(pool.z_other[:n], pool.z_own[:n], pool.r_w[:n], pool.z_f[:n])
+            lookup = {int(e): k for k, e in enumerate(own)}
+            if lens[row] > B:
+                t.sub_idx = np.array([lookup[int(e)] for e in seg])
+                entries.append((coords[own], vals[own]))
+            else:
+                entries.append((coords[own], vals[own]))
+            tapes.append(t)
+        eng.step(plan)
+        eng.check_flags()
+        want = so.copy_state(st0)
+        so.rows_step(want, cfg, dim, rows, entries, tapes)
+        assert_state_close(engine_dump_state(eng, st0), want, cfg, RTOL, what="subsampled mode %d" % dim)
+    eng.close()
