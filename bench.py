@@ -43,6 +43,9 @@ CONFIGS = {
                k2=64, desc="real 500x500x500x100, 1e8 nnz, D=50, normal, SSVI_TF_simple diag cov"),
     "c5": dict(dims=[10000, 10000, 10000], nnz=1_000_000_000, D=32, lik="normal", model="d", diag=False, k1=64,
                k2=64, desc="real 10k^3, 1e9 nnz, D=32, normal, SSVI_TF_d full cov"),
+    # diagnostic (not a BASELINE config): C5's rank with an index space whose one-slot sample table fits in L2
+    "c5l2": dict(dims=[2500, 2500, 2500], nnz=50_000_000, D=32, lik="normal", model="d", diag=False, k1=64,
+                 k2=64, desc="diagnostic: real 2500^3, 5e7 nnz, D=32, normal, SSVI_TF_d full cov"),
 }
 DATATYPE = {"normal": "real", "bernoulli": "binary", "poisson": "count"}
 
@@ -130,19 +133,26 @@ class DeviceTensorData(object):
             mus = np.linspace(0, 1.5, N)         # count_tensor.py:16-23
         else:
             mus = [0.5, 1.0, 0.2, 0.5][:N]
-        f = torch.ones((nnz, D), dtype=torch.float32, device=device)
-        for d in range(N):
-            U = float(mus[d]) + math.sqrt(0.1) * torch.randn((self.dims[d], D), generator=g, device=device)
-            f *= U[coords[:, d].long()]
-        f = f.sum(dim=1).double()
-        if c["lik"] == "normal":
-            vals = f + 0.05 * f.abs() * torch.randn(f.shape, generator=g, device=device, dtype=torch.float64)
-        elif c["lik"] == "bernoulli":
-            u = torch.rand(f.shape, generator=g, device=device, dtype=torch.float64)
-            vals = torch.where(u < torch.sigmoid(f), 1.0, -1.0).double()
-        else:
-            lam = torch.clamp(torch.log1p(torch.exp(f)), min=1e-8)
-            vals = torch.clamp(torch.poisson(lam, generator=g), max=170.0)      # y! finite in fp64
+        Us = [float(mus[d]) + math.sqrt(0.1) * torch.randn((self.dims[d], D), generator=g, device=device)
+              for d in range(N)]
+        vals = torch.empty((nnz,), dtype=torch.float64, device=device)
+        step = 1 << 24                                   # values in slabs: [nnz, D] at 1e9 entries would not fit
+        for s0 in range(0, nnz, step):
+            cc = coords[s0:s0 + step].long()
+            f = Us[0][cc[:, 0]]
+            for d in range(1, N):
+                f = f * Us[d][cc[:, d]]
+            f = f.sum(dim=1).double()
+            if c["lik"] == "normal":
+                v = f + 0.05 * f.abs() * torch.randn(f.shape, generator=g, device=device, dtype=torch.float64)
+            elif c["lik"] == "bernoulli":
+                u = torch.rand(f.shape, generator=g, device=device, dtype=torch.float64)
+                v = torch.where(u < torch.sigmoid(f), 1.0, -1.0).double()
+            else:
+                lam = torch.clamp(torch.log1p(torch.exp(f)), min=1e-8)
+                v = torch.clamp(torch.poisson(lam, generator=g), max=170.0)      # y! finite in fp64
+            vals[s0:s0 + step] = v
+        del Us
         n_train = int(nnz * 0.8)
         self.train_entries, self.train_vals = coords[:n_train].contiguous(), vals[:n_train].contiguous()
         self.test_entries = coords[n_train:].cpu().numpy().astype(np.int64)
@@ -271,10 +281,14 @@ def main():
     ap.add_argument("--table-mb", type=float, default=96.0, help="sample-table budget per call (L2-resident)")
     ap.add_argument("--sweep-chunk", type=int, default=64, help="max entries of one (row, slot) chunk")
     ap.add_argument("--sweep-streams", type=int, default=3, help="side streams the slot groups alternate between")
+    ap.add_argument("--tile-blocks", type=int, default=0,
+                    help="L2 tiling of the sweep launch order: blocks per other mode (0 = from the table budget, 1 = off)")
     ap.add_argument("--batch-size", type=int, default=0,
                     help="0: full-row sweeps (headline).  B > 0: reference-style subsampled sweeps, every row takes at "
                          "most B entries drawn afresh each sweep (SSVI_TF_interface.py:170-174), scale = len / B")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true",
+                    help="diagnostic runs only (config 5 at full size pins 35 GB of host memory for the e2e arm)")
     args = ap.parse_args()
     c = CONFIGS[args.config]
     rank = int(os.environ.get("RANK", "0"))
@@ -293,10 +307,10 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device(device))
         group = dist.group.WORLD
-    data = DeviceTensorData(c, device, seed=319 + int(args.config[1:]) + 1000 * rank, scale=args.scale)
+    data = DeviceTensorData(c, device, seed=319 + int(args.config[1]) + 1000 * rank, scale=args.scale)
     model = build_model(c, data, device, group, args.chunk_entries, args.noise_slots,
                         dict(table_budget_bytes=int(args.table_mb * (1 << 20)), sweep_chunk_entries=args.sweep_chunk,
-                             sweep_streams=args.sweep_streams))
+                             sweep_streams=args.sweep_streams, sweep_tile_blocks=args.tile_blocks))
     eng = model.engine
     N = model.order
     nnz_train = eng.nnz
@@ -375,78 +389,85 @@ def main():
     # Every step's inputs (COO entries, values, the per-mode entry lists the sweep kernels read, the noise pool) are
     # copied from pinned host memory and the posterior is copied back.  Two device input sets: the copy of step k+1
     # runs on a copy stream while step k computes (all K copies are inside the timed region).
-    from ssvi_tf_b200.engine import NoisePool, _ptr
-    pin = lambda x: x.cpu().pin_memory()                                      # noqa: E731
-    plans = [model.sweep_plan(d)[0] for d in range(N)] if B is None else [None] * N
-    nz = eng.noise
-    noise_names = [n for n in ("z_other", "z_own", "r_w", "z_f") if getattr(nz, n) is not None]
-    lists0 = [pl.entry_ids for pl in plans] if B is None else list(eng.perm)   # the per-mode entry lists the sweeps read
-    dev_sets = [dict(coords=eng.coords, vals=eng.vals, perm=lists0,
-                     noise=[getattr(nz, n) for n in noise_names])]
-    dev_sets.append(dict(coords=torch.empty_like(eng.coords), vals=torch.empty_like(eng.vals),
-                         perm=[torch.empty_like(x) for x in lists0],
-                         noise=[torch.empty_like(x) for x in dev_sets[0]["noise"]]))
-    host = dict(coords=pin(eng.coords), vals=pin(eng.vals), perm=[pin(x) for x in dev_sets[0]["perm"]],
-                noise=[pin(x) for x in dev_sets[0]["noise"]])
-    h_out = [torch.empty(p.shape, dtype=p.dtype).pin_memory() for p in eng.params]
-    h2d = (host["coords"].numel() * 4 + host["vals"].numel() * 8 + sum(x.numel() * 8 for x in host["perm"])
-           + sum(x.numel() * x.element_size() for x in host["noise"]))
-    d2h = sum(p.numel() * 8 for p in h_out)
-    main_stream = torch.cuda.current_stream()
-    copy_stream = torch.cuda.Stream()
-    ready = [torch.cuda.Event(), torch.cuda.Event()]
-    free = [torch.cuda.Event(), torch.cuda.Event()]
+    def run_e2e():
+        from ssvi_tf_b200.engine import NoisePool, _ptr
+        pin = lambda x: x.cpu().pin_memory()                                      # noqa: E731
+        plans = [model.sweep_plan(d)[0] for d in range(N)] if B is None else [None] * N
+        nz = eng.noise
+        noise_names = [n for n in ("z_other", "z_own", "r_w", "z_f") if getattr(nz, n) is not None]
+        lists0 = [pl.entry_ids for pl in plans] if B is None else list(eng.perm)   # the per-mode entry lists the sweeps read
+        dev_sets = [dict(coords=eng.coords, vals=eng.vals, perm=lists0,
+                         noise=[getattr(nz, n) for n in noise_names])]
+        dev_sets.append(dict(coords=torch.empty_like(eng.coords), vals=torch.empty_like(eng.vals),
+                             perm=[torch.empty_like(x) for x in lists0],
+                             noise=[torch.empty_like(x) for x in dev_sets[0]["noise"]]))
+        host = dict(coords=pin(eng.coords), vals=pin(eng.vals), perm=[pin(x) for x in dev_sets[0]["perm"]],
+                    noise=[pin(x) for x in dev_sets[0]["noise"]])
+        h_out = [torch.empty(p.shape, dtype=p.dtype).pin_memory() for p in eng.params]
+        h2d = (host["coords"].numel() * 4 + host["vals"].numel() * 8 + sum(x.numel() * 8 for x in host["perm"])
+               + sum(x.numel() * x.element_size() for x in host["noise"]))
+        d2h = sum(p.numel() * 8 for p in h_out)
+        main_stream = torch.cuda.current_stream()
+        copy_stream = torch.cuda.Stream()
+        ready = [torch.cuda.Event(), torch.cuda.Event()]
+        free = [torch.cuda.Event(), torch.cuda.Event()]
 
-    def stage(k):                       # H2D of step k's inputs into set k % 2
-        ds = dev_sets[k % 2]
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(free[k % 2])
-            ds["coords"].copy_(host["coords"], non_blocking=True)
-            ds["vals"].copy_(host["vals"], non_blocking=True)
-            for dp, hp in zip(ds["perm"], host["perm"]):
-                dp.copy_(hp, non_blocking=True)
-            for dn, hn in zip(ds["noise"], host["noise"]):
-                dn.copy_(hn, non_blocking=True)
-            ready[k % 2].record(copy_stream)
+        def stage(k):                       # H2D of step k's inputs into set k % 2
+            ds = dev_sets[k % 2]
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(free[k % 2])
+                ds["coords"].copy_(host["coords"], non_blocking=True)
+                ds["vals"].copy_(host["vals"], non_blocking=True)
+                for dp, hp in zip(ds["perm"], host["perm"]):
+                    dp.copy_(hp, non_blocking=True)
+                for dn, hn in zip(ds["noise"], host["noise"]):
+                    dn.copy_(hn, non_blocking=True)
+                ready[k % 2].record(copy_stream)
 
-    def bind(k):                        # point the library at set k % 2 (host-side pointer swaps only)
-        ds = dev_sets[k % 2]
-        eng.coords, eng.vals = ds["coords"], ds["vals"]
-        eng._call(eng.lib.ssvi_bind_data, _ptr(eng.coords), _ptr(eng.vals), eng.nnz)
-        for d_, (pl, t_) in enumerate(zip(plans, ds["perm"])):
-            if pl is None:
-                eng.perm[d_] = t_
-            else:
-                pl.entry_ids = t_
-        kw = dict(zip(noise_names, ds["noise"]))
-        eng.set_noise(NoisePool(kw.get("z_other"), kw.get("z_own"), kw.get("r_w"), kw.get("z_f")))
+        def bind(k):                        # point the library at set k % 2 (host-side pointer swaps only)
+            ds = dev_sets[k % 2]
+            eng.coords, eng.vals = ds["coords"], ds["vals"]
+            eng._call(eng.lib.ssvi_bind_data, _ptr(eng.coords), _ptr(eng.vals), eng.nnz)
+            for d_, (pl, t_) in enumerate(zip(plans, ds["perm"])):
+                if pl is None:
+                    eng.perm[d_] = t_
+                else:
+                    pl.entry_ids = t_
+            kw = dict(zip(noise_names, ds["noise"]))
+            eng.set_noise(NoisePool(kw.get("z_other"), kw.get("z_own"), kw.get("r_w"), kw.get("z_f")))
 
-    def e2e_run(steps):
-        for e in free:
-            e.record(main_stream)
-        stage(0)
-        for k in range(steps):
-            if k + 1 < steps:
-                stage(k + 1)
-            main_stream.wait_event(ready[k % 2])
-            bind(k)
-            one_step(model, flush, B)
-            free[k % 2].record(main_stream)
-            for ho, p in zip(h_out, eng.params):
-                ho.copy_(p, non_blocking=True)
+        def e2e_run(steps):
+            for e in free:
+                e.record(main_stream)
+            stage(0)
+            for k in range(steps):
+                if k + 1 < steps:
+                    stage(k + 1)
+                main_stream.wait_event(ready[k % 2])
+                bind(k)
+                one_step(model, flush, B)
+                free[k % 2].record(main_stream)
+                for ho, p in zip(h_out, eng.params):
+                    ho.copy_(p, non_blocking=True)
 
-    e2e_run(2)
-    barrier()
-    e0.record()
-    e2e_run(args.steps)
-    e1.record()
-    barrier()
-    bind(0)
-    t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * units_per_step * args.steps / (float(t.item()) * 1e-3)
-    eng.check_flags()
+        e2e_run(2)
+        barrier()
+        e0.record()
+        e2e_run(args.steps)
+        e1.record()
+        barrier()
+        bind(0)
+        t = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_value = world * units_per_step * args.steps / (float(t.item()) * 1e-3)
+        eng.check_flags()
+        return e2e_value, h2d, d2h
+
+    e2e = None
+    if not args.no_e2e:
+        e2e_value, h2d, d2h = run_e2e()
+        e2e = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
 
     if rank == 0:
         cpu = None
@@ -465,13 +486,13 @@ def main():
                        "reference-style minibatches: every row takes <= %d entries, drawn on the device each sweep "
                        "(scale = len/B), all rows of all modes" % B,
                        "noise": "f32 pool, %d slots" % eng.noise.slots, "chunk_entries": args.chunk_entries,
-                       "path": ("slot-major sweep kernels, %d slots/call" % model.sweep_plan(0)[0].groups[0][1])
+                       "path": ("slot-major sweep kernels, %d slots/call, %d L2 tile blocks per other mode"
+                                % (model.sweep_plan(0)[0].groups[0][1], getattr(model.sweep_plan(0)[0], "tile_blocks", 1)))
                        if eng.sweep_supported and B is None else "direct (one warp per row-chunk)",
                        "l2": l2_note,
                        "parallelism": "entries sharded x%d, all-reduce of row accumulators" % world},
             "roofline": roofline, "cpu_baseline": cpu,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-            "gpu_launches": launches, "clocks": clocks}))
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks}))
     if world > 1:
         dist.destroy_process_group()
 

@@ -197,6 +197,12 @@ int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo, int32_t n
  * acc_out double [n_rows][ssvi_acc_len] is the payload of the multi-GPU all-reduce. */
 int ssvi_reduce_chunks(SsviHandle* h, int64_t n_rows, const int64_t* row_chunk_ptr,
                        const double* partial, double* acc_out, void* stream);
+/* The same sum folded into a running accumulator (accumulate != 0: acc[r] += sum, else acc[r] = sum).  Lets a sweep
+ * be reduced slot group by slot group -- the same accumulation loops as above, split by group -- so the chunk-record
+ * buffer holds ONE group's records (config 5 at full size would need > 100 GB of records otherwise) and the records
+ * are still in L2 when they are summed.  Deterministic for a fixed sequence of calls. */
+int ssvi_reduce_chunks_into(SsviHandle* h, int64_t n_rows, const int64_t* row_chunk_ptr,
+                            const double* partial, double* acc_inout, int32_t accumulate, void* stream);
 
 /* Stage 4 for the listed rows of mode `dim`: scale = n_obs[r] / count[r] (:181-183), covariance
  * then mean update (:191-196, 595-681, 694-713), trackers (:199, :217, 722-729), write-back (:219)

@@ -55,6 +55,7 @@ SIGNATURES = {
     "ssvi_sweep_accumulate": (ctypes.c_int, [_P, _I32, _I32, _I32, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _I64, _I64, _I64, _P, _P]),
     "ssvi_sweep_work_bytes": (_I64, [_P, _I64]),
     "ssvi_reduce_chunks": (ctypes.c_int, [_P, _I64, _P, _P, _P, _P]),
+    "ssvi_reduce_chunks_into": (ctypes.c_int, [_P, _I64, _P, _P, _P, _I32, _P]),
     "ssvi_row_update": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _I32, _I32, _P, _P]),
     "ssvi_sigma_update": (ctypes.c_int, [_P, _I64, _P, _P, _P, _P]),
     "ssvi_hyper_reduce": (ctypes.c_int, [_P, _I32, _P, _P]),

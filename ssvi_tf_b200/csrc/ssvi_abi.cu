@@ -476,13 +476,14 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
 
 // acc_out[r][i] = sum over the row's chunk records, in chunk order (deterministic)
 __global__ void reduce_chunks_kernel(int64_t n_rows, int acc_len, const int64_t* __restrict__ row_chunk_ptr,
-                                     const double* __restrict__ partial, double* __restrict__ acc_out) {
+                                     const double* __restrict__ partial, double* __restrict__ acc_out, int accumulate) {
   const int64_t r = blockIdx.x;
   const int64_t c0 = row_chunk_ptr[r], c1 = row_chunk_ptr[r + 1];
+  if (accumulate && c0 == c1) return;
   for (int i = threadIdx.x; i < acc_len; i += blockDim.x) {
     double s = 0.0;
     for (int64_t c = c0; c < c1; ++c) s += partial[c * acc_len + i];
-    acc_out[r * acc_len + i] = s;
+    acc_out[r * acc_len + i] = accumulate ? acc_out[r * acc_len + i] + s : s;
   }
 }
 
@@ -491,7 +492,19 @@ extern "C" int ssvi_reduce_chunks(SsviHandle* h, int64_t n_rows, const int64_t* 
   if (!h) return SSVI_E_INVALID;
   if (n_rows == 0) return SSVI_OK;
   if (n_rows < 0 || !row_chunk_ptr || !partial || !acc_out) return fail(h, SSVI_E_INVALID, "reduce_chunks: null pointer%s");
-  reduce_chunks_kernel<<<(unsigned)n_rows, 128, 0, (cudaStream_t)stream>>>(n_rows, (int)h->acc_len, row_chunk_ptr, partial, acc_out);
+  reduce_chunks_kernel<<<(unsigned)n_rows, 128, 0, (cudaStream_t)stream>>>(n_rows, (int)h->acc_len, row_chunk_ptr, partial, acc_out, 0);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+extern "C" int ssvi_reduce_chunks_into(SsviHandle* h, int64_t n_rows, const int64_t* row_chunk_ptr, const double* partial,
+                                       double* acc_inout, int32_t accumulate, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (n_rows == 0) return SSVI_OK;
+  if (n_rows < 0 || !row_chunk_ptr || !partial || !acc_inout)
+    return fail(h, SSVI_E_INVALID, "reduce_chunks_into: null pointer%s");
+  reduce_chunks_kernel<<<(unsigned)n_rows, 128, 0, (cudaStream_t)stream>>>(n_rows, (int)h->acc_len, row_chunk_ptr, partial,
+                                                                           acc_inout, accumulate ? 1 : 0);
   CUDA_TRY(h, cudaGetLastError());
   return SSVI_OK;
 }

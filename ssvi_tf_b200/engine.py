@@ -122,23 +122,24 @@ class SweepPlan(object):
 class SlotSweepPlan(object):
     """Slot-major chunk tables for ssvi_sweep_accumulate (the sample-table path of a full sweep).
 
-    Chunks are sorted by (slot, row, segment) -- the launch order -- and carry the index of their record
-    in a row-major partial buffer (chunk_out), so ssvi_reduce_chunks still sums each row's records in
-    one contiguous, fixed-order run.  groups: [(slot_lo, n_slots, chunk_lo, chunk_hi)]."""
+    Chunks are sorted by (slot, [tile,] row, segment) -- the launch order -- and carry the index of their record
+    in their slot group's row-major record buffer (chunk_out), so ssvi_reduce_chunks_into sums each row's records
+    of the group in one contiguous, fixed-order run.  groups: [(slot_lo, n_slots, chunk_lo, chunk_hi)]."""
 
     def __init__(self, dim, rows, n_obs, entry_ids, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
-                 row_chunk_ptr, batch_sizes, groups, table_bytes):
+                 group_rcp, batch_sizes, groups, table_bytes):
         self.dim = dim
         self.rows, self.n_obs, self.entry_ids = rows, n_obs, entry_ids
         self.chunk_row, self.chunk_start, self.chunk_len = chunk_row, chunk_start, chunk_len
-        self.chunk_slot, self.chunk_out = chunk_slot, chunk_out
-        self.row_chunk_ptr = row_chunk_ptr
+        self.chunk_slot, self.chunk_out = chunk_slot, chunk_out     # chunk_out: record index inside the group's buffer
+        self.group_rcp = group_rcp                                  # int64 [n_groups][n_rows + 1] device
         self.n_rows = int(rows.numel())
         self.n_chunks = int(chunk_row.numel())
         self.batch_sizes = batch_sizes
         self.n_entries = int(batch_sizes.sum())
         self.groups = groups
         self.table_bytes = int(table_bytes)
+        self.tile_blocks = 1                # L2 tile blocks per other mode (_plan_sweep_tiled)
         self.chunk_start_h = None           # host int64 [n_chunks + 1]: first entry position of every chunk (+ total)
 
 
@@ -146,7 +147,8 @@ class Engine(object):
     """One GPU's view of the problem: COO shard + CSR index + posterior state + noise pool."""
 
     def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16,
-                 kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64, sweep_streams=2):
+                 kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64, sweep_streams=2,
+                 sweep_tile_blocks=0, sweep_tile_min_entries=24.0):
         """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
         cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
         if not torch.cuda.is_available():
@@ -162,6 +164,8 @@ class Engine(object):
         self.table_budget_bytes = int(table_budget_bytes)      # L2-resident sample table of the sweep path
         self.sweep_chunk_entries = int(sweep_chunk_entries)
         self.sweep_streams = int(sweep_streams)
+        self.sweep_tile_blocks = int(sweep_tile_blocks)        # 0: chosen from the table budget (_sweep_tile_blocks)
+        self.sweep_tile_min_entries = float(sweep_tile_min_entries)
         self._side_streams = []
         self.noise_dtype = noise_dtype
         if cfg["mean_update"] not in UPDATE_IDS or cfg["cov_update"] not in UPDATE_IDS:
@@ -411,6 +415,11 @@ class Engine(object):
         key = (dim, P, None if slot_offset is None else hash(np.asarray(slot_offset).tobytes()))
         if key in self._sweep_plans:
             return self._sweep_plans[key]
+        nb = self._sweep_tile_blocks(dim)
+        if nb > 1:
+            plan = self._plan_sweep_tiled(dim, slot_offset, nb)
+            self._sweep_plans[key] = plan
+            return plan
         n = self.dims[dim]
         dev = self.device
         rp = self.rowptr_h[dim]
@@ -446,36 +455,135 @@ class Engine(object):
         chunk_start = pair_start[pair_of] + seg * base + np.minimum(seg, rem)
         chunk_slot = pair_of // n
         chunk_row = pair_of % n
-        # record index in row-major (row, slot, segment) order
-        rm_chunk = np.zeros(n * P + 1, dtype=np.int64)
-        np.cumsum(nseg.T.reshape(-1), out=rm_chunk[1:])
-        chunk_out = rm_chunk[chunk_row * P + chunk_slot] + seg
-        row_chunk_ptr = rm_chunk[::P].copy()
         # ---- slot groups: as many slots per call as the table budget holds ----
         per_slot = int(self.lib.ssvi_sweep_table_bytes(self.h, dim, 1))
         gs = max(1, min(P, self.table_budget_bytes // max(per_slot, 1)))
         slot_chunk = pair_chunk[::n]                             # first chunk of each slot (+ total)
         groups = [(s0, min(gs, P - s0), int(slot_chunk[s0]), int(slot_chunk[min(s0 + gs, P)]))
                   for s0 in range(0, P, gs)]
+        chunk_out, group_rcp = self._group_records(chunk_slot // gs, chunk_row, n, groups)
         t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a.astype(dt))).to(dev)      # noqa: E731
         plan = SlotSweepPlan(dim, torch.arange(n, device=dev, dtype=torch.int64), lens_d, entry_ids,
                              t(chunk_row, np.int32), t(chunk_start, np.int64), t(chunk_len, np.int32),
-                             t(chunk_slot, np.int32), t(chunk_out, np.int64), t(row_chunk_ptr, np.int64), lens,
+                             t(chunk_slot, np.int32), t(chunk_out, np.int64), t(group_rcp, np.int64), lens,
                              groups, per_slot * gs)
         plan.chunk_start_h = np.concatenate([chunk_start, [int(pair_start[-1])]]).astype(np.int64)
         self._sweep_plans[key] = plan
         return plan
 
-    def _accumulate_sweep(self, plan, partial, st):
-        """Slot groups alternate between `sweep_streams` side streams, each with its own table, so the tail of one
-        group's launch overlaps the next group's sampling and ramp-up; joined back into the caller's stream."""
+    @staticmethod
+    def _group_records(chunk_group, chunk_row, n, groups):
+        """Chunk records are kept per slot group (one group's records live in the partial buffer at a time and are
+        folded into the row accumulators right after the group's launch).  For chunks listed in launch order:
+        chunk_out = index of the chunk's record inside its group's buffer, row-major (a row's records contiguous, in
+        launch order); group_rcp [n_groups][n + 1] = each group's row pointer into that buffer."""
+        G = len(groups)
+        key = chunk_group.astype(np.int64) * n + chunk_row
+        order = np.argsort(key, kind="stable")
+        rank = np.empty(len(key), dtype=np.int64)
+        rank[order] = np.arange(len(key), dtype=np.int64)
+        first = np.array([g[2] for g in groups], dtype=np.int64)
+        chunk_out = rank - first[chunk_group]
+        rcp = np.zeros((G, n + 1), dtype=np.int64)
+        np.cumsum(np.bincount(key, minlength=G * n).reshape(G, n), axis=1, out=rcp[:, 1:])
+        return chunk_out, rcp
+
+    def _sweep_tile_blocks(self, dim):
+        """Blocks per other mode for the L2-tiled launch order (1 = untiled).  When the sample table of ONE slot is
+        larger than the table budget (config 5: 2 x 10k rows x 16 KB = 320 MB against a 126 MB L2), the other modes'
+        index ranges are cut into nb blocks each and a slot's chunks are launched tile by tile, so the records the
+        resident CTAs gather stay inside one tile's share of the table."""
+        if self.diag:
+            return 1
+        if self.sweep_tile_blocks:
+            return int(self.sweep_tile_blocks)
+        per_slot = int(self.lib.ssvi_sweep_table_bytes(self.h, dim, 1))
+        nb = -(-per_slot // max(self.table_budget_bytes, 1))
+        rp = self.rowptr_h[dim]
+        per_pair = float(rp[-1]) / max(self.dims[dim] * int(self.noise.slots), 1)     # entries per (row, slot)
+        # short chunks cost more than the L2 misses they avoid (measured on config 5: 8 entries per chunk loses 13 %,
+        # 31 per chunk gains 5 % even with tiles of 1.3 x L2): take the finest tiling that keeps chunks long
+        while nb > 1 and per_pair / nb ** (self.N - 1) < self.sweep_tile_min_entries:
+            nb -= 1
+        return max(nb, 1)
+
+    def _plan_sweep_tiled(self, dim, slot_offset, nb):
+        """plan_sweep with the chunks of a slot launched tile by tile: one chunk per (slot, tile, row[, segment]),
+        tile = the block coordinates of the entry's other-mode rows.  Same records, same reduction (each row's
+        records are summed in (slot, tile, segment) order)."""
+        P, n, dev, N = int(self.noise.slots), self.dims[dim], self.device, self.N
+        rp = self.rowptr_h[dim]
+        lens = rp[1:] - rp[:-1]
+        off = np.zeros(n, dtype=np.int64) if slot_offset is None else np.asarray(slot_offset, dtype=np.int64) % P
+        T = nb ** (N - 1)
+        lens_d = torch.as_tensor(lens).to(dev)
+        row_of = torch.repeat_interleave(torch.arange(n, device=dev, dtype=torch.int64), lens_d)
+        b = torch.arange(int(rp[-1]), device=dev, dtype=torch.int64) - torch.as_tensor(rp[:-1]).to(dev)[row_of]
+        key = (b + torch.as_tensor(off).to(dev)[row_of]) % P                  # slot
+        del b
+        ent = self.perm[dim]
+        tile = torch.zeros_like(key)
+        for d in range(N):
+            if d == dim:
+                continue
+            bs = -(-self.dims[d] // nb)
+            tile = tile * nb + self.coords[ent, d].long() // bs
+        key = key * T + tile
+        del tile
+        key, order = torch.sort(key, stable=True)                # (slot, tile, row, b): stable keeps (row, b)
+        entry_ids = ent[order].contiguous()
+        triple = key * n + row_of[order]                         # non-decreasing
+        del key, order, row_of
+        uniq, counts = torch.unique_consecutive(triple, return_counts=True)
+        del triple
+        uniq, flat_cnt = uniq.cpu().numpy(), counts.cpu().numpy().astype(np.int64)
+        W = self.sweep_chunk_entries
+        flat_seg = (flat_cnt + W - 1) // W
+        npair = len(uniq)
+        pair_start = np.zeros(npair + 1, dtype=np.int64)
+        np.cumsum(flat_cnt, out=pair_start[1:])
+        pair_chunk = np.zeros(npair + 1, dtype=np.int64)
+        np.cumsum(flat_seg, out=pair_chunk[1:])
+        total = int(pair_chunk[-1])
+        pair_of = np.repeat(np.arange(npair, dtype=np.int64), flat_seg)
+        seg = np.arange(total, dtype=np.int64) - pair_chunk[pair_of]
+        c_cnt, c_nseg = flat_cnt[pair_of], flat_seg[pair_of]
+        base, rem = c_cnt // c_nseg, c_cnt % c_nseg
+        chunk_len = base + (seg < rem)
+        chunk_start = pair_start[pair_of] + seg * base + np.minimum(seg, rem)
+        c_key = uniq[pair_of]
+        chunk_row = c_key % n
+        chunk_slot = c_key // (n * T)
+        per_slot = int(self.lib.ssvi_sweep_table_bytes(self.h, dim, 1))
+        slot_chunk = np.searchsorted(chunk_slot, np.arange(P + 1, dtype=np.int64))
+        groups = [(s0, 1, int(slot_chunk[s0]), int(slot_chunk[s0 + 1])) for s0 in range(P)]
+        chunk_out, group_rcp = self._group_records(chunk_slot, chunk_row, n, groups)    # (row, tile, segment) per slot
+        t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a.astype(dt))).to(dev)      # noqa: E731
+        plan = SlotSweepPlan(dim, torch.arange(n, device=dev, dtype=torch.int64), lens_d, entry_ids,
+                             t(chunk_row, np.int32), t(chunk_start, np.int64), t(chunk_len, np.int32),
+                             t(chunk_slot, np.int32), t(chunk_out, np.int64), t(group_rcp, np.int64), lens,
+                             groups, per_slot)
+        plan.chunk_start_h = np.concatenate([chunk_start, [int(pair_start[-1])]]).astype(np.int64)
+        plan.tile_blocks = nb
+        return plan
+
+    def _accumulate_sweep(self, plan, st):
+        """Slot groups alternate between `sweep_streams` side streams, each with its own table, record buffer and row
+        accumulator, so the tail of one group's launch overlaps the next group's sampling and ramp-up.  Each group's
+        chunk records are folded into its stream's accumulator right after the launch (in group order per stream);
+        the streams' accumulators are added in stream order after the join.  Deterministic for a fixed plan."""
         ns = max(1, min(self.sweep_streams, len(plan.groups)))
+        n, L = plan.n_rows, self.acc_len
         tabs = [self._buf("sweep_table%d" % i, (plan.table_bytes + 7) // 8) for i in range(ns)]
+        max_chunks = max([c1 - c0 for (_, _, c0, c1) in plan.groups] + [0])
+        parts = [self._buf("sweep_partial%d" % i, max_chunks * L) for i in range(ns)]
+        accs = [self._buf("acc" if i == 0 else "sweep_acc%d" % i, n * L) for i in range(ns)]
         # simple / robust + full covariance: per-group work buffers (F, weights, si) of the three-pass path
         e_pos = plan.chunk_start_h
         max_n = max([int(e_pos[c1] - e_pos[c0]) for (_, _, c0, c1) in plan.groups] + [0])
         work_bytes = int(self.lib.ssvi_sweep_work_bytes(self.h, max_n))
         works = [self._buf("sweep_work%d" % i, (work_bytes + 7) // 8) for i in range(ns)] if work_bytes else None
+        per_call = 1 if self.diag else (2 if self.cfg["model"] == "d" else 4)
 
         def at(tensor, i):
             return ctypes.c_void_p(tensor.data_ptr() + i * tensor.element_size())
@@ -487,21 +595,32 @@ class Engine(object):
             fork.record(main)
             for s_ in self._side_streams[:ns]:
                 s_.wait_event(fork)
+        seen = [False] * ns
         for k, (s0, nsl, c0, c1) in enumerate(plan.groups):
-            stream = ctypes.c_void_p(self._side_streams[k % ns].cuda_stream) if ns > 1 else st
-            tab = tabs[k % ns]
+            i = k % ns
+            stream = ctypes.c_void_p(self._side_streams[i].cuda_stream) if ns > 1 else st
             self._call(self.lib.ssvi_sweep_accumulate, plan.dim, s0, nsl, c1 - c0, at(plan.chunk_row, c0),
                        at(plan.chunk_start, c0), at(plan.chunk_len, c0), at(plan.chunk_slot, c0),
-                       at(plan.chunk_out, c0), _ptr(plan.entry_ids), _ptr(plan.rows), _ptr(self.w_state), _ptr(tab),
-                       tab.numel() * 8, _ptr(works[k % ns]) if works else ctypes.c_void_p(0),
-                       works[k % ns].numel() * 8 if works else 0, int(e_pos[c0]), int(e_pos[c1] - e_pos[c0]),
-                       _ptr(partial), stream)
-            self.launches += (1 if self.diag else 2) if c1 > c0 else (0 if self.diag else 1)
+                       at(plan.chunk_out, c0), _ptr(plan.entry_ids), _ptr(plan.rows), _ptr(self.w_state), _ptr(tabs[i]),
+                       tabs[i].numel() * 8, _ptr(works[i]) if works else ctypes.c_void_p(0),
+                       works[i].numel() * 8 if works else 0, int(e_pos[c0]), int(e_pos[c1] - e_pos[c0]),
+                       _ptr(parts[i]), stream)
+            self._call(self.lib.ssvi_reduce_chunks_into, n, at(plan.group_rcp, k * (n + 1)), _ptr(parts[i]),
+                       _ptr(accs[i]), 1 if seen[i] else 0, stream)
+            seen[i] = True
+            self.launches += 1 + (per_call if c1 > c0 else (0 if self.diag else 1))
         if ns > 1:
             for s_ in self._side_streams[:ns]:
                 join = torch.cuda.Event()
                 join.record(s_)
                 main.wait_event(join)
+        acc = accs[0][:n * L]
+        for i in range(1, ns):
+            if seen[i]:
+                acc.add_(accs[i][:n * L])
+        if not seen[0]:
+            acc.zero_()
+        return acc
 
     # -------------------------------------------------------------------------------------------
     def _buf(self, name, numel):
@@ -514,20 +633,23 @@ class Engine(object):
     def accumulate(self, plan):
         """Stages 1-3 + in-order chunk reduction -> acc [n_rows, acc_len] (a view of a scratch buffer)."""
         assert self.noise is not None, "set_noise() first"
-        partial = self._buf("partial", plan.n_chunks * self.acc_len)
-        acc = self._buf("acc", plan.n_rows * self.acc_len)
         st = self._stream()
         ev = None
         if self.profile_events is not None:
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             ev[0].record()
         if isinstance(plan, SlotSweepPlan):
-            self._accumulate_sweep(plan, partial, st)
-        else:
-            self._call(self.lib.ssvi_accumulate, plan.dim, plan.n_chunks, _ptr(plan.chunk_row),
-                       _ptr(plan.chunk_start), _ptr(plan.chunk_len), _ptr(plan.chunk_slot0), _ptr(plan.entry_ids),
-                       _ptr(plan.rows), _ptr(self.w_state), _ptr(partial), st)
-            self.launches += 1 if plan.n_chunks else 0
+            acc = self._accumulate_sweep(plan, st)           # reduces group by group (records stay in L2)
+            if ev is not None:
+                ev[1].record()
+                self.profile_events.append((ev[0], ev[1], plan.n_entries))
+            return acc.view(plan.n_rows, self.acc_len)
+        partial = self._buf("partial", plan.n_chunks * self.acc_len)
+        acc = self._buf("acc", plan.n_rows * self.acc_len)
+        self._call(self.lib.ssvi_accumulate, plan.dim, plan.n_chunks, _ptr(plan.chunk_row),
+                   _ptr(plan.chunk_start), _ptr(plan.chunk_len), _ptr(plan.chunk_slot0), _ptr(plan.entry_ids),
+                   _ptr(plan.rows), _ptr(self.w_state), _ptr(partial), st)
+        self.launches += 1 if plan.n_chunks else 0
         if ev is not None:
             ev[1].record()
             self.profile_events.append((ev[0], ev[1], plan.n_entries))

@@ -245,6 +245,61 @@ def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W
             assert_state_close(got, want, cfg, RTOL, what="dims=%s mode %d" % (dims, dim))
 
 
+@pytest.mark.parametrize("dims,D,lik,P,W,nb,offs,model", [
+    ([7, 9, 8], 32, "normal", 3, 64, 2, False, "d"),         # config 5's kernel instance, 2 x 2 tiles per slot
+    ([7, 9, 8], 20, "bernoulli", 2, 2, 3, True, "d"),        # 3 x 3 tiles, segments of 2, shifted slots
+    ([5, 6, 4, 3], 12, "normal", 2, 64, 2, False, "d"),      # 4-way: 2 x 2 x 2 tiles
+    ([7, 9, 8], 30, "poisson", 2, 4, 2, False, "robust"),    # three-pass path over tiled chunks
+])
+def test_sweep_l2_tiled_launch_order_matches_untiled(dims, D, lik, P, W, nb, offs, model):
+    """L2-tiled launch order (one chunk per (slot, tile of other-mode blocks, row[, segment])): the same entry set,
+    the same per-row accumulators as the untiled sweep up to summation order, counts bit-exact."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(D * 77 + P + nb)
+    N = len(dims)
+    cfg = so.make_config(model, lik, D, diag=False, k1=64, k2=4, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, lik, dims, int(0.7 * np.prod(dims)))
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    pool = so.make_tape(rng, cfg, N, P)
+    for dim in range(N):
+        off = rng.integers(0, 50, size=dims[dim]) if offs else None
+        accs, states = [], []
+        for blocks in (1, nb):
+            eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, chunk_entries=3,
+                         sweep_chunk_entries=W, table_budget_bytes=1, sweep_tile_blocks=blocks)
+            eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=False))
+            engine_load_state(eng, st0)
+            plan = eng.plan_sweep(dim, off)
+            assert plan.tile_blocks == blocks and len(plan.groups) == P
+            np.testing.assert_array_equal(np.sort(plan.entry_ids.cpu().numpy()), np.sort(perm[dim]))
+            if blocks > 1:                              # every chunk's entries lie in ONE tile, slot and row
+                ids = plan.entry_ids.cpu().numpy()
+                cs, cl = plan.chunk_start.cpu().numpy(), plan.chunk_len.cpu().numpy()
+                cr = plan.chunk_row.cpu().numpy()
+                assert cl.sum() == len(ids) and cl.min() >= 1
+                for c in range(plan.n_chunks):
+                    e = coords[ids[cs[c]:cs[c] + cl[c]]]
+                    assert np.all(e[:, dim] == cr[c])
+                    for d in range(N):
+                        if d != dim:
+                            blk = e[:, d] // -(-dims[d] // blocks)
+                            assert np.all(blk == blk[0])
+                co = plan.chunk_out.cpu().numpy()
+                for (_, _, c0, c1) in plan.groups:      # record slots: a permutation inside every group's buffer
+                    assert sorted(co[c0:c1].tolist()) == list(range(c1 - c0))
+            acc = eng.accumulate(plan).cpu().numpy().copy()
+            eng.row_update(plan, eng.accumulate(plan))
+            eng.check_flags()
+            accs.append(acc)
+            states.append(engine_dump_state(eng, st0))
+            eng.close()
+        scale = np.abs(accs[0]).max()
+        np.testing.assert_allclose(accs[1], accs[0], rtol=1e-9, atol=1e-12 * scale)
+        np.testing.assert_array_equal(accs[1][:, -1], np.diff(rowptr[dim]))
+        assert_state_close(states[1], states[0], cfg, 1e-9, what="tiled dims=%s mode %d" % (dims, dim))
+
+
 @pytest.mark.parametrize("dims,D,k1,model,lik,P,W,offs", [
     ([6, 5, 4], 50, 64, "simple", "normal", 4, 64, False),       # BASELINE config 4's kernel instance (3-way slice)
     ([4, 3, 3, 3], 50, 64, "simple", "normal", 3, 64, False),    # config 4: 4-way, three other modes
