@@ -231,6 +231,23 @@ int ssvi_hyper_reduce(SsviHandle* h, int32_t dim, double* out /*double[3]*/, voi
  * entries int32 [n][N]. */
 int ssvi_predict_mean(SsviHandle* h, const int32_t* entries, int64_t n, double* out, void* stream);
 
+/* Per-entry Monte-Carlo estimators of the report path, from the bound noise pool (entry e reads slot
+ * (slot0 + e) mod P; mode 0 draws from z_own, mode d >= 1 from z_other[.][d-1]; k1 draws, k2 noise-layer draws):
+ *   what = SSVI_EST_EXPECTED_OBS (0)  out[e] = mean link(fs)        estimate_expected_observation_via_sampling (:1168-1189)
+ *   what = SSVI_EST_LOG_PDF      (1)  out[e] = mean log_pdf(y, fs)  estimate_expectation_term_vlb (:889-908)
+ *   what = SSVI_EST_PDF          (2)  out[e] = mean pdf(y, fs)      estimate_negative_log_likelihood (:939-964) before -log
+ *   what = SSVI_EST_ROBUST_VLB   (3)  out[e] = mean_i log mean_k pdf(y, link(fs[i][k]))   SSVI_TF_robust's override of the VLB
+ *                                     term (SSVI_TF_robust.py:234-262: link before the pdf, log of the first-layer mean);
+ *                                     simple / robust models only, k1 <= 128
+ * with ms_k = sum_D prod_modes x_mode[k], fs = ms for SSVI_TF_d and ms_k + w_sigma^2 r_k z_f[i][k] otherwise.
+ * entries int32 [n][N]; ys double [n] (may be NULL for what = 0); w_state as in ssvi_accumulate. */
+#define SSVI_EST_EXPECTED_OBS 0
+#define SSVI_EST_LOG_PDF 1
+#define SSVI_EST_PDF 2
+#define SSVI_EST_ROBUST_VLB 3
+int ssvi_estimate_entries(SsviHandle* h, int32_t what, const int32_t* entries, const double* ys, int64_t n,
+                          int32_t slot0, const double* w_state, double* out, void* stream);
+
 /* Reads and clears the device flag word (synchronises `stream`).  flags_out HOST. */
 int ssvi_check_flags(SsviHandle* h, int32_t* flags_out /*HOST*/, void* stream);
 

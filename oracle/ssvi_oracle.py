@@ -450,6 +450,94 @@ def predict_mean(state, entries):
 
 
 # --------------------------------------------------------------------------------------
+# Report-path estimators
+# --------------------------------------------------------------------------------------
+def log_pdf(lik, y, f, s):
+    """normal.py:29-30, bernoulli.py:38-39: log of the floored pdf; poisson.py:59-68: scipy's
+    poisson.logpmf(y, poisson_link(f)) = xlogy(y, A) - gammaln(y + 1) - A, nan_to_num."""
+    if lik == LIK_POISSON:
+        A = poisson_link(f)
+        with np.errstate(all="ignore"):
+            xl = np.where(y == 0, 0.0, y * np.log(A))
+            return np.nan_to_num(xl - math.lgamma(float(y) + 1.0) - A)
+    return np.log(pdf(lik, y, f, s))
+
+
+def link_fun(lik, f):
+    """SSVI_TF_interface.py:60-75."""
+    if lik == LIK_NORMAL:
+        return f
+    if lik == LIK_BERNOULLI:
+        return sigmoid(f)
+    return poisson_link(f)
+
+
+EST_EXPECTED_OBS, EST_LOG_PDF, EST_PDF, EST_ROBUST_VLB = 0, 1, 2, 3
+
+
+def estimate_entries(state, cfg, what, entries, ys, pool, slot0=0):
+    """The shared sampling pattern of estimate_expected_observation_via_sampling (:1168-1189),
+    estimate_expectation_term_vlb (:889-908) and estimate_negative_log_likelihood (:939-964): for EVERY mode of
+    the entry k draws x = m + L z, ms_k = sum_D prod_modes x; fs = ms (SSVI_TF_d) or
+    normal(ms, rayleigh(w_sigma^2, (k,)), size=(k2, k)); mean over all draws of link(fs) / log_pdf(y, fs) /
+    pdf(y, fs).  SSVI_TF_robust overrides the VLB term (SSVI_TF_robust.py:234-262): the link is applied BEFORE the
+    pdf, the pdf is averaged over the first-layer draws for each second-layer draw, and the logs are averaged:
+    mean_i log mean_k pdf(y, link(fs[i][k])) (EST_ROBUST_VLB).  pool: Tape of P slots -- entry e reads slot
+    (slot0 + e) mod P, mode 0 z_own, mode d >= 1 z_other[:, d-1]."""
+    P = pool.z_own.shape[0]
+    N = entries.shape[1]
+    lik, s = cfg["likelihood"], cfg["likelihood_param"]
+    out = np.zeros(len(entries))
+    for e, entry in enumerate(entries):
+        sl = (slot0 + e) % P
+        prod = np.ones((cfg["k1"], cfg["D"]))
+        for d in range(N):
+            m, S = get_vector_distribution(state, cfg, d, entry[d])
+            z = pool.z_own[sl] if d == 0 else pool.z_other[sl, d - 1]
+            prod = prod * (m + z @ _chol(cfg, S).T)
+        ms = prod.sum(axis=1)
+        if cfg["noise_added"]:
+            ws = state["w_sigma"] ** 2 * pool.r_w[sl]
+            fs = ms[None, :] + ws[None, :] * pool.z_f[sl]
+        else:
+            fs = ms
+        y = None if ys is None else ys[e]
+        if what == EST_EXPECTED_OBS:
+            out[e] = np.mean(link_fun(lik, fs))
+        elif what == EST_LOG_PDF:
+            out[e] = np.mean(log_pdf(lik, y, fs, s))
+        elif what == EST_PDF:
+            out[e] = np.mean(pdf(lik, y, fs, s))
+        else:
+            out[e] = np.mean(np.log(np.mean(pdf(lik, y, link_fun(lik, fs), s), axis=1)))
+    return out
+
+
+def estimate_vlb(state, cfg, entries, ys, pool):
+    """estimate_vlb (:874-883): (sum of the expectation terms, KL)."""
+    what = EST_ROBUST_VLB if cfg["model"] == "robust" else EST_LOG_PDF
+    return float(estimate_entries(state, cfg, what, entries, ys, pool).sum()), estimate_KL_divergence(state, cfg)
+
+
+def estimate_negative_log_likelihood(state, cfg, entries, ys, pool):
+    """(:939-964): -sum_e log mean pdf."""
+    return float(-np.log(estimate_entries(state, cfg, EST_PDF, entries, ys, pool)).sum())
+
+
+def estimate_KL_divergence(state, cfg):
+    """(:911-936).  The loop OVERWRITES KL (:923-925), so the value returned is the divergence of the LAST row of
+    the LAST mode from N(pmu, pSigma[dim] I) -- reproduced as is."""
+    dim = len(state["params"]) - 1
+    col = state["params"][dim].shape[0] - 1
+    m, S = get_vector_distribution(state, cfg, dim, col)
+    S0 = np.diag(S) if cfg["diag"] else S
+    D = cfg["D"]
+    sigma = state["pSigma"][dim]
+    dm = state["pmu"] - m
+    return float(0.5 * (np.trace(S0) / sigma + dm @ dm / sigma - D + np.log(sigma ** D / np.linalg.det(S0))))
+
+
+# --------------------------------------------------------------------------------------
 # Index (Tensor/Tensor.py:76-83, 152-169, 251-258): per-mode CSR in COO insertion order
 # --------------------------------------------------------------------------------------
 def build_index(coords, dims):

@@ -20,6 +20,8 @@ from ..Probability.bernoulli import BernoulliDistribution
 from ..Probability.normal import NormalDistribution
 from ..Probability.poisson import PoissonDistribution
 
+EST_EXPECTED_OBS, EST_LOG_PDF, EST_PDF, EST_ROBUST_VLB = 0, 1, 2, 3      # include/ssvi_b200.h: SSVI_EST_*
+
 
 class SSVI_TF(object):
     _model = "d"          # "d" | "simple" | "robust"; set by the subclasses
@@ -345,39 +347,50 @@ class SSVI_TF(object):
     def predict_entry(self, entry):
         return self.predict_entries(np.asarray(entry)[None, :])[0]
 
-    def _expected_observation_via_sampling(self, entries_dev, chunk=1 << 16):
-        """estimate_expected_observation_via_sampling (:1168-1189), batched with torch on the device:
-        predict_num_samples draws of every factor row, Hadamard product, (noise layer,) link, mean.
-        Off the timed path."""
-        eng, S = self.engine, self.predict_num_samples
-        g = torch.Generator(device=eng.device)
-        g.manual_seed(self._noise_gen_seed + 7919)
-        out = []
-        for s in range(0, entries_dev.shape[0], chunk):
-            e = entries_dev[s:s + chunk].long()
-            ms = torch.ones((e.shape[0], S, self.D), device=eng.device, dtype=torch.float64)
-            for d in range(self.order):
-                rows = eng.params[d][e[:, d]]                        # (n, D+1, D) | (n, 2, D)
-                z = torch.randn((e.shape[0], S, self.D), generator=g, device=eng.device, dtype=torch.float64)
-                if self.diag:
-                    x = rows[:, None, 0, :] + z * torch.sqrt(rows[:, None, 1, :])
-                else:
-                    x = rows[:, None, 0, :] + torch.einsum("nsc,ndc->nsd", z, torch.linalg.cholesky(rows[:, 1:, :]))
-                ms = ms * x
-            f = ms.sum(dim=2)                                        # (n, S)
-            if self.noise_added:
-                u = torch.rand(f.shape, generator=g, device=eng.device, dtype=torch.float64).clamp_(min=1e-300)
-                ws = (self.w_sigma ** 2) * torch.sqrt(-2.0 * torch.log(u))
-                zf = torch.randn((f.shape[0], S, S), generator=g, device=eng.device, dtype=torch.float64)
-                f = (f[:, None, :] + ws[:, None, :] * zf).reshape(f.shape[0], -1)
-            if self.likelihood_type == "bernoulli":
-                p = torch.sigmoid(f)
-            elif self.likelihood_type == "poisson":
-                p = torch.clamp(torch.log(1.0 + torch.exp(f)), min=1e-8)
-            else:
-                p = f
-            out.append(p.mean(dim=1))
-        return torch.cat(out) if out else torch.zeros(0, device=eng.device, dtype=torch.float64)
+    def _expected_observation_via_sampling(self, entries_dev):
+        """estimate_expected_observation_via_sampling (:1168-1189) for a batch of entries on the device
+        (ssvi_estimate_entries): draws of every factor row from the noise pool, Hadamard product, (noise layer,)
+        link, mean.  Uses the pool's k1 / k2 draws where the reference uses predict_num_samples."""
+        if self.engine.noise is None:
+            self.fresh_noise()
+        return self.engine.estimate_entries(EST_EXPECTED_OBS, entries_dev.contiguous())
+
+    # ---------------------------------------------------------------------------------------------
+    # VLB / KL / NLL estimators of the detailed report (:874-964), SURVEY.md 8f rank 4
+    # ---------------------------------------------------------------------------------------------
+    def _estimate(self, what, entries, vals):
+        entries = np.asarray(entries, dtype=np.int64).reshape(-1, self.order)
+        if self.engine.noise is None:
+            self.fresh_noise()
+        dev = torch.as_tensor(entries.astype(np.int32)).to(self.engine.device)
+        ys = torch.as_tensor(np.asarray(vals, dtype=np.float64).reshape(-1)).to(self.engine.device)
+        return self.engine.estimate_entries(what, dev, ys)
+
+    def estimate_expectation_term_vlb(self, entry, val):
+        """(:889-908; SSVI_TF_robust.py:234-262 for the robust model) for one entry."""
+        what = EST_ROBUST_VLB if self._model == "robust" else EST_LOG_PDF
+        return float(self._estimate(what, np.asarray(entry)[None, :], [val]).item())
+
+    def estimate_KL_divergence(self):
+        """(:911-936).  The reference's loop overwrites KL instead of summing (:923-925): the value is the divergence
+        of the LAST row of the LAST mode from N(pmu, pSigma[dim] I) -- kept as is."""
+        dim = self.order - 1
+        m, S = self.posterior.get_vector_distribution(dim, self.dims[dim] - 1)
+        m, S = np.asarray(m, dtype=np.float64), np.asarray(S, dtype=np.float64)
+        S0 = np.diag(S) if self.diag else S
+        sigma = float(self.pSigma[dim])
+        dm = self.pmu - m
+        return float(0.5 * (np.trace(S0) / sigma + dm @ dm / sigma - self.D
+                            + np.log(sigma ** self.D / np.linalg.det(S0))))
+
+    def estimate_vlb(self, entries, values):
+        """(:874-883): (sum over entries of the expectation term, KL)."""
+        what = EST_ROBUST_VLB if self._model == "robust" else EST_LOG_PDF
+        return float(self._estimate(what, entries, values).sum().item()), self.estimate_KL_divergence()
+
+    def estimate_negative_log_likelihood(self, entries, vals):
+        """(:939-964): -sum_e log mean_draws pdf(y_e, fs)."""
+        return float(-torch.log(self._estimate(EST_PDF, entries, vals)).sum().item())
 
     def evaluate_error(self, entries, vals):
         """(rsme, error) over entries not touching an unlearned row (:997-1030)."""
@@ -405,8 +418,7 @@ class SSVI_TF(object):
         return self.evaluate_error(self.tensor.test_entries, self.tensor.test_vals)
 
     # ---------------------------------------------------------------------------------------------
-    # reports (:764-871).  The VLB / NLL columns of the detailed report are SURVEY.md 8f rank 4 (not
-    # built yet): the detailed report prints the optimisation columns and leaves those as nan.
+    # reports (:764-871)
     # ---------------------------------------------------------------------------------------------
     def _print_header(self, detailed):
         self.header_printed = True
@@ -419,7 +431,7 @@ class SSVI_TF(object):
         print("eta = ", self.eta, " cov eta = ", self.cov_eta, " sigma eta = ", self.sigma_eta)
         if detailed:
             print("iteration |   time   | test_mae |rel-te-err|train_mae |rel-tr-err|   d_mean  |   d_cov  |avg_grad_m|avg_grad_c|"
-                  + ("   dw   |" if self.noise_added else ""))
+                  " test_nll | train_nll |    VLB   |  E-term  |    KL    " + ("|   dw   |" if self.noise_added else ""))
         else:
             print("iteration |   time   |  test_err  |  test_mae  |  trainerr  |  trainmae |")
 
@@ -439,6 +451,11 @@ class SSVI_TF(object):
         cols = [iteration, np.around(time.time() - start, 2), np.around(mae_test, dec), np.around(error_test, dec),
                 np.around(mae_train, dec), np.around(error_train, dec), np.around(mean_change, dec),
                 np.around(cov_change, dec), np.around(avg_grad_m, dec), np.around(avg_grad_c, dec)]
+        E_term, KL = self.estimate_vlb(self.tensor.train_entries, self.tensor.train_vals)       # :793
+        test_nll = self.estimate_negative_log_likelihood(self.tensor.test_entries, self.tensor.test_vals)
+        train_nll = self.estimate_negative_log_likelihood(self.tensor.train_entries, self.tensor.train_vals)
+        cols += [np.around(test_nll, 2), np.around(train_nll, 2), np.around(E_term - KL), np.around(E_term, 3),
+                 np.around(KL, 3)]                                                             # :821-826
         if self.noise_added:
             cols.append(np.around(self.w_changes, dec))
         print(" ".join("{:^10}".format(c) for c in cols))

@@ -59,6 +59,7 @@ SIGNATURES = {
     "ssvi_row_update": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _I32, _I32, _P, _P]),
     "ssvi_sigma_update": (ctypes.c_int, [_P, _I64, _P, _P, _P, _P]),
     "ssvi_hyper_reduce": (ctypes.c_int, [_P, _I32, _P, _P]),
+    "ssvi_estimate_entries": (ctypes.c_int, [_P, _I32, _P, _P, _I64, _I32, _P, _P, _P]),
     "ssvi_predict_mean": (ctypes.c_int, [_P, _P, _I64, _P, _P]),
     "ssvi_check_flags": (ctypes.c_int, [_P, ctypes.POINTER(_I32), _P]),
 }

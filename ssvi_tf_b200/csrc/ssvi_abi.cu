@@ -5,6 +5,7 @@
 
 #include "accumulate_memo2.cuh"
 #include "accumulate_diag.cuh"
+#include "estimate.cuh"
 #include "row_update.cuh"
 
 #define SSVI_VERSION_STR "ssvi_b200 0.1 sm_100a"
@@ -680,6 +681,34 @@ extern "C" int ssvi_predict_mean(SsviHandle* h, const int32_t* entries, int64_t 
   const int64_t blocks = (n * 32 + threads - 1) / threads;
   double** P = h->params;
   predict_mean_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(v, nullptr, entries, n, out, P[0], P[1], P[2], P[3], P[4], P[5], P[6], P[7]);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+extern "C" int ssvi_estimate_entries(SsviHandle* h, int32_t what, const int32_t* entries, const double* ys, int64_t n,
+                                     int32_t slot0, const double* w_state, double* out, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (!h->state_bound) return fail(h, SSVI_E_STATE, "estimate_entries: state not bound%s");
+  if (!h->noise_bound) return fail(h, SSVI_E_STATE, "estimate_entries: noise not bound%s");
+  if (what < SSVI_EST_EXPECTED_OBS || what > SSVI_EST_ROBUST_VLB) return fail(h, SSVI_E_INVALID, "estimate_entries: bad estimator%s");
+  if (what == SSVI_EST_ROBUST_VLB && (h->cfg.model == SSVI_MODEL_D || h->cfg.k1 > 128))
+    return fail(h, SSVI_E_INVALID, "estimate_entries: SSVI_EST_ROBUST_VLB needs a noise-layer model and k1 <= 128%s");
+  if (n == 0) return SSVI_OK;
+  if (n < 0 || !entries || !out || slot0 < 0) return fail(h, SSVI_E_INVALID, "estimate_entries: bad argument%s");
+  if (what != SSVI_EST_EXPECTED_OBS && !ys) return fail(h, SSVI_E_INVALID, "estimate_entries: ys required%s");
+  if (h->cfg.model != SSVI_MODEL_D && (!w_state || !h->r_w || !h->z_f))
+    return fail(h, SSVI_E_INVALID, "estimate_entries: w_state and the noise-layer pool are required for simple/robust%s");
+  const DevView v = make_view(h, 0);
+  const int64_t blocks = (n + 3) / 4;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (h->cfg.noise_dtype == SSVI_NOISE_F32)
+    estimate_entries_kernel<float><<<(unsigned)blocks, 128, 0, st>>>(
+        v, what, entries, ys, n, slot0, w_state, (const float*)h->z_other, (const float*)h->z_own, (const float*)h->r_w,
+        (const float*)h->z_f, out);
+  else
+    estimate_entries_kernel<double><<<(unsigned)blocks, 128, 0, st>>>(
+        v, what, entries, ys, n, slot0, w_state, (const double*)h->z_other, (const double*)h->z_own,
+        (const double*)h->r_w, (const double*)h->z_f, out);
   CUDA_TRY(h, cudaGetLastError());
   return SSVI_OK;
 }

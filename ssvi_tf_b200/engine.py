@@ -682,6 +682,17 @@ class Engine(object):
         self.pSigma[dim:dim + 1].copy_(self.hyper_out[dim, 0:1])
         self.launches += 1
 
+    def estimate_entries(self, what, entries, ys=None, slot0=0):
+        """Per-entry Monte-Carlo estimator over the bound noise pool (include/ssvi_b200.h: ssvi_estimate_entries).
+        entries: int32 device tensor [n, N]; ys: float64 device tensor [n] or None."""
+        assert self.noise is not None, "set_noise() first"
+        n = int(entries.shape[0])
+        out = torch.empty((n,), device=self.device, dtype=torch.float64)
+        self._call(self.lib.ssvi_estimate_entries, int(what), _ptr(entries), _ptr(ys) if ys is not None else None, n,
+                   int(slot0), _ptr(self.w_state), _ptr(out), self._stream())
+        self.launches += 1 if n else 0
+        return out
+
     def predict_mean(self, entries):
         """entries: int32 device tensor [n, N] -> posterior-mean prediction per entry."""
         n = int(entries.shape[0])
