@@ -131,8 +131,10 @@ class SlotSweepPlan(object):
         self.dim = dim
         self.rows, self.n_obs, self.entry_ids = rows, n_obs, entry_ids
         self.chunk_row, self.chunk_start, self.chunk_len = chunk_row, chunk_start, chunk_len
-        self.chunk_slot, self.chunk_out = chunk_slot, chunk_out     # chunk_out: record index inside the group's buffer
-        self.group_rcp = group_rcp                                  # int64 [n_groups][n_rows + 1] device
+        self.chunk_slot, self.chunk_out = chunk_slot, chunk_out     # chunk_out: record index inside the batch's buffer
+        self.group_rcp = group_rcp                                  # int64 [n_batches][n_rows + 1] device
+        self.batch_of = self.batch_last = None                      # host [n_groups]: reduction batch of every group
+        self.max_batch_records = 0
         self.n_rows = int(rows.numel())
         self.n_chunks = int(chunk_row.numel())
         self.batch_sizes = batch_sizes
@@ -148,7 +150,7 @@ class Engine(object):
 
     def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16,
                  kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64, sweep_streams=2,
-                 sweep_tile_blocks=0, sweep_tile_min_entries=24.0):
+                 sweep_tile_blocks=0, sweep_tile_min_entries=24.0, record_budget_bytes=256 << 20):
         """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
         cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
         if not torch.cuda.is_available():
@@ -166,6 +168,7 @@ class Engine(object):
         self.sweep_streams = int(sweep_streams)
         self.sweep_tile_blocks = int(sweep_tile_blocks)        # 0: chosen from the table budget (_sweep_tile_blocks)
         self.sweep_tile_min_entries = float(sweep_tile_min_entries)
+        self.record_budget_bytes = int(record_budget_bytes)    # chunk records kept per stream before they are folded
         self._side_streams = []
         self.noise_dtype = noise_dtype
         if cfg["mean_update"] not in UPDATE_IDS or cfg["cov_update"] not in UPDATE_IDS:
@@ -461,32 +464,56 @@ class Engine(object):
         slot_chunk = pair_chunk[::n]                             # first chunk of each slot (+ total)
         groups = [(s0, min(gs, P - s0), int(slot_chunk[s0]), int(slot_chunk[min(s0 + gs, P)]))
                   for s0 in range(0, P, gs)]
-        chunk_out, group_rcp = self._group_records(chunk_slot // gs, chunk_row, n, groups)
+        chunk_out, group_rcp, batch_of, batch_last, max_rec = self._group_records(chunk_slot // gs, chunk_row, n, groups)
         t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a.astype(dt))).to(dev)      # noqa: E731
         plan = SlotSweepPlan(dim, torch.arange(n, device=dev, dtype=torch.int64), lens_d, entry_ids,
                              t(chunk_row, np.int32), t(chunk_start, np.int64), t(chunk_len, np.int32),
                              t(chunk_slot, np.int32), t(chunk_out, np.int64), t(group_rcp, np.int64), lens,
                              groups, per_slot * gs)
         plan.chunk_start_h = np.concatenate([chunk_start, [int(pair_start[-1])]]).astype(np.int64)
+        plan.batch_of, plan.batch_last, plan.max_batch_records = batch_of, batch_last, max_rec
         self._sweep_plans[key] = plan
         return plan
 
-    @staticmethod
-    def _group_records(chunk_group, chunk_row, n, groups):
-        """Chunk records are kept per slot group (one group's records live in the partial buffer at a time and are
-        folded into the row accumulators right after the group's launch).  For chunks listed in launch order:
-        chunk_out = index of the chunk's record inside its group's buffer, row-major (a row's records contiguous, in
-        launch order); group_rcp [n_groups][n + 1] = each group's row pointer into that buffer."""
+    def _group_records(self, chunk_group, chunk_row, n, groups):
+        """Chunk records are folded into the row accumulators batch by batch: a batch = consecutive slot groups of ONE
+        stream (groups alternate between the streams) whose records fit the record budget; its records live in that
+        stream's buffer until the batch's last group has been launched.  For chunks listed in launch order returns
+        chunk_out (index of the chunk's record inside its batch's buffer, row-major: a row's records contiguous, in
+        launch order), batch_rcp [n_batches][n + 1] (each batch's row pointer into the buffer), batch_of [n_groups],
+        batch_last [n_groups] (group closes its batch) and the largest batch's record count."""
         G = len(groups)
-        key = chunk_group.astype(np.int64) * n + chunk_row
+        ns = max(1, min(self.sweep_streams, G))
+        cnt = np.array([g[3] - g[2] for g in groups], dtype=np.int64)
+        cap = max(self.record_budget_bytes // (self.acc_len * 8), 1)
+        batch_of = np.zeros(G, dtype=np.int64)
+        batch_last = np.zeros(G, dtype=bool)
+        nbatch = 0
+        for i in range(ns):
+            cur, prev = 0, None
+            for k in range(i, G, ns):
+                if prev is not None and cur + cnt[k] > cap:
+                    batch_last[prev] = True
+                    nbatch += 1
+                    cur = 0
+                batch_of[k] = nbatch
+                cur += cnt[k]
+                prev = k
+            if prev is not None:
+                batch_last[prev] = True
+                nbatch += 1
+        cb = batch_of[chunk_group]
+        key = cb * n + chunk_row
         order = np.argsort(key, kind="stable")
         rank = np.empty(len(key), dtype=np.int64)
         rank[order] = np.arange(len(key), dtype=np.int64)
-        first = np.array([g[2] for g in groups], dtype=np.int64)
-        chunk_out = rank - first[chunk_group]
-        rcp = np.zeros((G, n + 1), dtype=np.int64)
-        np.cumsum(np.bincount(key, minlength=G * n).reshape(G, n), axis=1, out=rcp[:, 1:])
-        return chunk_out, rcp
+        per_batch = np.bincount(cb, minlength=nbatch)
+        first = np.zeros(nbatch + 1, dtype=np.int64)
+        np.cumsum(per_batch, out=first[1:])
+        chunk_out = rank - first[cb]
+        rcp = np.zeros((nbatch, n + 1), dtype=np.int64)
+        np.cumsum(np.bincount(key, minlength=nbatch * n).reshape(nbatch, n), axis=1, out=rcp[:, 1:])
+        return chunk_out, rcp, batch_of, batch_last, int(per_batch.max()) if nbatch else 0
 
     def _sweep_tile_blocks(self, dim):
         """Blocks per other mode for the L2-tiled launch order (1 = untiled).  When the sample table of ONE slot is
@@ -557,13 +584,14 @@ class Engine(object):
         per_slot = int(self.lib.ssvi_sweep_table_bytes(self.h, dim, 1))
         slot_chunk = np.searchsorted(chunk_slot, np.arange(P + 1, dtype=np.int64))
         groups = [(s0, 1, int(slot_chunk[s0]), int(slot_chunk[s0 + 1])) for s0 in range(P)]
-        chunk_out, group_rcp = self._group_records(chunk_slot, chunk_row, n, groups)    # (row, tile, segment) per slot
+        chunk_out, group_rcp, batch_of, batch_last, max_rec = self._group_records(chunk_slot, chunk_row, n, groups)
         t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a.astype(dt))).to(dev)      # noqa: E731
         plan = SlotSweepPlan(dim, torch.arange(n, device=dev, dtype=torch.int64), lens_d, entry_ids,
                              t(chunk_row, np.int32), t(chunk_start, np.int64), t(chunk_len, np.int32),
                              t(chunk_slot, np.int32), t(chunk_out, np.int64), t(group_rcp, np.int64), lens,
                              groups, per_slot)
         plan.chunk_start_h = np.concatenate([chunk_start, [int(pair_start[-1])]]).astype(np.int64)
+        plan.batch_of, plan.batch_last, plan.max_batch_records = batch_of, batch_last, max_rec
         plan.tile_blocks = nb
         return plan
 
@@ -575,8 +603,7 @@ class Engine(object):
         ns = max(1, min(self.sweep_streams, len(plan.groups)))
         n, L = plan.n_rows, self.acc_len
         tabs = [self._buf("sweep_table%d" % i, (plan.table_bytes + 7) // 8) for i in range(ns)]
-        max_chunks = max([c1 - c0 for (_, _, c0, c1) in plan.groups] + [0])
-        parts = [self._buf("sweep_partial%d" % i, max_chunks * L) for i in range(ns)]
+        parts = [self._buf("sweep_partial%d" % i, plan.max_batch_records * L) for i in range(ns)]
         accs = [self._buf("acc" if i == 0 else "sweep_acc%d" % i, n * L) for i in range(ns)]
         # simple / robust + full covariance: per-group work buffers (F, weights, si) of the three-pass path
         e_pos = plan.chunk_start_h
@@ -605,10 +632,12 @@ class Engine(object):
                        tabs[i].numel() * 8, _ptr(works[i]) if works else ctypes.c_void_p(0),
                        works[i].numel() * 8 if works else 0, int(e_pos[c0]), int(e_pos[c1] - e_pos[c0]),
                        _ptr(parts[i]), stream)
-            self._call(self.lib.ssvi_reduce_chunks_into, n, at(plan.group_rcp, k * (n + 1)), _ptr(parts[i]),
-                       _ptr(accs[i]), 1 if seen[i] else 0, stream)
-            seen[i] = True
-            self.launches += 1 + (per_call if c1 > c0 else (0 if self.diag else 1))
+            self.launches += per_call if c1 > c0 else (0 if self.diag else 1)
+            if plan.batch_last[k]:                           # fold the batch's records into this stream's accumulator
+                self._call(self.lib.ssvi_reduce_chunks_into, n, at(plan.group_rcp, int(plan.batch_of[k]) * (n + 1)),
+                           _ptr(parts[i]), _ptr(accs[i]), 1 if seen[i] else 0, stream)
+                seen[i] = True
+                self.launches += 1
         if ns > 1:
             for s_ in self._side_streams[:ns]:
                 join = torch.cuda.Event()

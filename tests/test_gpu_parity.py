@@ -267,7 +267,8 @@ def test_sweep_l2_tiled_launch_order_matches_untiled(dims, D, lik, P, W, nb, off
         accs, states = [], []
         for blocks in (1, nb):
             eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, chunk_entries=3,
-                         sweep_chunk_entries=W, table_budget_bytes=1, sweep_tile_blocks=blocks)
+                         sweep_chunk_entries=W, table_budget_bytes=1, sweep_tile_blocks=blocks,
+                         record_budget_bytes=(1 if blocks == 1 else 40 * 8 * (D + D * D + 2)))
             eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=False))
             engine_load_state(eng, st0)
             plan = eng.plan_sweep(dim, off)
@@ -286,8 +287,10 @@ def test_sweep_l2_tiled_launch_order_matches_untiled(dims, D, lik, P, W, nb, off
                             blk = e[:, d] // -(-dims[d] // blocks)
                             assert np.all(blk == blk[0])
                 co = plan.chunk_out.cpu().numpy()
-                for (_, _, c0, c1) in plan.groups:      # record slots: a permutation inside every group's buffer
-                    assert sorted(co[c0:c1].tolist()) == list(range(c1 - c0))
+                for bt in np.unique(plan.batch_of):     # record slots: a permutation inside every batch's buffer
+                    got = np.concatenate([co[c0:c1] for k, (_, _, c0, c1) in enumerate(plan.groups)
+                                          if plan.batch_of[k] == bt])
+                    assert sorted(got.tolist()) == list(range(len(got))) and len(got) <= plan.max_batch_records
             acc = eng.accumulate(plan).cpu().numpy().copy()
             eng.row_update(plan, eng.accumulate(plan))
             eng.check_flags()
