@@ -105,7 +105,8 @@ class DeviceTensorData(object):
     """Synthetic tensor of a BASELINE config, generated on the device: uniform distinct
     cells, ground-truth CP factors U_d ~ N(mu_d, 0.1 I) of rank D, values through the data link."""
 
-    def __init__(self, c, device, seed, scale=1.0):
+    def __init__(self, c, device, seed, scale=1.0, window=None):
+        """window: [(lo, hi)] per mode -- this shard's block of the index space (None: the whole space)."""
         import torch
         self.datatype = DATATYPE[c["lik"]]
         self.dims = list(c["dims"])
@@ -113,7 +114,9 @@ class DeviceTensorData(object):
         nnz = max(int(c["nnz"] * scale), 1000)
         g = torch.Generator(device=device)
         g.manual_seed(seed)
-        total = int(np.prod(self.dims))
+        window = window or [(0, n) for n in self.dims]
+        ext = [hi - lo for lo, hi in window]
+        total = int(np.prod(ext))
         if nnz >= total:                      # dense (config 1): every cell, shuffled
             lin = torch.randperm(total, generator=g, device=device)
             nnz = total
@@ -124,8 +127,8 @@ class DeviceTensorData(object):
         coords = torch.empty((nnz, N), dtype=torch.int32, device=device)
         rem = lin
         for d in range(N - 1, -1, -1):
-            coords[:, d] = (rem % self.dims[d]).to(torch.int32)
-            rem = rem // self.dims[d]
+            coords[:, d] = (rem % ext[d] + window[d][0]).to(torch.int32)
+            rem = rem // ext[d]
         del lin, rem
         if c["lik"] == "bernoulli":
             mus = np.linspace(-1, 1, N)          # binary_tensor.py:12-19
@@ -133,7 +136,9 @@ class DeviceTensorData(object):
             mus = np.linspace(0, 1.5, N)         # count_tensor.py:16-23
         else:
             mus = [0.5, 1.0, 0.2, 0.5][:N]
-        Us = [float(mus[d]) + math.sqrt(0.1) * torch.randn((self.dims[d], D), generator=g, device=device)
+        gf = torch.Generator(device=device)              # ground-truth factors: the same on every rank
+        gf.manual_seed(319 + N * 1000 + D)
+        Us = [float(mus[d]) + math.sqrt(0.1) * torch.randn((self.dims[d], D), generator=gf, device=device)
               for d in range(N)]
         vals = torch.empty((nnz,), dtype=torch.float64, device=device)
         step = 1 << 24                                   # values in slabs: [nnz, D] at 1e9 entries would not fit
@@ -159,6 +164,26 @@ class DeviceTensorData(object):
         self.test_vals = vals[n_train:].cpu().numpy()
         self.max_count = int(vals.max().item()) if c["lik"] == "poisson" else 0
         self.min_count = int(vals.min().item()) if c["lik"] == "poisson" else 0
+
+
+def shard_window(dims, rank, world):
+    """Index-space block of `rank` when the observed entries are sharded along a grid of blocks (world = 2^k ranks:
+    the modes are halved in turn, 8 ranks -> 2 x 2 x 2).  Every rank then gathers only its blocks' rows of the other
+    modes and keeps whole (row, slot) chunks of the rows it owns."""
+    grid = [1] * len(dims)
+    w, d = world, 0
+    while w > 1:
+        assert w % 2 == 0, "block sharding needs a power-of-two world size"
+        grid[d % len(dims)] *= 2
+        w //= 2
+        d += 1
+    win, r = [], rank
+    for d_, n in enumerate(dims):
+        b = r % grid[d_]
+        r //= grid[d_]
+        step = -(-n // grid[d_])
+        win.append((b * step, min(n, (b + 1) * step)))
+    return win, grid
 
 
 def build_model(c, data, device, group, chunk_entries, noise_slots, engine_kwargs=None):
@@ -281,6 +306,11 @@ def main():
     ap.add_argument("--table-mb", type=float, default=96.0, help="sample-table budget per call (L2-resident)")
     ap.add_argument("--sweep-chunk", type=int, default=64, help="max entries of one (row, slot) chunk")
     ap.add_argument("--sweep-streams", type=int, default=3, help="side streams the slot groups alternate between")
+    ap.add_argument("--shard", default="random", choices=["random", "blocks"],
+                    help="N > 1: which entries a rank holds -- random: its own uniform sample of the whole index space; "
+                         "blocks: a uniform sample of its block of the index space (shard_window)")
+    ap.add_argument("--strong", action="store_true",
+                    help="strong scaling: the config's nnz (x --scale) is divided over the ranks")
     ap.add_argument("--tile-blocks", type=int, default=0,
                     help="L2 tiling of the sweep launch order: blocks per other mode (0 = from the table budget, 1 = off)")
     ap.add_argument("--batch-size", type=int, default=0,
@@ -307,7 +337,9 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device(device))
         group = dist.group.WORLD
-    data = DeviceTensorData(c, device, seed=319 + int(args.config[1]) + 1000 * rank, scale=args.scale)
+    window, grid = (shard_window(c["dims"], rank, world) if args.shard == "blocks" and world > 1 else (None, None))
+    data = DeviceTensorData(c, device, seed=319 + int(args.config[1]) + 1000 * rank,
+                            scale=args.scale / (world if args.strong else 1), window=window)
     model = build_model(c, data, device, group, args.chunk_entries, args.noise_slots,
                         dict(table_budget_bytes=int(args.table_mb * (1 << 20)), sweep_chunk_entries=args.sweep_chunk,
                              sweep_streams=args.sweep_streams, sweep_tile_blocks=args.tile_blocks))
@@ -478,7 +510,8 @@ def main():
                              "%.1f s, 1 thread (oracle/ssvi_oracle.py)" % (u // 128, w)}
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong" if args.strong else "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": c["desc"], "config_id": args.config, "nnz_train_per_gpu": nnz_train,
                        "units_per_step_per_gpu": units_per_step,
@@ -490,7 +523,9 @@ def main():
                                 % (model.sweep_plan(0)[0].groups[0][1], getattr(model.sweep_plan(0)[0], "tile_blocks", 1)))
                        if eng.sweep_supported and B is None else "direct (one warp per row-chunk)",
                        "l2": l2_note,
-                       "parallelism": "entries sharded x%d, all-reduce of row accumulators" % world},
+                       "parallelism": "entries sharded x%d (%s), all-reduce of row accumulators"
+                                      % (world, "index-space blocks %s" % "x".join(map(str, grid)) if grid else
+                                         "every rank a uniform sample of the whole index space")},
             "roofline": roofline, "cpu_baseline": cpu,
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks}))
     if world > 1:

@@ -225,6 +225,11 @@ class Engine(object):
             self.perm = [torch.as_tensor(p).to(self.device) for p in perm_h]
             self._perm_h = perm_h
         self._call(self.lib.ssvi_bind_data, _ptr(self.coords), _ptr(self.vals), self.nnz)
+        # index range this shard touches in every mode (a shard cut along index-space blocks touches a sub-range)
+        self.row_window = []
+        for d in range(self.N):
+            ne = np.nonzero(np.diff(self.rowptr_h[d]))[0]
+            self.row_window.append((int(ne[0]), int(ne[-1])) if len(ne) else (0, 0))
 
         # ---- state ------------------------------------------------------------------------------
         f64 = dict(device=self.device, dtype=torch.float64)
@@ -525,9 +530,13 @@ class Engine(object):
         if self.sweep_tile_blocks:
             return int(self.sweep_tile_blocks)
         per_slot = int(self.lib.ssvi_sweep_table_bytes(self.h, dim, 1))
+        others = [d for d in range(self.N) if d != dim]
+        touched = sum(self.row_window[d][1] - self.row_window[d][0] + 1 for d in others)
+        per_slot = per_slot * touched // max(sum(self.dims[d] for d in others), 1)   # the records this shard gathers
         nb = -(-per_slot // max(self.table_budget_bytes, 1))
         rp = self.rowptr_h[dim]
-        per_pair = float(rp[-1]) / max(self.dims[dim] * int(self.noise.slots), 1)     # entries per (row, slot)
+        rows_here = self.row_window[dim][1] - self.row_window[dim][0] + 1
+        per_pair = float(rp[-1]) / max(rows_here * int(self.noise.slots), 1)          # entries per (row, slot)
         # short chunks cost more than the L2 misses they avoid (measured on config 5: 8 entries per chunk loses 13 %,
         # 31 per chunk gains 5 % even with tiles of 1.3 x L2): take the finest tiling that keeps chunks long
         while nb > 1 and per_pair / nb ** (self.N - 1) < self.sweep_tile_min_entries:
@@ -553,8 +562,9 @@ class Engine(object):
         for d in range(N):
             if d == dim:
                 continue
-            bs = -(-self.dims[d] // nb)
-            tile = tile * nb + self.coords[ent, d].long() // bs
+            lo, hi = self.row_window[d]
+            bs = -(-(hi - lo + 1) // nb)
+            tile = tile * nb + (self.coords[ent, d].long() - lo) // bs
         key = key * T + tile
         del tile
         key, order = torch.sort(key, stable=True)                # (slot, tile, row, b): stable keeps (row, b)

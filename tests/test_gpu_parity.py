@@ -284,7 +284,8 @@ def test_sweep_l2_tiled_launch_order_matches_untiled(dims, D, lik, P, W, nb, off
                     assert np.all(e[:, dim] == cr[c])
                     for d in range(N):
                         if d != dim:
-                            blk = e[:, d] // -(-dims[d] // blocks)
+                            lo, hi = eng.row_window[d]
+                            blk = (e[:, d] - lo) // -(-(hi - lo + 1) // blocks)
                             assert np.all(blk == blk[0])
                 co = plan.chunk_out.cpu().numpy()
                 for bt in np.unique(plan.batch_of):     # record slots: a permutation inside every batch's buffer

@@ -1,0 +1,21 @@
+#!/bin/bash
+# config 5 (1e9 observed entries in total), strong scaling over N GPUs with block sharding: tools/gpu_c5n.sh <tag> N [pytest]
+OUT=gpurun_out; mkdir -p $OUT; TAG=$1; N=$2
+if [ "$3" = "pytest" ]; then
+  timeout 1200 python -m pytest tests -m gpu -x -q > $OUT/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 $OUT/${TAG}_pytest.log
+fi
+S0=$SECONDS
+if [ "$N" = "1" ]; then
+  timeout 1500 python bench.py --gpus 1 --config c5 --steps 3 --warmup 3 --no-cpu-baseline --strong > $OUT/${TAG}_n$N.json 2> $OUT/${TAG}_n$N.err
+else
+  timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2961$N bench.py --gpus $N --config c5 --steps 3 --warmup 3 --strong --shard blocks > $OUT/${TAG}_n$N.json 2> $OUT/${TAG}_n$N.err
+fi
+echo "N=$N rc=$? wall=$((SECONDS-S0))s"
+python - <<PY
+import json
+try:
+    d=json.loads([l for l in open("$OUT/${TAG}_n$N.json") if l.startswith("{")][-1])
+    print("  value %.4g e2e %.4g ms/step %.1f frac %.3f path %s | %s" % (d["value"], d["e2e"]["value"], d["ms_per_step"], d["roofline"]["frac"], d["config"]["path"], d["config"]["parallelism"]))
+except Exception as e:
+    print("  failed", e); print(open("$OUT/${TAG}_n$N.err").read()[-1500:])
+PY
