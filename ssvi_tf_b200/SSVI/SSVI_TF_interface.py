@@ -23,6 +23,13 @@ from ..Probability.poisson import PoissonDistribution
 EST_EXPECTED_OBS, EST_LOG_PDF, EST_PDF, EST_ROBUST_VLB = 0, 1, 2, 3      # include/ssvi_b200.h: SSVI_EST_*
 
 
+class _RowBlock(object):
+    """The rows of a sweep plan whose stage 4 this rank runs (Engine.row_update reads dim, rows, n_rows, n_obs)."""
+
+    def __init__(self, dim, rows):
+        self.dim, self.rows, self.n_rows, self.n_obs = dim, rows, int(rows.numel()), None
+
+
 class SSVI_TF(object):
     _model = "d"          # "d" | "simple" | "robust"; set by the subclasses
 
@@ -92,6 +99,7 @@ class SSVI_TF(object):
         self.fixed_covariance = False
         self.rows_per_iteration = 1
         self.process_group = process_group
+        self.shard_row_update = True       # multi-GPU full sweeps of SSVI_TF_d: stage 4 on row blocks + all-gather
 
         cfg = dict(model=self._model, likelihood=self.likelihood_type, D=rank, diag=diag, k1=k1, k2=k2,
                    batch_size=batch_size, mean_update=mean_update, cov_update=cov_update, eta=eta,
@@ -195,6 +203,19 @@ class SSVI_TF(object):
         if self.process_group is not None:
             from .. import dist as sdist
             sdist.allreduce_accumulators(acc, self.process_group)   # the exchange step: (di, Di, si, count)
+            own = sdist.owned_rows(plan.n_rows, self.process_group) if plan.n_rows == self.dims[plan.dim] else None
+            if own is not None and self._model == "d" and self.shard_row_update:
+                # full sweep: stage 4 on this rank's block of rows, then the updated rows of every state array
+                lo, hi = own
+                sub = _RowBlock(plan.dim, plan.rows[lo:hi])
+                eng.row_update(sub, acc[lo:hi], self.fixed_covariance,
+                               n_obs=(plan.n_obs if n_obs_global is None else n_obs_global)[lo:hi])
+                d = plan.dim
+                state = [eng.params[d], eng.sampler[d], eng.ada_mean[d], eng.norm_changes[d], eng.grad_norms[d]]
+                if self.diag:
+                    state.append(eng.ada_cov[d])
+                sdist.allgather_rows(state, lo, hi, self.process_group)
+                return
         eng.row_update(plan, acc, self.fixed_covariance, n_obs=n_obs_global)
 
     def update_natural_param_rows(self, dim, rows, noise=None, sub_idx=None):

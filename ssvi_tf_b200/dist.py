@@ -4,9 +4,11 @@ The path shards by OBSERVED ENTRY: rank r holds a contiguous block of the COO li
 entry lists of the ranks, concatenated in rank order, are the global lists in the reference's append
 order).  Contributions of different entries to a row are summed (SSVI_TF_d.py:47-56,
 SSVI_TF_interface.py:581-591, SSVI_TF_robust.py:135-137), so one exchange step per mode sweep suffices:
-an all-reduce of the per-row accumulator records [di | Di | si_sum | count].  Stage 4 then runs
-redundantly on every rank from identical inputs, which keeps the replicated posterior bit-identical
-across ranks without a second collective.
+an all-reduce of the per-row accumulator records [di | Di | si_sum | count].  Stage 4 then runs either
+redundantly on every rank from identical inputs (bit-identical replicas without a second collective), or --
+for full sweeps of SSVI_TF_d, where stage 4 of a 10k-row mode is a tenth of an 8-GPU step -- on each rank's
+block of rows (owned_rows) followed by an all-gather of the updated rows of every state array
+(allgather_rows), which also leaves the replicas bit-identical.
 
 Noise slots are a function of an entry's GLOBAL position inside its row's minibatch, so an N-GPU sweep
 consumes exactly the draws the 1-GPU sweep does: row_slot_offsets() gives every rank the number of
@@ -47,3 +49,20 @@ def max_over_ranks(x, group=None):
     t = x if torch.is_tensor(x) else torch.tensor([float(x)], dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
     return t
+
+
+def owned_rows(n_rows, group=None):
+    """Block [lo, hi) of a mode's rows whose stage 4 this rank runs, or None when the rows do not divide evenly
+    (the caller then updates every row redundantly)."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    if n_rows % world:
+        return None
+    share = n_rows // world
+    return rank * share, (rank + 1) * share
+
+
+def allgather_rows(tensors, lo, hi, group=None):
+    """Every tensor is [n_rows, ...] with this rank's block [lo, hi) freshly updated: gather all blocks in place."""
+    for t in tensors:
+        assert t.is_contiguous()
+        dist.all_gather_into_tensor(t.view(-1), t[lo:hi].reshape(-1).clone(), group=group)

@@ -64,6 +64,14 @@ def _worker(rank, world, port, q):
         res[dim] = (acc.numpy(), tot.numpy(), off.numpy())
     t = sdist.max_over_ranks(float(rank + 1))
     res["max"] = float(t.item())
+    # stage 4 on row blocks: every rank updates its block of the (replicated) state, then the blocks are gathered
+    state = [torch.zeros((6, 5), dtype=torch.float64), torch.zeros((6, 2), dtype=torch.float64)]
+    own = sdist.owned_rows(6)
+    res["own"], res["own_uneven"] = own, sdist.owned_rows(7)
+    for k, a in enumerate(state):
+        a[own[0]:own[1]] = 100.0 * (k + 1) + torch.arange(own[0], own[1], dtype=torch.float64)[:, None]
+    sdist.allgather_rows(state, own[0], own[1])
+    res["gathered"] = [a.numpy().copy() for a in state]
     q.put((rank, res))
     dist.barrier()
     dist.destroy_process_group()
@@ -91,6 +99,10 @@ def test_sharded_accumulators_equal_single_process():
         np.testing.assert_array_equal(got[0][dim][2], 0)                              # rank 0 starts every row
         np.testing.assert_array_equal(got[0][dim][0], got[1][dim][0])                 # replicas stay identical
     assert got[0]["max"] == got[1]["max"] == 2.0
+    assert got[0]["own"] == (0, 3) and got[1]["own"] == (3, 6) and got[0]["own_uneven"] is None
+    for r in range(world):
+        for k, a in enumerate(got[r]["gathered"]):
+            np.testing.assert_array_equal(a, 100.0 * (k + 1) + np.arange(6.0)[:, None] * np.ones_like(a))
 
 
 def test_shard_range_partitions():
