@@ -408,6 +408,8 @@ def main():
                 "traffic": None, "kernel": "accumulate (stages 1-3)", "peak_source": peak_src,
                 "algorithmic_bytes_per_unit": bpu, "kernel_ms_per_launch": float(np.mean(acc_ms)),
                 "kernel_share_of_step": sum(acc_ms) / ms,
+                "launch": "one call of Engine.accumulate = stages 1-3 of one mode sweep (CUDA events around it; a sweep "
+                          "issues one sample-table + one accumulate launch per slot group, profiles/*_launches_*)",
                 "fp64_pipe": fp64_pipe_stats(c, sum(acc_units) / (sum(acc_ms) * 1e-3)) if B is None else None,
                 "note": "fp64 contract: the FP64 pipe (37 TFLOP/s measured), not HBM, bounds this kernel; see DESIGN.md 3.1"}
     tr_path = os.path.join(ROOT, "profiles", "traffic.json")
