@@ -134,6 +134,13 @@ int ssvi_bind_state(SsviHandle* h, double* const* params /*HOST*/, double* const
 int ssvi_bind_noise(SsviHandle* h, const void* z_other, const void* z_own, const void* r_w,
                     const void* z_f, int32_t pool_slots);
 
+/* SSVI_TF_robust(quadrature=True) (SSVI_TF_robust.py:11, :22-25, :175-214): replace the k2 second-layer draws of
+ * estimate_expected_derivatives_pdf_batch by the Gauss-Hermite rule
+ *   E[g(f)] = sum_i w_i g(mean + sqrt(2 ws^2) x_i) / sqrt(pi)   (estimate_expected_pdf_quadrature, :198-214).
+ * rule: DEVICE double[2 n] = [nodes x_i | weights w_i] (np.polynomial.hermite.hermgauss(n); the reference uses
+ * n = 30), borrowed until rebound.  n == 0 returns to Monte Carlo.  z_f is not read while a rule is bound. */
+int ssvi_bind_quadrature(SsviHandle* h, const double* rule, int32_t n);
+
 /* Recompute sampler[dim] rows from params[dim] (Cholesky / sqrt).  rows == NULL: all n_dim rows.
  * Replaces the per-draw factorisation inside np.random.multivariate_normal at
  * SSVI_TF_interface.py:743-745, 252-254. */

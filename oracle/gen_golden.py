@@ -61,17 +61,18 @@ def random_state(rng, cfg, dims):
 
 
 def run_case(name, model, lik, diag, dims, nnz, D, k1, k2, batch_size, seed,
-             mean_update="S", cov_update="N", cov_eta=1.0, n_rows=2, fixed_covariance=False):
+             mean_update="S", cov_update="N", cov_eta=1.0, n_rows=2, fixed_covariance=False, quadrature=False):
     rng = np.random.default_rng(seed)
     cfg = so.make_config(model, lik, D, diag=diag, k1=k1, k2=k2, batch_size=batch_size,
-                         mean_update=mean_update, cov_update=cov_update, cov_eta=cov_eta)
+                         mean_update=mean_update, cov_update=cov_update, cov_eta=cov_eta,
+                         quadrature=30 if quadrature else 0)       # the reference fixes degree 30
     coords, vals = random_problem(rng, lik, dims, nnz)
     rowptr, perm = so.build_index(coords, dims)
     state0 = random_state(rng, cfg, dims)
     state0["fixed_covariance"] = fixed_covariance
     obj = ref_shim.make_reference_model(model, DATATYPE[lik], dims, coords, vals, D, diag, k1, k2,
                                         batch_size, mean_update=mean_update, cov_update=cov_update,
-                                        cov_eta=cov_eta)
+                                        cov_eta=cov_eta, quadrature=quadrature)
     steps = []
     N = len(dims)
     for s in range(n_rows):
@@ -136,6 +137,11 @@ def case_list():
                       n_rows=2))
     cases.append(dict(name="simple_bernoulli_full_nosub", model="simple", lik="bernoulli", diag=False,
                       dims=[6, 5, 4], nnz=40, D=5, k1=8, k2=4, batch_size=64, seed=409, n_rows=3))
+    # SSVI_TF_robust(quadrature=True): Gauss-Hermite rule in place of the k2 draws (SSVI_TF_robust.py:175-214)
+    for lik, diag, sd in (("normal", False, 410), ("bernoulli", True, 411), ("poisson", False, 412)):
+        cases.append(dict(name="robust_%s_%s_quadrature" % (lik, "diag" if diag else "full"), model="robust",
+                          lik=lik, diag=diag, dims=[6, 5, 4], nnz=60, D=5, k1=8, k2=4, batch_size=6, seed=sd,
+                          n_rows=2, quadrature=True))
     # BASELINE.json config 1 at full per-row size: 50^3, D=10, k1=64, k2=128, B=128, SSVI_TF_d full
     cases.append(dict(name="config1_d_normal_full", model="d", lik="normal", diag=False, dims=[50, 50, 50],
                       nnz=12000, D=10, k1=64, k2=128, batch_size=128, seed=408, n_rows=1))
@@ -144,7 +150,10 @@ def case_list():
 
 def main():
     os.makedirs(GOLDEN_DIR, exist_ok=True)
+    only = sys.argv[1:]          # optional name filters: regenerate only the cases containing one of them
     for c in case_list():
+        if only and not any(o in c["name"] for o in only):
+            continue
         path = run_case(**c)
         print("wrote %-40s %7.1f KB" % (os.path.basename(path), os.path.getsize(path) / 1024.0))
 

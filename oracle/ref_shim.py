@@ -180,7 +180,7 @@ def make_list_tensor(datatype, dims, coords, vals, max_count=0, min_count=0):
 
 
 def make_reference_model(model, datatype, dims, coords, vals, D, diag, k1, k2, batch_size,
-                         mean_update="S", cov_update="N", eta=1, cov_eta=1, sigma_eta=1):
+                         mean_update="S", cov_update="N", eta=1, cov_eta=1, sigma_eta=1, quadrature=False):
     """Build a reference SSVI_TF_{d,simple,robust} object over a COO tensor (randstart=False;
     the caller then overwrites the state with load_state)."""
     ref = import_reference()
@@ -191,9 +191,10 @@ def make_reference_model(model, datatype, dims, coords, vals, D, diag, k1, k2, b
     tensor = make_list_tensor(datatype, dims, coords, vals,
                          max_count=int(vals.max()) if datatype == "count" else 0,
                          min_count=int(vals.min()) if datatype == "count" else 0)
+    extra = dict(quadrature=True) if quadrature else {}        # SSVI_TF_robust.py:11 (robust only)
     obj = cls(tensor, D, mean_update=mean_update, cov_update=cov_update, diag=diag,
               mean0=np.ones((D,)), cov0=np.eye(D), k1=k1, k2=k2, batch_size=batch_size,
-              eta=eta, cov_eta=cov_eta, sigma_eta=sigma_eta, randstart=False)
+              eta=eta, cov_eta=cov_eta, sigma_eta=sigma_eta, randstart=False, **extra)
     obj.missing = {}
     obj.fixed_covariance = False
     return obj

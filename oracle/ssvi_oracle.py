@@ -31,7 +31,7 @@ DATATYPE_TO_LIK = {"real": LIK_NORMAL, "binary": LIK_BERNOULLI, "count": LIK_POI
 
 
 def make_config(model, likelihood, D, diag=False, k1=64, k2=64, batch_size=128,
-                mean_update="S", cov_update="N", eta=1.0, cov_eta=1.0, sigma_eta=1.0):
+                mean_update="S", cov_update="N", eta=1.0, cov_eta=1.0, sigma_eta=1.0, quadrature=0):
     """Constructor kwargs + hidden constants of SSVI_TF.__init__ (SSVI_TF_interface.py:21-98)."""
     assert model in ("d", "simple", "robust")
     assert likelihood in (LIK_NORMAL, LIK_BERNOULLI, LIK_POISSON)
@@ -42,7 +42,9 @@ def make_config(model, likelihood, D, diag=False, k1=64, k2=64, batch_size=128,
                 min_eigenval=0.01,          # :48
                 epsilon=1e-4,               # :80
                 likelihood_param=1.0 if likelihood == LIK_NORMAL else 0.0,   # :62, :67, :76
-                noise_added=(model != "d"))  # SSVI_TF_simple.py:18, SSVI_TF_robust.py:19
+                noise_added=(model != "d"),  # SSVI_TF_simple.py:18, SSVI_TF_robust.py:19
+                # SSVI_TF_robust(quadrature=True): Gauss-Hermite degree (the reference fixes 30, :23); 0 = Monte Carlo
+                quadrature=int(quadrature) if model == "robust" else 0)
 
 
 def new_state(cfg, dims, rng=None, mean0=None, cov0=None, randstart=True):
@@ -250,7 +252,16 @@ def estimate_di_Di_si(state, cfg, dim, m, S, coords, ys, tape):
         phi = np.empty((B, k1))
         phi1 = np.empty((B, k1))
         phi2 = np.empty((B, k1))
-        for b in range(B):
+        if cfg.get("quadrature", 0):
+            # estimate_expected_derivatives_pdf_batch_quadrature / estimate_expected_pdf_quadrature (:175-214):
+            # fs = m + sqrt(2 w^2) xs;  E = sum(weights * g(fs)) / sqrt(pi); no second-layer draws are consumed
+            xs, wts = np.polynomial.hermite.hermgauss(int(cfg["quadrature"]))            # :23-24
+            for b in range(B):
+                fs = mean_batch[b][None, :] + np.sqrt(2 * np.square(ws[b]))[None, :] * xs[:, None]   # (degree, k1)
+                phi[b] = np.sum(wts[:, None] * pdf(lik, ys[b], fs, s), axis=0) / np.sqrt(np.pi)
+                phi1[b] = np.sum(wts[:, None] * fst_derivative_pdf(lik, ys[b], fs, s), axis=0) / np.sqrt(np.pi)
+                phi2[b] = np.sum(wts[:, None] * snd_derivative_pdf(lik, ys[b], fs, s), axis=0) / np.sqrt(np.pi)
+        for b in range(B if not cfg.get("quadrature", 0) else 0):
             fs = mean_batch[b] + ws[b] * tape.z_f[b]                         # :163
             phi[b] = np.mean(pdf(lik, ys[b], fs, s), axis=0)
             phi1[b] = np.mean(fst_derivative_pdf(lik, ys[b], fs, s), axis=0)

@@ -48,6 +48,7 @@ SIGNATURES = {
     "ssvi_bind_data": (ctypes.c_int, [_P, _P, _P, _I64]),
     "ssvi_bind_state": (ctypes.c_int, [_P] + [ctypes.POINTER(_P)] * 6),
     "ssvi_bind_noise": (ctypes.c_int, [_P, _P, _P, _P, _P, _I32]),
+    "ssvi_bind_quadrature": (ctypes.c_int, [_P, _P, _I32]),
     "ssvi_refresh_sampler": (ctypes.c_int, [_P, _I32, _P, _I64, _P]),
     "ssvi_accumulate": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "ssvi_sweep_supported": (ctypes.c_int, [_P]),

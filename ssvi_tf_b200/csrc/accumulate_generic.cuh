@@ -61,17 +61,35 @@ __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* _
     si_part += ss * ws;
   } else {
     double p = 0.0, p1 = 0.0, p2 = 0.0;
-    for (int i2 = 0; i2 < k2; ++i2) {                  // (the pdf terms are too large a body to unroll profitably)
-      double fs = f + ws * ldz(zf, (int64_t)i2 * k1);
-      double a, b, c;
-      pdf_derivs(v.lik, y, fs, s, yfact, a, b, c);
-      p += a;
-      p1 += b;
-      p2 += c;
+    if (v.quad) {
+      // SSVI_TF_robust(quadrature=True), SSVI_TF_robust.py:175-214: the k2 draws are replaced by the Gauss-Hermite
+      // rule  E[g] = sum_i w_i g(f + sqrt(2 ws^2) x_i) / sqrt(pi)
+      const double sw = sqrt(2.0 * (ws * ws));
+      for (int i2 = 0; i2 < v.quad_n; ++i2) {
+        const double wq = __ldg(v.quad + v.quad_n + i2);
+        double a, b, c;
+        pdf_derivs(v.lik, y, f + sw * __ldg(v.quad + i2), s, yfact, a, b, c);
+        p += wq * a;
+        p1 += wq * b;
+        p2 += wq * c;
+      }
+      const double sqrt_pi = 1.7724538509055159;
+      p /= sqrt_pi;
+      p1 /= sqrt_pi;
+      p2 /= sqrt_pi;
+    } else {
+      for (int i2 = 0; i2 < k2; ++i2) {                // (the pdf terms are too large a body to unroll profitably)
+        double fs = f + ws * ldz(zf, (int64_t)i2 * k1);
+        double a, b, c;
+        pdf_derivs(v.lik, y, fs, s, yfact, a, b, c);
+        p += a;
+        p1 += b;
+        p2 += c;
+      }
+      p /= (double)k2;
+      p1 /= (double)k2;
+      p2 /= (double)k2;
     }
-    p /= (double)k2;
-    p1 /= (double)k2;
-    p2 /= (double)k2;
     if (!(isfinite(p) && isfinite(p1) && isfinite(p2)) || p == 0.0) bad = true;
     aw = (p1 / p) * inv_k1;
     dw = 0.5 / ((double)k1 * p) * (p2 - p2 * p2 / p);                        // Q6

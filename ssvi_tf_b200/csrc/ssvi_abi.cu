@@ -140,6 +140,15 @@ extern "C" int ssvi_bind_noise(SsviHandle* h, const void* z_other, const void* z
   return SSVI_OK;
 }
 
+extern "C" int ssvi_bind_quadrature(SsviHandle* h, const double* rule, int32_t n) {
+  if (!h) return SSVI_E_INVALID;
+  if (n < 0 || (n > 0 && !rule)) return fail(h, SSVI_E_INVALID, "bind_quadrature: null rule%s");
+  if (n > 0 && h->cfg.model != SSVI_MODEL_ROBUST) return fail(h, SSVI_E_INVALID, "bind_quadrature: only SSVI_TF_robust has a quadrature option%s");
+  h->quad = n > 0 ? rule : nullptr;
+  h->quad_n = n;
+  return SSVI_OK;
+}
+
 static DevView make_view(const SsviHandle* h, int dim) {
   DevView v;
   memset(&v, 0, sizeof(v));
@@ -163,6 +172,8 @@ static DevView make_view(const SsviHandle* h, int dim) {
   v.vals = h->vals;
   for (int d = 0; d < c.order; ++d) v.sampler[d] = h->sampler[d];
   v.flags = h->d_flags;
+  v.quad = h->quad;
+  v.quad_n = h->quad_n;
   return v;
 }
 

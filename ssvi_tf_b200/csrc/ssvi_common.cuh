@@ -28,6 +28,9 @@ struct SsviHandle {
   const void* r_w;
   const void* z_f;
   int32_t pool_slots;
+  // Gauss-Hermite rule of SSVI_TF_robust(quadrature=True): device [nodes (n) | weights (n)], n == 0: Monte Carlo
+  const double* quad;
+  int32_t quad_n;
   // device flag word
   int32_t* d_flags;
   int sm_count;
@@ -51,6 +54,8 @@ struct DevView {
   const double* vals;
   const double* sampler[SSVI_MAX_ORDER];
   int32_t* flags;
+  const double* quad;    // SSVI_TF_robust quadrature rule [nodes | weights], NULL: second-layer Monte Carlo
+  int32_t quad_n;
 };
 
 // ------------------------------------------------------------------------------------------------

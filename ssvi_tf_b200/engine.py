@@ -197,6 +197,9 @@ class Engine(object):
         if rc != 0:
             raise _lib.SsviError("ssvi_create failed: %s" % self.lib.ssvi_last_error(None).decode())
         self.h = h
+        self._quad_rule = None
+        if cfg.get("quadrature"):                        # SSVI_TF_robust(quadrature=True): Gauss-Hermite degree
+            self.set_quadrature(int(cfg["quadrature"]))
 
         # ---- data: COO + per-mode CSR -------------------------------------------------------
         if torch.is_tensor(coords) and coords.is_cuda:
@@ -305,6 +308,17 @@ class Engine(object):
         self.noise = pool
         self._call(self.lib.ssvi_bind_noise, _ptr(pool.z_other), _ptr(pool.z_own),
                    _ptr(pool.r_w if need2 else None), _ptr(pool.z_f if need2 else None), pool.slots)
+
+    def set_quadrature(self, degree):
+        """SSVI_TF_robust(quadrature=True), SSVI_TF_robust.py:22-25: Gauss-Hermite rule of `degree` nodes in place of
+        the k2 second-layer draws (degree 0 / None: back to Monte Carlo)."""
+        if not degree:
+            self._quad_rule = None
+            self._call(self.lib.ssvi_bind_quadrature, None, 0)
+            return
+        xs, ws = np.polynomial.hermite.hermgauss(int(degree))
+        self._quad_rule = torch.as_tensor(np.concatenate([xs, ws]), dtype=torch.float64).to(self.device)
+        self._call(self.lib.ssvi_bind_quadrature, _ptr(self._quad_rule), int(degree))
 
     def refresh_sampler(self, dim=None, rows=None):
         dims = range(self.N) if dim is None else [dim]

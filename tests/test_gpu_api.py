@@ -20,7 +20,8 @@ class _COO(object):
         self.min_count = int(self.train_vals.min()) if datatype == "count" else 0
 
 
-@pytest.mark.parametrize("name", ["d_normal_full", "simple_poisson_diag", "robust_bernoulli_full"])
+@pytest.mark.parametrize("name", ["d_normal_full", "simple_poisson_diag", "robust_bernoulli_full",
+                                  "robust_poisson_full_quadrature"])
 def test_update_natural_param_batch_is_drop_in(name):
     """model.update_natural_param_batch(dim, i) under a supplied tape == the reference's own call."""
     import ssvi_tf_b200 as pkg
@@ -28,8 +29,11 @@ def test_update_natural_param_batch_is_drop_in(name):
     cfg = case["cfg"]
     dt = {"normal": "real", "bernoulli": "binary", "poisson": "count"}[cfg["likelihood"]]
     cls = {"d": pkg.SSVI_TF_d, "simple": pkg.SSVI_TF_simple, "robust": pkg.SSVI_TF_robust}[cfg["model"]]
+    extra = dict(quadrature=True) if cfg.get("quadrature") else {}          # SSVI_TF_robust.py:11
     m = cls(_COO(dt, case["dims"], case["coords"], case["vals"]), cfg["D"], diag=cfg["diag"], k1=cfg["k1"],
-            k2=cfg["k2"], batch_size=cfg["batch_size"], randstart=False, noise_dtype=torch.float64)
+            k2=cfg["k2"], batch_size=cfg["batch_size"], randstart=False, noise_dtype=torch.float64, **extra)
+    if extra:
+        assert m.quadrature and m.gauss_degree == 30
     st0 = case["state0"]
     for step in case["steps"]:
         for d in range(m.order):

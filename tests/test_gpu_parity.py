@@ -193,6 +193,8 @@ def test_mma_path_matches_oracle_and_generic(D, k1, model, lik):
     ([6, 5, 4], 12, 64, "normal", 2, 64, False, "simple"),
     ([4, 3, 3, 3], 9, 64, "poisson", 3, 5, True, "simple"),
     ([7, 9], 32, 64, "normal", 2, 64, False, "robust"),
+    ([5, 4, 4], 20, 64, "poisson", 3, 64, False, "robust+quad"),   # SSVI_TF_robust(quadrature=True), every kernel path
+    ([6, 5, 4], 12, 64, "bernoulli", 2, 3, True, "robust+quad"),
 ])
 def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W, offs, model):
     """Full sweep through the slot-major sample-table kernels == the direct DMMA kernel == the generic CUDA-core
@@ -200,7 +202,8 @@ def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W
     from ssvi_tf_b200.engine import Engine, NoisePool
     rng = np.random.default_rng(D * 1000 + k1 + P)
     N = len(dims)
-    cfg = so.make_config(model, lik, D, diag=False, k1=k1, k2=4, batch_size=10 ** 9)
+    quad = 30 if model.endswith("+quad") else 0
+    cfg = so.make_config(model.split("+")[0], lik, D, diag=False, k1=k1, k2=4, batch_size=10 ** 9, quadrature=quad)
     nnz = int(0.8 * np.prod(dims))
     coords, vals = random_problem(rng, lik, dims, nnz)
     st0 = random_state(rng, cfg, dims)
@@ -312,13 +315,15 @@ def test_sweep_l2_tiled_launch_order_matches_untiled(dims, D, lik, P, W, nb, off
     ([5, 4, 4], 20, 64, "robust", "poisson", 4, 2, True),
     ([5, 4, 4], 64, 48, "robust", "bernoulli", 2, 64, False),    # D = 64: every lane busy
     ([7, 9], 12, 64, "simple", "poisson", 3, 64, False),         # matrix
+    ([5, 4, 4], 20, 64, "robust+quad", "normal", 3, 64, False),  # SSVI_TF_robust(quadrature=True), diagonal
 ])
 def test_sweep_diag_path_matches_generic_and_oracle(dims, D, k1, model, lik, P, W, offs):
     """Diagonal covariance, full sweep through the slot-major shared-noise kernel == the generic kernel == the oracle."""
     from ssvi_tf_b200.engine import Engine, NoisePool
     rng = np.random.default_rng(D * 1000 + k1 + P)
     N = len(dims)
-    cfg = so.make_config(model, lik, D, diag=True, k1=k1, k2=6, batch_size=10 ** 9)
+    cfg = so.make_config(model.split("+")[0], lik, D, diag=True, k1=k1, k2=6, batch_size=10 ** 9,
+                         quadrature=30 if model.endswith("+quad") else 0)
     nnz = int(0.8 * np.prod(dims))
     coords, vals = random_problem(rng, lik, dims, nnz)
     st0 = random_state(rng, cfg, dims)
