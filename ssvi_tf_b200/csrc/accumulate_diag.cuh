@@ -68,7 +68,7 @@ __device__ __forceinline__ void diag_v(const double* __restrict__ zs, int blk_st
 }
 
 // One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.
-template <int NOTH, typename ZT, bool SECOND>
+template <int NOTH, typename ZT, bool SECOND, bool LIN>
 __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
     DevView v, int64_t n_chunks, const int32_t* __restrict__ chunk_row, const int64_t* __restrict__ chunk_start,
     const int32_t* __restrict__ chunk_len, const int32_t* __restrict__ chunk_slot,
@@ -112,8 +112,8 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
   }
 
   // ---- stage the slot's noise blocks as doubles, [blk][k][c] (pool layout is [c][k]) ----------------------------------
-  for (int b = 0; b < N; ++b) {
-    const ZT* src = (b < N - 1) ? z_other + ((int64_t)slot * (N - 1) + b) * v.zblk : z_own + (int64_t)slot * v.zblk;
+  for (int b = 0; b < N - 1; ++b) {
+    const ZT* src = z_other + ((int64_t)slot * (N - 1) + b) * v.zblk;
     double* dst = zs + (size_t)b * blk_stride;
     for (int idx = tid; idx < D * k1; idx += 128) {
       const int cc = idx / k1, k = idx - cc * k1;
@@ -122,24 +122,27 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
     if (DP != D)
       for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
   }
-  // own row: lane l owns components 2l, 2l+1 (zero beyond D: they then contribute exact zeros everywhere)
+  {
+    // own row (ui samples, SSVI_TF_interface.py:251-254): U[k][c] = m[c] + sqrt(S)[c] z_own[c][k], once per chunk
+    const ZT* src = z_own + (int64_t)slot * v.zblk;
+    const double* own = v.sampler[dim] + row * (int64_t)v.srow_len;
+    double* dst = zs + (size_t)(N - 1) * blk_stride;
+    for (int idx = tid; idx < D * k1; idx += 128) {
+      const int cc = idx / k1, k = idx - cc * k1;
+      dst[k * DP + cc] = fma(own[D + cc], (double)src[idx], own[cc]);
+    }
+    if (DP != D)
+      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
+  }
+  // lane l owns components 2l, 2l+1 (gathered rows read as zero beyond D: v is then an exact zero there)
   const int n0 = 2 * lane, n1 = 2 * lane + 1;
   const int zoff = n0 < DP ? n0 : 0;                    // idle lanes (n0 >= D) read valid noise against m = s = 0
-  double mo[2], so[2];
-  {
-    const double* src = v.sampler[dim] + row * (int64_t)v.srow_len;
-    mo[0] = n0 < D ? src[n0] : 0.0;
-    mo[1] = n1 < D ? src[n1] : 0.0;
-    so[0] = n0 < D ? src[D + n0] : 0.0;
-    so[1] = n1 < D ? src[D + n1] : 0.0;
-  }
   __syncthreads();
 
   // SSVI_TF_simple + normal likelihood: d log p / df is linear in f, so the k2 mean of SSVI_TF_simple.py:35-38 is
   // (y - f - ws * mean_i z_f[i][k]) / s^2, and both ws and that mean are constants of the chunk (one slot).
-  const bool lin = SECOND && v.model == SSVI_MODEL_SIMPLE && v.lik == SSVI_LIK_NORMAL;
   double zbar[2] = {0.0, 0.0}, wsl[2] = {0.0, 0.0};
-  if (lin) {
+  if (LIN) {
 #pragma unroll
     for (int a = 0; a < 2; ++a) {
       const int k = 16 * (2 * a + (lane & 1)) + (lane >> 1);
@@ -158,9 +161,21 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
       }
     }
   }
+  // LIN: c[t] = ws_k * mean_i z_f[i][k] of the sample k = 16 t + (lane >> 1) this lane holds after tile t's reduction
+  // (the lane computed tiles t = lane & 1 and 2 + (lane & 1) above; its pair partner holds the other two)
+  double ckt[4] = {0.0, 0.0, 0.0, 0.0};
+  if (LIN) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const double mine = wsl[t >> 1] * zbar[t >> 1];
+      const double other = __shfl_xor_sync(0xffffffffu, mine, 1);
+      ckt[t] = ((t & 1) == (lane & 1)) ? mine : other;
+    }
+  }
   double g0 = 0.0, g1 = 0.0, G0 = 0.0, G1 = 0.0, si_part = 0.0;
   bool bad = false;
   const double inv_k1 = 1.0 / (double)k1;
+  const double is2 = LIN ? 1.0 / (v.lik_param * v.lik_param) : 0.0;
   const double* zo = zs + (size_t)(N - 1) * blk_stride;
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
@@ -212,25 +227,59 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
       double fk[2] = {0.0, 0.0};                         // lane owns samples 16*(2a + (lane&1)) + (lane>>1), a = 0, 1
       for (int tile = 0; tile < (k1 >> 4); ++tile) {
         double p[16];
+        double vk[LIN ? 16 : 1][2];
 #pragma unroll
         for (int kk = 0; kk < 16; ++kk) {
           const int k = tile * 16 + kk;
           double v0, v1;
           diag_v<NOTH>(zs, blk_stride, k, DP, zoff, m, s, v0, v1);
-          const double2 z = *reinterpret_cast<const double2*>(zo + k * DP + zoff);
-          const double u0 = fma(so[0], z.x, mo[0]), u1 = fma(so[1], z.y, mo[1]);
-          p[kk] = fma(u1, v1, u0 * v0);
+          const double2 u = *reinterpret_cast<const double2*>(zo + k * DP + zoff);
+          p[kk] = fma(u.y, v1, u.x * v0);
           if (!SECOND) {
             sv0 += v0;
             sv1 += v1;
+          }
+          if (!SECOND || LIN) {
             sq0 = fma(v0, v0, sq0);
             sq1 = fma(v1, v1, sq1);
           }
+          if (LIN) {
+            vk[kk][0] = v0;
+            vk[kk][1] = v1;
+          }
         }
         const double f = transpose_reduce16(p, lane);
-        if ((tile & 1) == (lane & 1)) {
+        if (LIN) {
+          // SSVI_TF_simple.py:35-38 with the normal likelihood: mean_k2 dlogp = (y - f_k - ws_k zbar_k) / s^2; every lane
+          // of a pair holds the tile's sample (lane >> 1); the 16 weights go round the warp through shared memory
+          double ck = ckt[0];
+          if (tile == 1) ck = ckt[1];
+          if (tile == 2) ck = ckt[2];
+          if (tile == 3) ck = ckt[3];
+          __syncwarp();
+          if ((lane & 1) == 0) reinterpret_cast<double*>(AW)[lane >> 1] = is2 * (y - f - ck) * inv_k1;
+          __syncwarp();
+#pragma unroll
+          for (int kk = 0; kk < 16; kk += 2) {
+            const double2 w2 = AW[kk >> 1];
+            g0 = fma(w2.x, vk[kk][0], g0);
+            g1 = fma(w2.x, vk[kk][1], g1);
+            g0 = fma(w2.y, vk[kk + 1][0], g0);
+            g1 = fma(w2.y, vk[kk + 1][1], g1);
+          }
+        } else if ((tile & 1) == (lane & 1)) {
           if (tile < 2) fk[0] = f; else fk[1] = f;
         }
+      }
+      if (LIN) {
+        // d2 log p / df2 = -1/s^2 for every sample: Di weight -0.5 / (s^2 k1) (applied once, at the end of the chunk);
+        // si takes mean_k2 snd * ws = -ws_k / s^2 of the samples this lane owns (same split as the generic branch)
+        G0 += sq0;
+        G1 += sq1;
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+          if (16 * (2 * a + (lane & 1)) + (lane >> 1) < k1) si_part -= is2 * wsl[a];
+        continue;
       }
       if (!SECOND) {
         // SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1, then broadcast
@@ -261,14 +310,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
           const int k = 16 * (2 * a + (lane & 1)) + (lane >> 1);
           const bool active = k < k1;
           double aw, dw;
-          if (lin) {
-            const double is2 = 1.0 / (v.lik_param * v.lik_param);
-            aw = is2 * (y - fk[a] - wsl[a] * zbar[a]) * inv_k1;
-            dw = -0.5 * is2 * inv_k1;
-            if (active) si_part -= is2 * wsl[a];
-          } else {
-            likelihood_weights<ZT>(v, r_w, z_f, slot, k, active, y, yfact, fk[a], w_sigma, aw, dw, si_part, bad);
-          }
+          likelihood_weights<ZT>(v, r_w, z_f, slot, k, active, y, yfact, fk[a], w_sigma, aw, dw, si_part, bad);
           if (active) AW[k] = make_double2(aw, dw);
         }
         __syncwarp();
@@ -287,6 +329,11 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
   }
 
   // ---- CTA reduction in fixed warp order; chunk record [di (D) | Di (D) | si_sum | count] -----------------------------
+  if (LIN) {
+    const double dwc = -0.5 * is2 * inv_k1;
+    G0 *= dwc;
+    G1 *= dwc;
+  }
   si_part = warp_sum(si_part);
   const unsigned anybad = __ballot_sync(0xffffffffu, bad);
   double* rw = red + warp * (2 * DP + 2);

@@ -370,13 +370,13 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
   return SSVI_OK;
 }
 
-template <int NOTH, typename ZT, bool SECOND>
+template <int NOTH, typename ZT, bool SECOND, bool LIN>
 static int launch_sweep_diag(SsviHandle* h, const DevView& v, int64_t n_chunks, const int32_t* chunk_row,
                              const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
                              const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows,
                              const double* w_state, double* partial_out, cudaStream_t st) {
   const size_t smem = diag_cta_smem(v.N, v.D, v.k1);
-  auto kern = accumulate_diag_kernel<NOTH, ZT, SECOND>;
+  auto kern = accumulate_diag_kernel<NOTH, ZT, SECOND, LIN>;
   CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
                                               entry_ids, rows, w_state, (const ZT*)h->z_other, (const ZT*)h->z_own,
@@ -396,10 +396,16 @@ static int sweep_diag(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_
   if (second && !w_state) return fail(h, SSVI_E_INVALID, "sweep_accumulate: w_state required for simple/robust%s");
   const DevView v = make_view(h, dim);
 #define SSVI_DIAG_ARGS h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, w_state, partial_out, st
+  // closed-form weights: SSVI_TF_simple + normal likelihood (BASELINE config 4), see accumulate_diag.cuh
+  const bool lin = h->cfg.model == SSVI_MODEL_SIMPLE && h->cfg.likelihood == SSVI_LIK_NORMAL;
 #define SSVI_DIAG_CASE(NOTH)                                                                              \
   if (h->cfg.noise_dtype == SSVI_NOISE_F32)                                                               \
-    return second ? launch_sweep_diag<NOTH, float, true>(SSVI_DIAG_ARGS) : launch_sweep_diag<NOTH, float, false>(SSVI_DIAG_ARGS); \
-  return second ? launch_sweep_diag<NOTH, double, true>(SSVI_DIAG_ARGS) : launch_sweep_diag<NOTH, double, false>(SSVI_DIAG_ARGS);
+    return lin ? launch_sweep_diag<NOTH, float, true, true>(SSVI_DIAG_ARGS)                               \
+               : second ? launch_sweep_diag<NOTH, float, true, false>(SSVI_DIAG_ARGS)                     \
+                        : launch_sweep_diag<NOTH, float, false, false>(SSVI_DIAG_ARGS);                   \
+  return lin ? launch_sweep_diag<NOTH, double, true, true>(SSVI_DIAG_ARGS)                                \
+             : second ? launch_sweep_diag<NOTH, double, true, false>(SSVI_DIAG_ARGS)                      \
+                      : launch_sweep_diag<NOTH, double, false, false>(SSVI_DIAG_ARGS);
   switch (h->cfg.order - 1) {
     case 1: SSVI_DIAG_CASE(1)
     case 2: SSVI_DIAG_CASE(2)

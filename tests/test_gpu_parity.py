@@ -316,6 +316,8 @@ def test_sweep_l2_tiled_launch_order_matches_untiled(dims, D, lik, P, W, nb, off
     ([5, 4, 4], 64, 48, "robust", "bernoulli", 2, 64, False),    # D = 64: every lane busy
     ([7, 9], 12, 64, "simple", "poisson", 3, 64, False),         # matrix
     ([5, 4, 4], 20, 64, "robust+quad", "normal", 3, 64, False),  # SSVI_TF_robust(quadrature=True), diagonal
+    ([6, 5, 4], 9, 32, "simple", "normal", 2, 3, True),          # closed-form (LIN) instance: odd D, two k-tiles
+    ([6, 5, 4], 64, 48, "simple", "normal", 3, 64, True),        # LIN: three k-tiles, every lane busy
 ])
 def test_sweep_diag_path_matches_generic_and_oracle(dims, D, k1, model, lik, P, W, offs):
     """Diagonal covariance, full sweep through the slot-major shared-noise kernel == the generic kernel == the oracle."""
