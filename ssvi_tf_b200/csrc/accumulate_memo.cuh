@@ -106,6 +106,13 @@ __device__ __forceinline__ void mma_sample_tile(const double* __restrict__ S, co
 }
 
 #define SSVI_MEMO_KT 8                                  // the sample-table path is specialised for k1 == 64
+// Tuning knobs of accumulate_memo_kernel (A/B builds: -DSSVI_MEMO_PF=2 -DSSVI_MEMO_MINB=3 ...)
+#ifndef SSVI_MEMO_PF
+#define SSVI_MEMO_PF 1                                  // k-tiles of table records in flight ahead of the one in use
+#endif
+#ifndef SSVI_MEMO_MINB
+#define SSVI_MEMO_MINB 4                                // resident CTAs per SM asked of ptxas for NT <= 3
+#endif
 // Shared memory of one CTA (4 warps), bytes: one region reused as {staging | U | reduction} + per-warp G.
 __host__ __device__ inline int memo_region_bytes(int NT, int D) {
   int a = smp_row_len(D, false) * 8 + smp_zblk(D, 8 * SSVI_MEMO_KT, false) * 8;      // staging: row + z (as double)
@@ -127,7 +134,7 @@ __device__ __forceinline__ double2 ld_tab(const double2* p) { return __ldcg(p); 
 //         otherwise the row sums are accumulated with DADDs.
 // ---------------------------------------------------------------------------------------------------------------------
 template <int NT, int NOTH, bool ONES>
-__global__ void __launch_bounds__(128, (NT <= 3 ? 4 : 3)) accumulate_memo_kernel(
+__global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulate_memo_kernel(
     DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
     const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
     const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
@@ -170,12 +177,18 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? 4 : 3)) accumulate_memo_kernel
     for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
   }
 
+  constexpr int PF = SSVI_MEMO_PF;
   double2 cur[NOTH][NT];                                // first k-tile of the first entry: in flight during the prologue
+  double2 pf[PF - 1 > 0 ? PF - 1 : 1][NOTH][NT];        // k-tiles 1 .. PF-1 (deeper prefetch only)
 #pragma unroll
   for (int jj = 0; jj < NOTH; ++jj) {
     const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
 #pragma unroll
     for (int i = 0; i < NT; ++i) cur[jj][i] = ld_tab(p + (i * KT) * 32);
+#pragma unroll
+    for (int d = 1; d < PF; ++d)
+#pragma unroll
+      for (int i = 0; i < NT; ++i) pf[d - 1][jj][i] = ld_tab(p + (i * KT + d) * 32);
   }
 
   // ---- prologue: U(row, slot) = m + L z_own, once per CTA (ui samples, SSVI_TF_interface.py:251-254) --------------------
@@ -230,6 +243,10 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? 4 : 3)) accumulate_memo_kernel
         const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
 #pragma unroll
         for (int i = 0; i < NT; ++i) cur[jj][i] = ld_tab(p + (i * KT) * 32);
+#pragma unroll
+        for (int d = 1; d < PF; ++d)
+#pragma unroll
+          for (int i = 0; i < NT; ++i) pf[d - 1][jj][i] = ld_tab(p + (i * KT + d) * 32);
       }
     }
     for (int el = 0; el < nb; ++el) {
@@ -250,10 +267,10 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? 4 : 3)) accumulate_memo_kernel
       for (int i = 0; i < NT; ++i) rs[i] = 0.0;
 #pragma unroll
       for (int t = 0; t < KT; ++t) {
-        double2 nxt[NOTH][NT];                          // one k-tile ahead (the next entry's first tile at t == KT-1)
+        double2 nxt[NOTH][NT];                          // PF k-tiles ahead (the next entry's first tiles at t >= KT-PF)
 #pragma unroll
         for (int jj = 0; jj < NOTH; ++jj) {
-          const double2* p = (t + 1 < KT) ? pc[jj] + (t + 1) * 32 : pn[jj];
+          const double2* p = (t + PF < KT) ? pc[jj] + (t + PF) * 32 : pn[jj] + (t + PF - KT) * 32;
 #pragma unroll
           for (int i = 0; i < NT; ++i) nxt[jj][i] = ld_tab(p + (i * KT) * 32);
         }
@@ -291,7 +308,16 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? 4 : 3)) accumulate_memo_kernel
 #pragma unroll
         for (int jj = 0; jj < NOTH; ++jj)
 #pragma unroll
-          for (int i = 0; i < NT; ++i) cur[jj][i] = nxt[jj][i];
+          for (int i = 0; i < NT; ++i) {
+            if (PF == 1) {
+              cur[jj][i] = nxt[jj][i];
+            } else {
+              cur[jj][i] = pf[0][jj][i];
+#pragma unroll
+              for (int d = 1; d < PF - 1; ++d) pf[d - 1][jj][i] = pf[d][jj][i];
+              pf[PF - 2 >= 0 ? PF - 2 : 0][jj][i] = nxt[jj][i];
+            }
+          }
       }
       // ---- f_k = u_k . v_k: sum over the 8 row groups through shared memory; lane (g, q) ends with the samples
       //      k = 8g + 2q + {0,1}, i.e. it reads the partials of k-tile t = g held by the lanes (g', q), g' = 0..7 -----------
