@@ -110,6 +110,9 @@ __device__ __forceinline__ void mma_sample_tile(const double* __restrict__ S, co
 #ifndef SSVI_MEMO_PF
 #define SSVI_MEMO_PF 1                                  // k-tiles of table records in flight ahead of the one in use
 #endif
+#ifndef SSVI_MEMO_DIAG
+#define SSVI_MEMO_DIAG 0                                // timing diagnostics (wrong results): 1 no likelihood, 2 + no warp sum, 3 no DMMA
+#endif
 #ifndef SSVI_MEMO_MINB
 #define SSVI_MEMO_MINB 4                                // resident CTAs per SM asked of ptxas for NT <= 3
 #endif
@@ -301,7 +304,11 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
           for (int i1 = 0; i1 < NT; ++i1)
 #pragma unroll
             for (int i2 = 0; i2 <= i1; ++i2) {
+#if SSVI_MEMO_DIAG == 3
+              acc[p][0] += (s ? vv[i1].y : vv[i1].x);                    // timing diagnostic only: no contraction
+#else
               dmma_m8n8k4(acc[p][0], acc[p][1], s ? vv[i1].y : vv[i1].x, s ? vv[i2].y : vv[i2].x);
+#endif
               ++p;
             }
         }
@@ -323,29 +330,31 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
       //      k = 8g + 2q + {0,1}, i.e. it reads the partials of k-tile t = g held by the lanes (g', q), g' = 0..7 -----------
       double f[2];
       __syncwarp();
-      {
-        double2 a = FP[g * 32 + (((0 ^ g) << 2) | q)];
+      {                                                 // pairwise tree: depth 3 on the shared FP64 pipe, not 7
+        double2 b[8];
 #pragma unroll
-        for (int gg = 1; gg < 8; ++gg) {
-          const double2 b = FP[g * 32 + (((gg ^ g) << 2) | q)];
-          a.x += b.x;
-          a.y += b.y;
-        }
-        f[0] = a.x;
-        f[1] = a.y;
+        for (int gg = 0; gg < 8; ++gg) b[gg] = FP[g * 32 + (((gg ^ g) << 2) | q)];
+        f[0] = ((b[0].x + b[1].x) + (b[2].x + b[3].x)) + ((b[4].x + b[5].x) + (b[6].x + b[7].x));
+        f[1] = ((b[0].y + b[1].y) + (b[2].y + b[3].y)) + ((b[4].y + b[5].y) + (b[6].y + b[7].y));
       }
       __syncwarp();
       // ---- SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1, then broadcast -------------------------------------
-      double sum_a = 0.0, sum_d = 0.0;
-#pragma unroll
-      for (int s = 0; s < 2; ++s) {
-        double a, b;
-        log_pdf_derivs(v.lik, y, f[s], v.lik_param, a, b);
-        sum_a += a;
-        sum_d += b;
+      double sum_a, sum_d;
+      {
+        double a0, b0, a1, b1;
+#if SSVI_MEMO_DIAG == 1 || SSVI_MEMO_DIAG == 2
+        a0 = f[0]; b0 = f[1]; a1 = y; b1 = y;                             // timing diagnostic only: no likelihood
+#else
+        log_pdf_derivs_pair(v.lik, y, f[0], f[1], v.lik_param, a0, b0, a1, b1);
+#endif
+        sum_a = a0 + a1;
+        sum_d = b0 + b1;
       }
-      sum_a = warp_sum(sum_a) * inv_k1;
-      sum_d = warp_sum(sum_d) * inv_k1;
+#if SSVI_MEMO_DIAG != 2
+      warp_sum2(sum_a, sum_d, lane);
+#endif
+      sum_a *= inv_k1;
+      sum_d *= inv_k1;
       const double aw = sum_a * inv_k1, dw = 0.5 * sum_d * inv_k1;
 #pragma unroll
       for (int i = 0; i < NT; ++i) {                    // ONES: sum_b aw_b * (row D of V V^T); else sum_b aw_b * row sums

@@ -58,6 +58,63 @@ __device__ __forceinline__ PoissonTerms poisson_terms(double f) {
   return t;
 }
 
+// exp(x) for x <= 0 as straight-line code with a SHORT dependency chain.  The FP64 pipe of a B200 SM is shared with the
+// DMMAs of the other warps, so every dependent FP64 instruction of a likelihood evaluation queues behind 16-cycle
+// tensor operations: what costs time is the chain depth, not the instruction count.  libm's exp is a 12-deep Horner
+// chain plus a range-check branch (which also stops ptxas interleaving two evaluations); here: round-to-int by the
+// magic-number add, Cody-Waite reduction, degree-13 Taylor polynomial in Estrin form (4 levels; truncation error
+// 0.347^14 / 14! = 4e-18), exponent spliced in with integer arithmetic.  Arguments below -708 return exp(-708) ~ 3e-308
+// (the exact value is smaller still; no caller can tell the difference).  About 2 ulp.
+__device__ __forceinline__ double exp_nonpos(double x) {
+  const double xc = fmax(x, -708.0);
+  const double t = fma(xc, 1.4426950408889634, 6755399441055744.0);
+  const int n = __double2loint(t);
+  const double nd = t - 6755399441055744.0;
+  double r = fma(nd, -6.93147180369123816490e-01, xc);
+  r = fma(nd, -1.90821492927058770002e-10, r);
+  const double r2 = r * r;
+  const double p01 = 1.0 + r;
+  const double p23 = fma(r, 1.0 / 6.0, 0.5);
+  const double p45 = fma(r, 1.0 / 120.0, 1.0 / 24.0);
+  const double p67 = fma(r, 1.0 / 5040.0, 1.0 / 720.0);
+  const double p89 = fma(r, 1.0 / 362880.0, 1.0 / 40320.0);
+  const double pab = fma(r, 1.0 / 39916800.0, 1.0 / 3628800.0);
+  const double pcd = fma(r, 1.0 / 6227020800.0, 1.0 / 479001600.0);
+  const double r4 = r2 * r2;
+  const double q0 = fma(r2, p23, p01);
+  const double q1 = fma(r2, p67, p45);
+  const double q2 = fma(r2, pab, p89);
+  const double r8 = r4 * r4;
+  const double q3 = fma(r4, pcd, q2);
+  const double s0 = fma(r4, q1, q0);
+  const double p = fma(r8, q3, s0);                    // in [0.70, 1.42]: adding n to the exponent field cannot carry
+  return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
+
+// 1 / a for a in [1, 2]: hardware seed (MUFU.RCP64H, ~20 bits) + two Newton steps, no special cases to branch on
+__device__ __forceinline__ double rcp_1to2(double a) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  double e = fma(-a, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-a, y, 1.0);
+  return fma(y, e, y);
+}
+
+// bernoulli.py:40-51: sigmoid(yf) and sigmoid(-yf) from ONE exponential: with e = exp(-|yf|) in (0, 1],
+// sigmoid(|yf|) = 1/(1+e) and sigmoid(-|yf|) = e/(1+e); equal to the reference's two evaluations to a few ulp, and
+// saturating to {1, 0} where 1/(1+exp(-x)) does.
+__device__ __forceinline__ void bernoulli_log_derivs(double y, double f, double& fst, double& snd) {
+  const double yf = y * f;
+  const double e = exp_nonpos(-fabs(yf));
+  const double hi = rcp_1to2(1.0 + e), lo = e * hi;
+  const bool pos = yf >= 0.0;
+  double sp = pos ? hi : lo, sm = pos ? lo : hi;
+  if (isnan(yf)) sp = sm = 0.0;                        // nan_to_num(sigmoid(nan)) = 0 (ProbFun.py:24)
+  fst = y * sm;
+  snd = -sp * sm;
+}
+
 // d / simple models: first and second derivative of log p(y|f) w.r.t. f
 //   normal.py:32-36, bernoulli.py:40-51, poisson.py:70-87
 __device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, double s, double& fst,
@@ -67,23 +124,31 @@ __device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, doub
     fst = is2 * (y - f);
     snd = -is2;
   } else if (lik == SSVI_LIK_BERNOULLI) {
-    // sigmoid(yf) and sigmoid(-yf) (bernoulli.py:40-51) from ONE exponential: with e = exp(-|yf|) in (0, 1],
-    // sigmoid(|yf|) = 1/(1+e) and sigmoid(-|yf|) = e/(1+e); equal to the reference's two evaluations to 2 ulp, and
-    // saturating to {1, 0} exactly where 1/(1+exp(-x)) does.
-    const double yf = y * f;
-    const double e = exp(-fabs(yf));
-    const double hi = 1.0 / (1.0 + e), lo = e * hi;
-    const bool pos = yf >= 0.0;
-    double sp = pos ? hi : lo, sm = pos ? lo : hi;
-    if (isnan(yf)) sp = sm = 0.0;                      // nan_to_num(sigmoid(nan)) = 0 (ProbFun.py:24)
-    fst = y * sm;
-    snd = -sp * sm;
+    bernoulli_log_derivs(y, f, fst, snd);
   } else {
     const PoissonTerms pt = poisson_terms(f);
     const double sg = pt.sg, A = pt.A;
     double t = y / A - 1.0;
     fst = nan_to_num(sg * t);
     snd = nan_to_num(sg * (1.0 - sg) * t - y * (sg * sg) / (A * A));
+  }
+}
+
+// Two evaluations at once (the memo / diag sweep kernels hold two samples per lane): the likelihood switch sits OUTSIDE
+// the pair, so the two chains are one basic block and ptxas interleaves them.
+__device__ __forceinline__ void log_pdf_derivs_pair(int lik, double y, double f0, double f1, double s, double& a0,
+                                                    double& b0, double& a1, double& b1) {
+  if (lik == SSVI_LIK_BERNOULLI) {
+    bernoulli_log_derivs(y, f0, a0, b0);
+    bernoulli_log_derivs(y, f1, a1, b1);
+  } else if (lik == SSVI_LIK_NORMAL) {
+    const double is2 = 1.0 / (s * s);
+    a0 = is2 * (y - f0);
+    a1 = is2 * (y - f1);
+    b0 = b1 = -is2;
+  } else {
+    log_pdf_derivs(lik, y, f0, s, a0, b0);
+    log_pdf_derivs(lik, y, f1, s, a1, b1);
   }
 }
 

@@ -101,6 +101,19 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
+// warp sums of TWO values for half the shuffles and additions of two warp_sum calls: after the first exchange even
+// lanes carry a's pair sums and odd lanes b's; the butterfly then runs over lane pairs.  Every lane gets both totals.
+__device__ __forceinline__ void warp_sum2(double& a, double& b, int lane) {
+  const bool odd = lane & 1;
+  double keep = odd ? b : a;
+  keep += __shfl_xor_sync(0xffffffffu, odd ? a : b, 1);
+#pragma unroll
+  for (int o = 16; o > 1; o >>= 1) keep += __shfl_xor_sync(0xffffffffu, keep, o);
+  const double other = __shfl_xor_sync(0xffffffffu, keep, 1);
+  a = odd ? other : keep;
+  b = odd ? keep : other;
+}
+
 __device__ __forceinline__ double ldz(const double* p, int64_t i) { return __ldg(p + i); }
 __device__ __forceinline__ double ldz(const float* p, int64_t i) { return (double)__ldg(p + i); }
 
