@@ -376,11 +376,19 @@ static int launch_sweep_diag(SsviHandle* h, const DevView& v, int64_t n_chunks, 
                              const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows,
                              const double* w_state, double* partial_out, cudaStream_t st) {
   const size_t smem = diag_cta_smem(v.N, v.D, v.k1);
-  auto kern = accumulate_diag_kernel<NOTH, ZT, SECOND, LIN>;
-  CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
-                                              entry_ids, rows, w_state, (const ZT*)h->z_other, (const ZT*)h->z_own,
-                                              (const ZT*)h->r_w, (const ZT*)h->z_f, partial_out);
+  if constexpr (LIN) {                                  // closed-form weights, two entries per warp step
+    auto kern = accumulate_diag_lin_kernel<NOTH, ZT>;
+    CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
+                                                entry_ids, rows, w_state, (const ZT*)h->z_other, (const ZT*)h->z_own,
+                                                (const ZT*)h->r_w, (const ZT*)h->z_f, partial_out);
+  } else {
+    auto kern = accumulate_diag_kernel<NOTH, ZT, SECOND>;
+    CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
+                                                entry_ids, rows, w_state, (const ZT*)h->z_other, (const ZT*)h->z_own,
+                                                (const ZT*)h->r_w, (const ZT*)h->z_f, partial_out);
+  }
   CUDA_TRY(h, cudaGetLastError());
   return SSVI_OK;
 }

@@ -318,6 +318,9 @@ def test_sweep_l2_tiled_launch_order_matches_untiled(dims, D, lik, P, W, nb, off
     ([5, 4, 4], 20, 64, "robust+quad", "normal", 3, 64, False),  # SSVI_TF_robust(quadrature=True), diagonal
     ([6, 5, 4], 9, 32, "simple", "normal", 2, 3, True),          # closed-form (LIN) instance: odd D, two k-tiles
     ([6, 5, 4], 64, 48, "simple", "normal", 3, 64, True),        # LIN: three k-tiles, every lane busy
+    ([2, 40, 30], 10, 16, "simple", "normal", 1, 2000, False),   # LIN: ~960-entry chunks (a warp walks > 32 entries)
+    ([3, 33, 29], 6, 32, "simple", "normal", 2, 2000, True),     # LIN: long chunks, odd per-warp counts (lone last entry)
+    ([2, 40, 30], 10, 16, "d", "bernoulli", 1, 2000, False),     # one-entry kernel on the same long chunks
 ])
 def test_sweep_diag_path_matches_generic_and_oracle(dims, D, k1, model, lik, P, W, offs):
     """Diagonal covariance, full sweep through the slot-major shared-noise kernel == the generic kernel == the oracle."""
