@@ -288,16 +288,23 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
 // SSVI_TF_simple + normal likelihood (BASELINE config 4), entry-blocked.
 //
 // The one-entry-at-a-time kernel above reads the N staged noise blocks from shared memory once per ENTRY: N*k1*DP*8 bytes
-// (102 KB at config 4) against ~1300 FP64 instructions, so the shared-memory datapath (128 B/clk/SM), not the FP64 pipe,
-// sets its pace.  Here a warp walks its entries TWO at a time: every noise / own-sample double2 read from shared memory
-// serves both entries (half the bytes per unit, two independent FMA chains per lane).  The predictive means of T samples
-// of both entries (2T partial sums per lane) go through ONE transposing shuffle reduction, after which lane l holds
-// f of entry (l >> 4); the closed-form weight  w_k = (y - f_k - ws_k * mean_i z_f[i][k]) / (s^2 k1)
-// (SSVI_TF_simple.py:35-38 with normal.py:32-36: the k2 mean is linear in f) is handed round the warp through 2T doubles
-// of shared memory and applied to the v kept in registers.  ws_k * zbar_k and sum_k ws_k are constants of the chunk.
+// (102 KB at config 4) against ~1100 FP64 instructions, so the shared-memory datapath (128 B/clk/SM), not the FP64 pipe,
+// sets its pace.  Here a warp walks its entries E at a time: every noise / own-sample double2 read from shared memory
+// serves E entries (1/E of the bytes per unit, E independent FMA chains per lane).  The predictive means of T samples
+// of the E entries (E*T partial sums per lane) go through ONE transposing shuffle reduction, after which every lane
+// holds f of one (entry, sample) of the tile; the closed-form weight  w_k = (y - f_k - ws_k * mean_i z_f[i][k]) / (s^2 k1)
+// (SSVI_TF_simple.py:35-38 with normal.py:32-36: the k2 mean is linear in f) is handed round the warp through E*T
+// doubles of shared memory and applied to the v kept in registers.  ws_k * zbar_k and sum_k ws_k are constants of the
+// chunk.  A group's missing entries (end of the warp's list) run with m = sqrt S = 0, i.e. v = 0: they add exact zeros.
 // ---------------------------------------------------------------------------------------------------------------------
+#ifndef SSVI_DIAG_LIN_E
+#define SSVI_DIAG_LIN_E 4                               // entries per warp step: 2 or 4
+#endif
 #ifndef SSVI_DIAG_LIN_T
-#define SSVI_DIAG_LIN_T 8                               // samples per reduction tile (k1 % T == 0); 4 or 8
+#define SSVI_DIAG_LIN_T 4                               // samples per reduction tile; E*T is 8 or 16, k1 % T == 0
+#endif
+#ifndef SSVI_DIAG_LIN_PF
+#define SSVI_DIAG_LIN_PF 0                              // next group's gathered rows prefetched into registers
 #endif
 
 // sum over the 32 lanes of p[0..7]; on return lane l holds the total of index (l >> 2) (all four lanes of a quad)
@@ -320,11 +327,42 @@ __device__ __forceinline__ double transpose_reduce8(double (&p)[8], int lane) {
   r += __shfl_xor_sync(0xffffffffu, r, 1);
   return r;
 }
+// transpose_reduce16 for E = 4 entries x T = 4 samples, p[4 e' + kk], when the lanes of quarter q = (lane >> 3) keep entry
+// e' ^ q in slot e': the two entry-splitting stages then keep / give the same registers in every lane (no selects);
+// on return lane l holds the total of entry (l >> 3), sample (l >> 1) & 3 -- index (l >> 1), as transpose_reduce16.
+__device__ __forceinline__ double transpose_reduce16_perm(double (&p)[16], int lane) {
+  const bool b2 = (lane & 4) != 0, b1 = (lane & 2) != 0;
+  double r8[8], r4[4], r2[2];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) r8[j] = p[j] + __shfl_xor_sync(0xffffffffu, p[j + 8], 16);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) r4[j] = r8[j] + __shfl_xor_sync(0xffffffffu, r8[j + 4], 8);
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+    const double give = b2 ? r4[j] : r4[j + 2], keep = b2 ? r4[j + 2] : r4[j];
+    r2[j] = keep + __shfl_xor_sync(0xffffffffu, give, 4);
+  }
+  const double give = b1 ? r2[0] : r2[1], keep = b1 ? r2[1] : r2[0];
+  double r = keep + __shfl_xor_sync(0xffffffffu, give, 2);
+  r += __shfl_xor_sync(0xffffffffu, r, 1);
+  return r;
+}
+__device__ __forceinline__ double transpose_reduce_group(double (&p)[16], int lane) { return transpose_reduce16(p, lane); }
+__device__ __forceinline__ double transpose_reduce_group(double (&p)[8], int lane) { return transpose_reduce8(p, lane); }
 
-__device__ __forceinline__ double transpose_reduce_pair(double (&p)[16], int lane) { return transpose_reduce16(p, lane); }
-__device__ __forceinline__ double transpose_reduce_pair(double (&p)[8], int lane) { return transpose_reduce8(p, lane); }
+// (mean, sqrt S) of this lane's two components of row `col` of mode-`d` sampler cache; zeros when !live or beyond D
+__device__ __forceinline__ void diag_load_row(const DevView& v, int d, int32_t col, bool live, int n0, int n1, int D,
+                                              double (&m)[2], double (&s)[2]) {
+  const double* src = v.sampler[d] + (int64_t)col * v.srow_len;
+  m[0] = (live && n0 < D) ? src[n0] : 0.0;
+  m[1] = (live && n1 < D) ? src[n1] : 0.0;
+  s[0] = (live && n0 < D) ? src[D + n0] : 0.0;
+  s[1] = (live && n1 < D) ? src[D + n1] : 0.0;
+}
 
-template <int NOTH, typename ZT>
+// CD: the rank as a compile-time constant (with k1 == 64), 0 = read D and k1 from the view: every shared-memory address
+// of the sample loop becomes base + immediate.
+template <int NOTH, typename ZT, int E, int T, bool PF, int CD>
 __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
     DevView v, int64_t n_chunks, const int32_t* __restrict__ chunk_row, const int64_t* __restrict__ chunk_start,
     const int32_t* __restrict__ chunk_len, const int32_t* __restrict__ chunk_slot,
@@ -332,18 +370,20 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
     const double* __restrict__ w_state, const ZT* __restrict__ z_other, const ZT* __restrict__ z_own,
     const ZT* __restrict__ r_w, const ZT* __restrict__ z_f, double* __restrict__ partial_out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  constexpr int T = SSVI_DIAG_LIN_T;
-  static_assert(T == 4 || T == 8, "tile of 4 or 8 samples");
+  constexpr int R = E * T;                              // values per lane entering one reduction
+  static_assert((E == 2 || E == 4) && (R == 8 || R == 16) && (T % 2) == 0, "E*T partial sums per reduction: 8 or 16");
+  constexpr bool PERM = (E == 4 && T == 4);             // slot e' of quarter-warp q works on entry e' ^ q (see above)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t c = blockIdx.x;
   if (c >= n_chunks) return;
-  const int N = v.N, D = v.D, k1 = v.k1, DP = diag_dp(D), dim = v.dim;
+  const int N = v.N, D = CD ? CD : v.D, k1 = CD ? 64 : v.k1, DP = diag_dp(D), dim = v.dim;
+  const int qperm = PERM ? (lane >> 3) : 0;
   const int blk_stride = k1 * DP;
-  // shared memory (inside the diag_cta_smem budget): noise blocks | ck [k1] | ws [k1] | per-warp weights [2T] | reduction
+  // shared memory (inside the diag_cta_smem budget): noise blocks | ck [k1] | ws [k1] | per-warp weights [R] | reduction
   double* zs = reinterpret_cast<double*>(smem_raw);                      // [N][k1][DP]: other modes, then own sample
   double* CK = zs + (size_t)N * blk_stride;
   double* WSK = CK + k1;
-  double* Wt = WSK + k1 + warp * (2 * T);
+  double* Wt = WSK + k1 + warp * R;
   double* red = zs + (size_t)N * blk_stride + 4 * k1 * 2;
 
   const int64_t row = rows[chunk_row[c]];
@@ -412,14 +452,14 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
   const int zoff = n0 < DP ? n0 : 0;                    // idle lanes (n0 >= D) read valid noise against m = s = 0
   __syncthreads();
 
-  double g0 = 0.0, g1 = 0.0, G0 = 0.0, G1 = 0.0;
+  double g0 = 0.0, g1 = 0.0, G0 = 0.0, G1 = 0.0, H0 = 0.0, H1 = 0.0;
   const double inv_k1 = 1.0 / (double)k1;
   const double is2 = 1.0 / (v.lik_param * v.lik_param);
   const double alpha = is2 * inv_k1;
   const double* zo = zs + (size_t)(N - 1) * blk_stride;
-  const int e_mine = lane >> 4;                                          // entry of the pair whose f this lane receives
-  const int k_mine = (T == 8) ? ((lane >> 1) & 7) : ((lane >> 2) & 3);   // and which sample of the tile
-  const bool writer = (T == 8) ? ((lane & 1) == 0) : ((lane & 3) == 0);
+  const int idx_mine = (R == 16) ? (lane >> 1) : (lane >> 2);            // which of the R totals this lane receives
+  const int e_mine = idx_mine / T, k_mine = idx_mine % T;
+  const bool writer = (R == 16) ? ((lane & 1) == 0) : ((lane & 3) == 0);
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
     const int nb = min(32, my_cnt - b0);
@@ -434,49 +474,43 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
         for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
       }
     }
-    // gathered (mean, sqrt S) rows of the first pair (a missing second entry repeats the first, with weight zero)
-    double mn[2][NOTH][2], sn[2][NOTH][2];
+    double mn[PF ? E : 1][NOTH][2], sn[PF ? E : 1][NOTH][2];
+    if (PF) {                                           // gathered (mean, sqrt S) rows of the first group
 #pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int ee = min(e, nb - 1);
+      for (int e = 0; e < E; ++e)
 #pragma unroll
-      for (int jj = 0; jj < NOTH; ++jj) {
-        const double* src = v.sampler[od[jj]] + (int64_t)__shfl_sync(0xffffffffu, my_col[jj], ee) * v.srow_len;
-        mn[e][jj][0] = n0 < D ? src[n0] : 0.0;
-        mn[e][jj][1] = n1 < D ? src[n1] : 0.0;
-        sn[e][jj][0] = n0 < D ? src[D + n0] : 0.0;
-        sn[e][jj][1] = n1 < D ? src[D + n1] : 0.0;
-      }
+        for (int jj = 0; jj < NOTH; ++jj)
+          diag_load_row(v, od[jj], __shfl_sync(0xffffffffu, my_col[jj], min(e ^ qperm, 31)), (e ^ qperm) < nb, n0, n1,
+                        D, mn[e][jj], sn[e][jj]);
     }
-    for (int el = 0; el < nb; el += 2) {
-      const bool two = el + 1 < nb;
-      const double y_mine = __shfl_sync(0xffffffffu, my_y, (e_mine && two) ? el + 1 : el);
-      double m[2][NOTH][2], s[2][NOTH][2];
+    for (int el = 0; el < nb; el += E) {
+      const double y_mine = __shfl_sync(0xffffffffu, my_y, min(el + e_mine, nb - 1));
+      double m[E][NOTH][2], s[E][NOTH][2];
 #pragma unroll
-      for (int e = 0; e < 2; ++e)
-#pragma unroll
-        for (int jj = 0; jj < NOTH; ++jj) {
-          m[e][jj][0] = mn[e][jj][0];
-          m[e][jj][1] = mn[e][jj][1];
-          s[e][jj][0] = sn[e][jj][0];
-          s[e][jj][1] = sn[e][jj][1];
-        }
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {                      // prefetch the next pair's rows (past the end: the last entry)
-        const int ee = min(el + 2 + e, nb - 1);
+      for (int e = 0; e < E; ++e)
 #pragma unroll
         for (int jj = 0; jj < NOTH; ++jj) {
-          const double* src = v.sampler[od[jj]] + (int64_t)__shfl_sync(0xffffffffu, my_col[jj], ee) * v.srow_len;
-          mn[e][jj][0] = n0 < D ? src[n0] : 0.0;
-          mn[e][jj][1] = n1 < D ? src[n1] : 0.0;
-          sn[e][jj][0] = n0 < D ? src[D + n0] : 0.0;
-          sn[e][jj][1] = n1 < D ? src[D + n1] : 0.0;
+          if (PF) {
+            m[e][jj][0] = mn[e][jj][0];
+            m[e][jj][1] = mn[e][jj][1];
+            s[e][jj][0] = sn[e][jj][0];
+            s[e][jj][1] = sn[e][jj][1];
+          } else {
+            diag_load_row(v, od[jj], __shfl_sync(0xffffffffu, my_col[jj], min(el + (e ^ qperm), 31)),
+                          el + (e ^ qperm) < nb, n0, n1, D, m[e][jj], s[e][jj]);
+          }
         }
+      if (PF) {                                         // the next group's rows travel while this one is worked on
+#pragma unroll
+        for (int e = 0; e < E; ++e)
+#pragma unroll
+          for (int jj = 0; jj < NOTH; ++jj)
+            diag_load_row(v, od[jj], __shfl_sync(0xffffffffu, my_col[jj], min(el + E + (e ^ qperm), 31)),
+                          el + E + (e ^ qperm) < nb, n0, n1, D, mn[e][jj], sn[e][jj]);
       }
-      double sq[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
       for (int tile = 0; tile < k1 / T; ++tile) {
-        double p[2 * T];
-        double vk[2][T][2];
+        double p[R];
+        double vk[E][T][2];
 #pragma unroll
         for (int kk = 0; kk < T; ++kk) {
           const int k = tile * T + kk;
@@ -486,7 +520,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
             z[jj] = *reinterpret_cast<const double2*>(zs + (size_t)jj * blk_stride + k * DP + zoff);
           const double2 u = *reinterpret_cast<const double2*>(zo + k * DP + zoff);
 #pragma unroll
-          for (int e = 0; e < 2; ++e) {
+          for (int e = 0; e < E; ++e) {
             double v0 = fma(s[e][0][0], z[0].x, m[e][0][0]), v1 = fma(s[e][0][1], z[0].y, m[e][0][1]);
 #pragma unroll
             for (int jj = 1; jj < NOTH; ++jj) {
@@ -494,38 +528,36 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
               v1 *= fma(s[e][jj][1], z[jj].y, m[e][jj][1]);
             }
             p[e * T + kk] = fma(u.y, v1, u.x * v0);
-            sq[e][0] = fma(v0, v0, sq[e][0]);
-            sq[e][1] = fma(v1, v1, sq[e][1]);
+            // sum_k v^2 (Di): d2 log p / df2 = -1/s^2 for every sample, so the weight -0.5 / (s^2 k1) is applied once,
+            // at the end of the chunk; two accumulators per component keep the FMA chains short
+            if (e & 1) {
+              H0 = fma(v0, v0, H0);
+              H1 = fma(v1, v1, H1);
+            } else {
+              G0 = fma(v0, v0, G0);
+              G1 = fma(v1, v1, G1);
+            }
             vk[e][kk][0] = v0;
             vk[e][kk][1] = v1;
           }
         }
-        const double f = transpose_reduce_pair(p, lane);
-        double w = alpha * (y_mine - f - CK[tile * T + k_mine]);
-        if (e_mine && !two) w = 0.0;
+        double f;
+        if constexpr (PERM) f = transpose_reduce16_perm(p, lane); else f = transpose_reduce_group(p, lane);
+        const double w = alpha * (y_mine - f - CK[tile * T + k_mine]);
         __syncwarp();
-        if (writer) Wt[e_mine * T + k_mine] = w;
+        if (writer) Wt[idx_mine] = w;
         __syncwarp();
 #pragma unroll
         for (int kk = 0; kk < T; kk += 2) {
-          const double2 wa = *reinterpret_cast<const double2*>(Wt + kk);
-          const double2 wb = *reinterpret_cast<const double2*>(Wt + T + kk);
-          g0 = fma(wa.x, vk[0][kk][0], g0);
-          g1 = fma(wa.x, vk[0][kk][1], g1);
-          g0 = fma(wb.x, vk[1][kk][0], g0);
-          g1 = fma(wb.x, vk[1][kk][1], g1);
-          g0 = fma(wa.y, vk[0][kk + 1][0], g0);
-          g1 = fma(wa.y, vk[0][kk + 1][1], g1);
-          g0 = fma(wb.y, vk[1][kk + 1][0], g0);
-          g1 = fma(wb.y, vk[1][kk + 1][1], g1);
+#pragma unroll
+          for (int e = 0; e < E; ++e) {
+            const double2 w2 = *reinterpret_cast<const double2*>(Wt + (e ^ qperm) * T + kk);
+            g0 = fma(w2.x, vk[e][kk][0], g0);
+            g1 = fma(w2.x, vk[e][kk][1], g1);
+            g0 = fma(w2.y, vk[e][kk + 1][0], g0);
+            g1 = fma(w2.y, vk[e][kk + 1][1], g1);
+          }
         }
-      }
-      // d2 log p / df2 = -1/s^2 for every sample: Di weight -0.5 / (s^2 k1), applied once at the end of the chunk
-      G0 += sq[0][0];
-      G1 += sq[0][1];
-      if (two) {
-        G0 += sq[1][0];
-        G1 += sq[1][1];
       }
     }
   }
@@ -533,8 +565,8 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
   // ---- CTA reduction in fixed warp order; chunk record [di (D) | Di (D) | si_sum | count] -----------------------------
   {
     const double dwc = -0.5 * alpha;
-    G0 *= dwc;
-    G1 *= dwc;
+    G0 = (G0 + H0) * dwc;
+    G1 = (G1 + H1) * dwc;
   }
   double* rw = red + warp * (2 * DP + 2);
   if (n0 < DP) {
@@ -547,7 +579,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
     // si takes mean_k2 snd * ws = -ws_k / s^2 of every (entry, sample): the same sum for each of this warp's entries
     double wsum = 0.0;
     for (int k = 0; k < k1; ++k) wsum += WSK[k];
-    rw[2 * DP] = -is2 * wsum * (double)my_cnt;
+    rw[2 * DP] = -is2 * wsum * (double)max(my_cnt, 0);
   }
   __syncthreads();
   double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;

@@ -376,8 +376,11 @@ static int launch_sweep_diag(SsviHandle* h, const DevView& v, int64_t n_chunks, 
                              const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows,
                              const double* w_state, double* partial_out, cudaStream_t st) {
   const size_t smem = diag_cta_smem(v.N, v.D, v.k1);
-  if constexpr (LIN) {                                  // closed-form weights, two entries per warp step
-    auto kern = accumulate_diag_lin_kernel<NOTH, ZT>;
+  if constexpr (LIN) {                                  // closed-form weights, SSVI_DIAG_LIN_E entries per warp step
+    // BASELINE config 4's shape (4-way, D = 50, k1 = 64) has an instance with the rank compiled in
+    const bool c4 = NOTH == 3 && v.D == 50 && v.k1 == 64;
+    auto kern = c4 ? accumulate_diag_lin_kernel<NOTH, ZT, SSVI_DIAG_LIN_E, SSVI_DIAG_LIN_T, (SSVI_DIAG_LIN_PF != 0), (NOTH == 3 ? 50 : 0)>
+                   : accumulate_diag_lin_kernel<NOTH, ZT, SSVI_DIAG_LIN_E, SSVI_DIAG_LIN_T, (SSVI_DIAG_LIN_PF != 0), 0>;
     CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
                                                 entry_ids, rows, w_state, (const ZT*)h->z_other, (const ZT*)h->z_own,
