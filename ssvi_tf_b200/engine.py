@@ -162,6 +162,7 @@ class Engine(object):
         self.D = int(cfg["D"])
         self.diag = bool(cfg["diag"])
         self.device = torch.device(device)
+        self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count   # 148 on a B200
         self.chunk_entries = int(chunk_entries)
         self.table_budget_bytes = int(table_budget_bytes)      # L2-resident sample table of the sweep path
         self.sweep_chunk_entries = int(sweep_chunk_entries)
@@ -461,7 +462,14 @@ class Engine(object):
         s_idx = np.arange(P, dtype=np.int64)[:, None]
         b0 = (s_idx - off[None, :]) % P                          # first position of row r that reads slot s
         cnt = np.where(lens[None, :] > b0, (lens[None, :] - b0 + P - 1) // P, 0)      # [P, n]
-        W = self.sweep_chunk_entries * (4 if self.diag else 1)   # diagonal: a CTA stages N noise blocks per chunk
+        W = self.sweep_chunk_entries
+        if self.diag:
+            # diagonal: a CTA stages N noise blocks (100 KB at config 4) per chunk, so chunks are as long as the launch
+            # can afford: 16x the base length while that still leaves >= 8 waves of CTAs (2 per SM), else 8x, else 4x
+            for mult in (16, 8, 4):
+                if mult == 4 or int(((cnt + W * mult - 1) // (W * mult)).sum()) >= 8 * 2 * self.sm_count:
+                    W *= mult
+                    break
         nseg = (cnt + W - 1) // W                                # [P, n]
         flat_cnt, flat_seg = cnt.reshape(-1), nseg.reshape(-1)   # (slot, row) order == launch order
         pair_start = np.zeros(P * n + 1, dtype=np.int64)
