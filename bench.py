@@ -46,6 +46,9 @@ CONFIGS = {
     # diagnostic (not a BASELINE config): C5's rank with an index space whose one-slot sample table fits in L2
     "c5l2": dict(dims=[2500, 2500, 2500], nnz=50_000_000, D=32, lik="normal", model="d", diag=False, k1=64,
                  k2=64, desc="diagnostic: real 2500^3, 5e7 nnz, D=32, normal, SSVI_TF_d full cov"),
+    # diagnostic (not a BASELINE config): C4's shape under SSVI_TF_d (the other diagonal-covariance sweep kernel)
+    "c4d": dict(dims=[500, 500, 500, 100], nnz=100_000_000, D=50, lik="normal", model="d", diag=True, k1=64,
+                k2=64, desc="diagnostic: real 500x500x500x100, 1e8 nnz, D=50, normal, SSVI_TF_d diag cov"),
 }
 DATATYPE = {"normal": "real", "bernoulli": "binary", "poisson": "count"}
 

@@ -590,3 +590,179 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
   }
   if (tid == 0) out[2 * D + 1] = (double)len;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// SSVI_TF_d with a diagonal covariance, entry-blocked the same way (four entries per warp step, four samples per
+// reduction tile, entries permuted per quarter-warp).  The weights are uniform in k (SSVI_TF_d.py:31-57, quirk Q3: the
+// derivatives are averaged over k1, then broadcast), so nothing but sum_k v and sum_k v^2 of each entry is kept: after
+// the reduction of a tile lane l holds f of entry (l >> 3), sample 4 tile + ((l >> 1) & 3), in both lanes of a pair;
+// even lanes keep the even tiles' value, odd lanes the odd tiles', and every second tile each lane evaluates ONE
+// likelihood derivative pair -- every (entry, sample) exactly once across the quarter-warp.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int NOTH, typename ZT>
+__global__ void __launch_bounds__(128, 2) accumulate_diag_d_kernel(
+    DevView v, int64_t n_chunks, const int32_t* __restrict__ chunk_row, const int64_t* __restrict__ chunk_start,
+    const int32_t* __restrict__ chunk_len, const int32_t* __restrict__ chunk_slot,
+    const int64_t* __restrict__ chunk_out, const int64_t* __restrict__ entry_ids, const int64_t* __restrict__ rows,
+    const ZT* __restrict__ z_other, const ZT* __restrict__ z_own, double* __restrict__ partial_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int E = 4, T = 4;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t c = blockIdx.x;
+  if (c >= n_chunks) return;
+  const int N = v.N, D = v.D, k1 = v.k1, DP = diag_dp(D), dim = v.dim;
+  const int blk_stride = k1 * DP;
+  const int qperm = lane >> 3;
+  double* zs = reinterpret_cast<double*>(smem_raw);                      // [N][k1][DP]: other modes, then own sample
+  double* red = zs + (size_t)N * blk_stride + 4 * k1 * 2;
+
+  const int64_t row = rows[chunk_row[c]];
+  const int64_t start = chunk_start[c];
+  const int len = chunk_len[c], slot = chunk_slot[c];
+
+  int od[NOTH];
+  {
+    int jj = 0;
+#pragma unroll
+    for (int d = 0; d < SSVI_MAX_ORDER; ++d)
+      if (d < N && d != dim && jj < NOTH) od[jj++] = d;
+  }
+  const int my_cnt = (len - warp + 3) >> 2;             // this warp's entries: w, w+4, ...
+  double my_y = 0.0;
+  int32_t my_col[NOTH];
+#pragma unroll
+  for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
+  if (lane < my_cnt) {
+    const int64_t eid = entry_ids[start + (int64_t)lane * 4 + warp];
+    my_y = v.vals[eid];
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
+  }
+  for (int b = 0; b < N - 1; ++b) {
+    const ZT* src = z_other + ((int64_t)slot * (N - 1) + b) * v.zblk;
+    double* dst = zs + (size_t)b * blk_stride;
+    for (int idx = tid; idx < D * k1; idx += 128) {
+      const int cc = idx / k1, k = idx - cc * k1;
+      dst[k * DP + cc] = (double)src[idx];
+    }
+    if (DP != D)
+      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
+  }
+  {
+    const ZT* src = z_own + (int64_t)slot * v.zblk;
+    const double* own = v.sampler[dim] + row * (int64_t)v.srow_len;
+    double* dst = zs + (size_t)(N - 1) * blk_stride;
+    for (int idx = tid; idx < D * k1; idx += 128) {
+      const int cc = idx / k1, k = idx - cc * k1;
+      dst[k * DP + cc] = fma(own[D + cc], (double)src[idx], own[cc]);
+    }
+    if (DP != D)
+      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
+  }
+  const int n0 = 2 * lane, n1 = 2 * lane + 1;
+  const int zoff = n0 < DP ? n0 : 0;
+  __syncthreads();
+
+  double g0 = 0.0, g1 = 0.0, G0 = 0.0, G1 = 0.0;
+  const double inv_k1 = 1.0 / (double)k1;
+  const double* zo = zs + (size_t)(N - 1) * blk_stride;
+  const int e_mine = lane >> 3;
+
+  for (int b0 = 0; b0 < my_cnt; b0 += 32) {
+    const int nb = min(32, my_cnt - b0);
+    if (b0 > 0) {
+      my_y = 0.0;
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
+      if (lane < nb) {
+        const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
+        my_y = v.vals[eid];
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
+      }
+    }
+    for (int el = 0; el < nb; el += E) {
+      const double y_mine = __shfl_sync(0xffffffffu, my_y, min(el + e_mine, nb - 1));
+      double m[E][NOTH][2], s[E][NOTH][2];
+#pragma unroll
+      for (int e = 0; e < E; ++e)
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj)
+          diag_load_row(v, od[jj], __shfl_sync(0xffffffffu, my_col[jj], min(el + (e ^ qperm), 31)),
+                        el + (e ^ qperm) < nb, n0, n1, D, m[e][jj], s[e][jj]);
+      double sv[E][2], sq[E][2];
+#pragma unroll
+      for (int e = 0; e < E; ++e) sv[e][0] = sv[e][1] = sq[e][0] = sq[e][1] = 0.0;
+      double sum_a = 0.0, sum_d = 0.0;
+      for (int tile2 = 0; tile2 < k1 / (2 * T); ++tile2) {
+        double fsel = 0.0;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          double p[E * T];
+#pragma unroll
+          for (int kk = 0; kk < T; ++kk) {
+            const int k = (2 * tile2 + h) * T + kk;
+            double2 z[NOTH];
+#pragma unroll
+            for (int jj = 0; jj < NOTH; ++jj)
+              z[jj] = *reinterpret_cast<const double2*>(zs + (size_t)jj * blk_stride + k * DP + zoff);
+            const double2 u = *reinterpret_cast<const double2*>(zo + k * DP + zoff);
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+              double v0 = fma(s[e][0][0], z[0].x, m[e][0][0]), v1 = fma(s[e][0][1], z[0].y, m[e][0][1]);
+#pragma unroll
+              for (int jj = 1; jj < NOTH; ++jj) {
+                v0 *= fma(s[e][jj][0], z[jj].x, m[e][jj][0]);
+                v1 *= fma(s[e][jj][1], z[jj].y, m[e][jj][1]);
+              }
+              p[e * T + kk] = fma(u.y, v1, u.x * v0);
+              sv[e][0] += v0;
+              sv[e][1] += v1;
+              sq[e][0] = fma(v0, v0, sq[e][0]);
+              sq[e][1] = fma(v1, v1, sq[e][1]);
+            }
+          }
+          const double f = transpose_reduce16_perm(p, lane);
+          if ((lane & 1) == h) fsel = f;
+        }
+        double fa, fb;
+        log_pdf_derivs(v.lik, y_mine, fsel, v.lik_param, fa, fb);
+        sum_a += fa;
+        sum_d += fb;
+      }
+      // SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1 (the 8 lanes of a quarter-warp hold one entry's samples)
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) {
+        sum_a += __shfl_xor_sync(0xffffffffu, sum_a, o);
+        sum_d += __shfl_xor_sync(0xffffffffu, sum_d, o);
+      }
+      const double aw_q = (sum_a * inv_k1) * inv_k1, dw_q = 0.5 * (sum_d * inv_k1) * inv_k1;
+#pragma unroll
+      for (int e = 0; e < E; ++e) {                       // slot e of this lane worked on entry e ^ qperm
+        const double aw = __shfl_sync(0xffffffffu, aw_q, (e ^ qperm) << 3);
+        const double dw = __shfl_sync(0xffffffffu, dw_q, (e ^ qperm) << 3);
+        g0 = fma(aw, sv[e][0], g0);
+        g1 = fma(aw, sv[e][1], g1);
+        G0 = fma(dw, sq[e][0], G0);
+        G1 = fma(dw, sq[e][1], G1);
+      }
+    }
+  }
+
+  double* rw = red + warp * (2 * DP + 2);
+  if (n0 < DP) {
+    rw[n0] = g0;
+    rw[n1] = g1;
+    rw[DP + n0] = G0;
+    rw[DP + n1] = G1;
+  }
+  if (lane == 0) rw[2 * DP] = 0.0;
+  __syncthreads();
+  double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;
+  const int rs = 2 * DP + 2;
+  for (int i = tid; i < 2 * D + 1; i += 128) {
+    const int src = i < D ? i : (i < 2 * D ? DP + (i - D) : 2 * DP);
+    out[i] = ((red[src] + red[rs + src]) + red[2 * rs + src]) + red[3 * rs + src];
+  }
+  if (tid == 0) out[2 * D + 1] = (double)len;
+}
