@@ -162,6 +162,7 @@ class Engine(object):
         self.D = int(cfg["D"])
         self.diag = bool(cfg["diag"])
         self.device = torch.device(device)
+        self._dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
         self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count   # 148 on a B200
         self.chunk_entries = int(chunk_entries)
         self.table_budget_bytes = int(table_budget_bytes)      # L2-resident sample table of the sweep path
@@ -268,12 +269,33 @@ class Engine(object):
 
     # -------------------------------------------------------------------------------------------
     def _call(self, fn, *args):
-        with torch.cuda.device(self.device):
+        if torch.cuda.current_device() == self._dev_index:       # the per-row path makes ~10 calls per row update
             rc = fn(self.h, *args)
+        else:
+            with torch.cuda.device(self.device):
+                rc = fn(self.h, *args)
         _lib.check(self.lib, self.h, rc)
 
     def _stream(self):
-        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        """The caller's current CUDA stream on this device, as the void* the C ABI takes."""
+        return ctypes.c_void_p(torch._C._cuda_getCurrentRawStream(self._dev_index))
+
+    def _pack_to_device(self, arrays):
+        """Host int32 / int64 arrays -> device tensors through ONE host-to-device copy (16-byte aligned sections of one
+        buffer): a per-row plan is eight small tables, and eight synchronous copies were half of a row update's host
+        time (tools/factorize_profile.py)."""
+        arrays = [np.ascontiguousarray(a) for a in arrays]
+        offs, total = [], 0
+        for a in arrays:
+            total = (total + 15) & ~15
+            offs.append(total)
+            total += a.nbytes
+        buf = np.empty(max(total, 16), dtype=np.uint8)
+        for a, o in zip(arrays, offs):
+            buf[o:o + a.nbytes] = a.reshape(-1).view(np.uint8)
+        d = torch.from_numpy(buf).to(self.device)
+        return [d[o:o + a.nbytes].view(torch.int32 if a.dtype == np.int32 else torch.int64)
+                for a, o in zip(arrays, offs)]
 
     def _bind_state(self):
         def arr(lst):
@@ -336,9 +358,10 @@ class Engine(object):
             raise AssertionError("; ".join(t for b, t in FLAG_TEXT.items() if f.value & b))
 
     # -------------------------------------------------------------------------------------------
-    def _chunk_tables(self, dim, rows_h, seg_start, seg_len, slot_offset=None):
+    def _chunk_tables(self, dim, rows_h, seg_start, seg_len, slot_offset=None, extra=()):
         """rows_h: host int64 row ids; seg_start/seg_len: each row's minibatch as a run of entry_ids;
-        slot_offset: per-row position of this shard's first entry inside the GLOBAL minibatch (multi-GPU)."""
+        slot_offset: per-row position of this shard's first entry inside the GLOBAL minibatch (multi-GPU).
+        Returns the five device tables followed by the device copies of the host arrays in `extra` (one upload)."""
         W = self.chunk_entries
         nch = (seg_len + W - 1) // W
         rcp = np.zeros(len(rows_h) + 1, dtype=np.int64)
@@ -348,12 +371,10 @@ class Engine(object):
         t = np.arange(total, dtype=np.int64) - rcp[chunk_row]
         chunk_start = seg_start[chunk_row] + t * W
         chunk_len = np.minimum(W, seg_len[chunk_row] - t * W)
-        dev = self.device
         slot0 = t * W if slot_offset is None else t * W + np.asarray(slot_offset, dtype=np.int64)[chunk_row]
-        return (torch.as_tensor(chunk_row.astype(np.int32)).to(dev), torch.as_tensor(chunk_start).to(dev),
-                torch.as_tensor(chunk_len.astype(np.int32)).to(dev),
-                torch.as_tensor(slot0.astype(np.int32)).to(dev),
-                torch.as_tensor(rcp).to(dev))
+        return self._pack_to_device([chunk_row.astype(np.int32), chunk_start.astype(np.int64),
+                                     chunk_len.astype(np.int32), slot0.astype(np.int32), rcp] +
+                                    [np.asarray(a, dtype=np.int64) for a in extra])
 
     def plan_full(self, dim, rows=None, slot_offset=None):
         """Every observed entry of every listed row (scale = 1): the throughput sweep."""
@@ -364,9 +385,8 @@ class Engine(object):
         rows_h = np.arange(self.dims[dim], dtype=np.int64) if rows is None else np.asarray(rows, dtype=np.int64)
         rp = self.rowptr_h[dim]
         seg_start, seg_len = rp[rows_h], rp[rows_h + 1] - rp[rows_h]
-        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset)
-        plan = SweepPlan(dim, torch.as_tensor(rows_h).to(self.device), torch.as_tensor(seg_len).to(self.device),
-                         self.perm[dim], tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
+        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset, extra=(rows_h, seg_len))
+        plan = SweepPlan(dim, tabs[5], tabs[6], self.perm[dim], tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
         self._full_plans[key] = plan
         return plan
 
@@ -391,10 +411,9 @@ class Engine(object):
             ids.append(seg)
         seg_start = np.zeros(len(rows_h), dtype=np.int64)
         np.cumsum(seg_len[:-1], out=seg_start[1:])
-        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset)
-        entry_ids = torch.as_tensor(np.concatenate(ids) if ids else np.zeros(0, np.int64)).to(self.device)
-        return SweepPlan(dim, torch.as_tensor(rows_h).to(self.device), torch.as_tensor(lens).to(self.device),
-                         entry_ids, tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
+        entry_ids = np.concatenate(ids) if ids else np.zeros(0, np.int64)
+        tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset, extra=(rows_h, lens, entry_ids))
+        return SweepPlan(dim, tabs[5], tabs[6], tabs[7], tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
 
     def plan_subsampled_sweep(self, dim, batch_size, generator=None):
         """The reference's minibatch rule (SSVI_TF_interface.py:170-174) for EVERY row of mode `dim` at once, drawn on
