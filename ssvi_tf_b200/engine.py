@@ -172,6 +172,7 @@ class Engine(object):
         self.sweep_tile_min_entries = float(sweep_tile_min_entries)
         self.record_budget_bytes = int(record_budget_bytes)    # chunk records kept per stream before they are folded
         self._side_streams = []
+        self._pin_ring = None
         self.noise_dtype = noise_dtype
         if cfg["mean_update"] not in UPDATE_IDS or cfg["cov_update"] not in UPDATE_IDS:
             raise Exception("Unidentified update formula for covariance param")   # SSVI_TF_interface.py:612, 632
@@ -280,6 +281,8 @@ class Engine(object):
         """The caller's current CUDA stream on this device, as the void* the C ABI takes."""
         return ctypes.c_void_p(torch._C._cuda_getCurrentRawStream(self._dev_index))
 
+    _PIN_SLOT, _PIN_SLOTS = 1 << 16, 16                    # pinned staging ring of _pack_to_device
+
     def _pack_to_device(self, arrays):
         """Host int32 / int64 arrays -> device tensors through ONE host-to-device copy (16-byte aligned sections of one
         buffer): a per-row plan is eight small tables, and eight synchronous copies were half of a row update's host
@@ -290,10 +293,33 @@ class Engine(object):
             total = (total + 15) & ~15
             offs.append(total)
             total += a.nbytes
-        buf = np.empty(max(total, 16), dtype=np.uint8)
-        for a, o in zip(arrays, offs):
-            buf[o:o + a.nbytes] = a.reshape(-1).view(np.uint8)
-        d = torch.from_numpy(buf).to(self.device)
+        total = max(total, 16)
+        if total <= self._PIN_SLOT:
+            # small plans (the per-row path) go through a ring of pinned slots with an asynchronous copy, so the host
+            # builds the next row's plan while the device still works on this one; a slot is reused only after the
+            # copy that read it has completed
+            if self._pin_ring is None:
+                self._pin_ring = torch.empty((self._PIN_SLOTS, self._PIN_SLOT), dtype=torch.uint8).pin_memory()
+                self._pin_np = self._pin_ring.numpy()
+                self._pin_events = [None] * self._PIN_SLOTS
+                self._pin_next = 0
+            i = self._pin_next
+            self._pin_next = (i + 1) % self._PIN_SLOTS
+            if self._pin_events[i] is not None:
+                self._pin_events[i].synchronize()
+            buf = self._pin_np[i]
+            for a, o in zip(arrays, offs):
+                buf[o:o + a.nbytes] = a.reshape(-1).view(np.uint8)
+            d = torch.empty((total,), dtype=torch.uint8, device=self.device)
+            d.copy_(self._pin_ring[i, :total], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            self._pin_events[i] = ev
+        else:
+            buf = np.empty(total, dtype=np.uint8)
+            for a, o in zip(arrays, offs):
+                buf[o:o + a.nbytes] = a.reshape(-1).view(np.uint8)
+            d = torch.from_numpy(buf).to(self.device)
         return [d[o:o + a.nbytes].view(torch.int32 if a.dtype == np.int32 else torch.int64)
                 for a, o in zip(arrays, offs)]
 
