@@ -10,11 +10,12 @@
 //
 // Lanes run over components: lane l owns n = 2l, 2l+1, so the per-row accumulators g[n], G[n] (di, Di) live in
 // registers across the whole chunk and need no reduction.  The predictive mean f_k = sum_n u[n][k] v[n][k] is reduced
-// over lanes 16 samples at a time with a transposing shuffle reduction (16 shuffles per 16 samples), after which every
-// lane owns two samples' f and evaluates their likelihood weights (the k2 second-layer loop for SSVI_TF_simple /
-// SSVI_TF_robust).  SSVI_TF_d (weights uniform in k, SSVI_TF_d.py:31-57 quirk Q3) needs one pass; simple / robust
-// re-evaluate v in a second pass once the per-sample weights are known.  SSVI_TF_simple with the normal likelihood has
-// its own entry-blocked kernel at the end of this file (accumulate_diag_lin_kernel).
+// over lanes with a transposing shuffle reduction, after which every lane owns a few samples' f.  Three kernels:
+//   accumulate_diag_kernel      SSVI_TF_simple / SSVI_TF_robust, any likelihood: the k2 second-layer loop gives per-sample
+//                               weights, then a second pass re-evaluates v (one entry per warp step)
+//   accumulate_diag_lin_kernel  SSVI_TF_simple + normal likelihood (BASELINE config 4): closed-form weights, four entries
+//                               per warp step sharing every shared-memory read
+//   accumulate_diag_d_kernel    SSVI_TF_d (weights uniform in k, SSVI_TF_d.py:31-57 quirk Q3), entry-blocked the same way
 #pragma once
 #include "accumulate_generic.cuh"
 
@@ -22,6 +23,85 @@ __host__ __device__ inline int diag_dp(int D) { return (D + 1) & ~1; }          
 // shared memory of one CTA (4 warps): N noise blocks [k][DP] as doubles | per-warp weights [k1] double2 | reduction
 __host__ __device__ inline size_t diag_cta_smem(int N, int D, int k1) {
   return (size_t)N * k1 * diag_dp(D) * 8 + (size_t)4 * k1 * 16 + (size_t)4 * (2 * diag_dp(D) + 2) * 8;
+}
+
+// ---- pieces shared by the three sweep kernels of this file ---------------------------------------------------------------
+// the other modes of the sweep's mode, ascending
+template <int NOTH>
+__device__ __forceinline__ void diag_other_modes(int N, int dim, int (&od)[NOTH]) {
+  int jj = 0;
+#pragma unroll
+  for (int d = 0; d < SSVI_MAX_ORDER; ++d)
+    if (d < N && d != dim && jj < NOTH) od[jj++] = d;
+}
+
+// Entries b0 .. b0+31 of warp `warp`'s list (the chunk's entries warp, warp+4, ...): lane l fetches the value and the
+// other-mode rows of entry b0 + l; the warp later reads them with shuffles.  Lanes past the end hold y = 0, row 0.
+template <int NOTH>
+__device__ __forceinline__ void diag_fetch_entries(const DevView& v, const int64_t* __restrict__ entry_ids, int64_t start,
+                                                   int b0, int nb, int lane, int warp, const int (&od)[NOTH],
+                                                   double& my_y, int32_t (&my_col)[NOTH]) {
+  my_y = 0.0;
+#pragma unroll
+  for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
+  if (lane < nb) {
+    const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
+    my_y = v.vals[eid];
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * v.N + od[jj]];
+  }
+}
+
+// Stage the chunk's slot in shared memory as doubles: the N-1 noise blocks of the other modes, transposed from the
+// pool's [c][k] to [k][DP], then the own-row sample U[k][c] = m[c] + sqrt(S)[c] z_own[c][k] (ui samples,
+// SSVI_TF_interface.py:251-254) -- once per chunk.  The caller synchronises.
+template <typename ZT>
+__device__ __forceinline__ void diag_stage_chunk(const DevView& v, double* __restrict__ zs, const ZT* __restrict__ z_other,
+                                                 const ZT* __restrict__ z_own, int slot, int64_t row, int D, int k1,
+                                                 int DP, int tid) {
+  const int N = v.N, blk_stride = k1 * DP;
+  for (int b = 0; b < N - 1; ++b) {
+    const ZT* src = z_other + ((int64_t)slot * (N - 1) + b) * v.zblk;
+    double* dst = zs + (size_t)b * blk_stride;
+    for (int idx = tid; idx < D * k1; idx += 128) {
+      const int cc = idx / k1, k = idx - cc * k1;
+      dst[k * DP + cc] = (double)src[idx];
+    }
+    if (DP != D)
+      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
+  }
+  const ZT* src = z_own + (int64_t)slot * v.zblk;
+  const double* own = v.sampler[v.dim] + row * (int64_t)v.srow_len;
+  double* dst = zs + (size_t)(N - 1) * blk_stride;
+  for (int idx = tid; idx < D * k1; idx += 128) {
+    const int cc = idx / k1, k = idx - cc * k1;
+    dst[k * DP + cc] = fma(own[D + cc], (double)src[idx], own[cc]);
+  }
+  if (DP != D)
+    for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
+}
+
+// CTA reduction in fixed warp order and the chunk record [di (D) | Di (D) | si_sum | count]: every lane hands in the
+// sums of its two components, lane 0 of each warp the warp's si.
+__device__ __forceinline__ void diag_write_record(const DevView& v, double* __restrict__ red, double* __restrict__ out,
+                                                  int D, int DP, int len, int tid, double g0, double g1, double G0,
+                                                  double G1, double si_warp) {
+  const int lane = tid & 31, warp = tid >> 5, n0 = 2 * lane;
+  const int rs = 2 * DP + 2;
+  double* rw = red + warp * rs;
+  if (n0 < DP) {
+    rw[n0] = g0;
+    rw[n0 + 1] = g1;
+    rw[DP + n0] = G0;
+    rw[DP + n0 + 1] = G1;
+  }
+  if (lane == 0) rw[2 * DP] = si_warp;
+  __syncthreads();
+  for (int i = tid; i < 2 * D + 1; i += 128) {
+    const int src = i < D ? i : (i < 2 * D ? DP + (i - D) : 2 * DP);
+    out[i] = ((red[src] + red[rs + src]) + red[2 * rs + src]) + red[3 * rs + src];
+  }
+  if (tid == 0) out[2 * D + 1] = (double)len;
 }
 
 // sum over the 32 lanes of p[0..15]; on return lane l holds the total of sample (l >> 1) (both lanes of a pair)
@@ -68,8 +148,9 @@ __device__ __forceinline__ void diag_v(const double* __restrict__ zs, int blk_st
   }
 }
 
-// One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.
-template <int NOTH, typename ZT, bool SECOND>
+// One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.  SSVI_TF_simple / SSVI_TF_robust with
+// any likelihood (SSVI_TF_d and the closed-form simple + normal case have the entry-blocked kernels below).
+template <int NOTH, typename ZT>
 __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
     DevView v, int64_t n_chunks, const int32_t* __restrict__ chunk_row, const int64_t* __restrict__ chunk_start,
     const int32_t* __restrict__ chunk_len, const int32_t* __restrict__ chunk_slot,
@@ -89,52 +170,18 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
   const int64_t row = rows[chunk_row[c]];
   const int64_t start = chunk_start[c];
   const int len = chunk_len[c], slot = chunk_slot[c];
-  const double w_sigma = SECOND ? w_state[0] : 1.0;
+  const double w_sigma = w_state[0];
 
   int od[NOTH];
-  {
-    int jj = 0;
-#pragma unroll
-    for (int d = 0; d < SSVI_MAX_ORDER; ++d)
-      if (d < N && d != dim && jj < NOTH) od[jj++] = d;
-  }
+  diag_other_modes<NOTH>(N, dim, od);
 
   // ---- this warp's entries (w, w+4, ...): ids, values and gathered-row offsets fetched lane-parallel -----------------
   const int my_cnt = (len - warp + 3) >> 2;
-  double my_y = 0.0;
+  double my_y;
   int32_t my_col[NOTH];
-#pragma unroll
-  for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
-  if (lane < my_cnt) {
-    const int64_t eid = entry_ids[start + (int64_t)lane * 4 + warp];
-    my_y = v.vals[eid];
-#pragma unroll
-    for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
-  }
+  diag_fetch_entries<NOTH>(v, entry_ids, start, 0, my_cnt, lane, warp, od, my_y, my_col);
 
-  // ---- stage the slot's noise blocks as doubles, [blk][k][c] (pool layout is [c][k]) ----------------------------------
-  for (int b = 0; b < N - 1; ++b) {
-    const ZT* src = z_other + ((int64_t)slot * (N - 1) + b) * v.zblk;
-    double* dst = zs + (size_t)b * blk_stride;
-    for (int idx = tid; idx < D * k1; idx += 128) {
-      const int cc = idx / k1, k = idx - cc * k1;
-      dst[k * DP + cc] = (double)src[idx];
-    }
-    if (DP != D)
-      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
-  }
-  {
-    // own row (ui samples, SSVI_TF_interface.py:251-254): U[k][c] = m[c] + sqrt(S)[c] z_own[c][k], once per chunk
-    const ZT* src = z_own + (int64_t)slot * v.zblk;
-    const double* own = v.sampler[dim] + row * (int64_t)v.srow_len;
-    double* dst = zs + (size_t)(N - 1) * blk_stride;
-    for (int idx = tid; idx < D * k1; idx += 128) {
-      const int cc = idx / k1, k = idx - cc * k1;
-      dst[k * DP + cc] = fma(own[D + cc], (double)src[idx], own[cc]);
-    }
-    if (DP != D)
-      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
-  }
+  diag_stage_chunk<ZT>(v, zs, z_other, z_own, slot, row, D, k1, DP, tid);
   // lane l owns components 2l, 2l+1 (gathered rows read as zero beyond D: v is then an exact zero there)
   const int n0 = 2 * lane, n1 = 2 * lane + 1;
   const int zoff = n0 < DP ? n0 : 0;                    // idle lanes (n0 >= D) read valid noise against m = s = 0
@@ -142,22 +189,11 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
 
   double g0 = 0.0, g1 = 0.0, G0 = 0.0, G1 = 0.0, si_part = 0.0;
   bool bad = false;
-  const double inv_k1 = 1.0 / (double)k1;
   const double* zo = zs + (size_t)(N - 1) * blk_stride;
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
     const int nb = min(32, my_cnt - b0);
-    if (b0 > 0) {
-      my_y = 0.0;
-#pragma unroll
-      for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
-      if (lane < nb) {
-        const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
-        my_y = v.vals[eid];
-#pragma unroll
-        for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
-      }
-    }
+    if (b0 > 0) diag_fetch_entries<NOTH>(v, entry_ids, start, b0, nb, lane, warp, od, my_y, my_col);
     // gathered rows of the first entry
     double mn[NOTH][2], sn[NOTH][2];
 #pragma unroll
@@ -189,8 +225,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
           sn[jj][1] = n1 < D ? src[D + n1] : 0.0;
         }
       }
-      // ---- pass 1: f_k, and for SSVI_TF_d the plain sums over k ---------------------------------------------------
-      double sv0 = 0.0, sv1 = 0.0, sq0 = 0.0, sq1 = 0.0;
+      // ---- pass 1: f_k ---------------------------------------------------------------------------------------------
       double fk[2] = {0.0, 0.0};                         // lane owns samples 16*(2a + (lane&1)) + (lane>>1), a = 0, 1
       for (int tile = 0; tile < (k1 >> 4); ++tile) {
         double p[16];
@@ -201,40 +236,14 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
           diag_v<NOTH>(zs, blk_stride, k, DP, zoff, m, s, v0, v1);
           const double2 u = *reinterpret_cast<const double2*>(zo + k * DP + zoff);
           p[kk] = fma(u.y, v1, u.x * v0);
-          if (!SECOND) {
-            sv0 += v0;
-            sv1 += v1;
-            sq0 = fma(v0, v0, sq0);
-            sq1 = fma(v1, v1, sq1);
-          }
         }
         const double f = transpose_reduce16(p, lane);
         if ((tile & 1) == (lane & 1)) {
           if (tile < 2) fk[0] = f; else fk[1] = f;
         }
       }
-      if (!SECOND) {
-        // SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1, then broadcast
-        double sum_a = 0.0, sum_d = 0.0;
-#pragma unroll
-        for (int a = 0; a < 2; ++a) {
-          const int k = 16 * (2 * a + (lane & 1)) + (lane >> 1);
-          if (k < k1) {
-            double fa, fb;
-            log_pdf_derivs(v.lik, y, fk[a], v.lik_param, fa, fb);
-            sum_a += fa;
-            sum_d += fb;
-          }
-        }
-        sum_a = warp_sum(sum_a) * inv_k1;
-        sum_d = warp_sum(sum_d) * inv_k1;
-        const double aw = sum_a * inv_k1, dw = 0.5 * sum_d * inv_k1;
-        g0 = fma(aw, sv0, g0);
-        g1 = fma(aw, sv1, g1);
-        G0 = fma(dw, sq0, G0);
-        G1 = fma(dw, sq1, G1);
-      } else {
-        // simple / robust: per-sample weights (second-layer k2 loop), then pass 2 re-evaluates v
+      {
+        // per-sample weights (second-layer k2 loop), then pass 2 re-evaluates v
         const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? 1.0 / factorial_ref(y) : 1.0;
         __syncwarp();
 #pragma unroll
@@ -260,28 +269,10 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_kernel(
     }
   }
 
-  // ---- CTA reduction in fixed warp order; chunk record [di (D) | Di (D) | si_sum | count] -----------------------------
   si_part = warp_sum(si_part);
   const unsigned anybad = __ballot_sync(0xffffffffu, bad);
-  double* rw = red + warp * (2 * DP + 2);
-  if (n0 < DP) {
-    rw[n0] = g0;
-    rw[n1] = g1;
-    rw[DP + n0] = G0;
-    rw[DP + n1] = G1;
-  }
-  if (lane == 0) {
-    rw[2 * DP] = si_part;
-    if (anybad) atomicOr(v.flags, SSVI_FLAG_PHI_ZERO);
-  }
-  __syncthreads();
-  double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;
-  const int rs = 2 * DP + 2;
-  for (int i = tid; i < 2 * D + 1; i += 128) {
-    const int src = i < D ? i : (i < 2 * D ? DP + (i - D) : 2 * DP);
-    out[i] = ((red[src] + red[rs + src]) + red[2 * rs + src]) + red[3 * rs + src];
-  }
-  if (tid == 0) out[2 * D + 1] = (double)len;
+  if (lane == 0 && anybad) atomicOr(v.flags, SSVI_FLAG_PHI_ZERO);
+  diag_write_record(v, red, partial_out + chunk_out[c] * (int64_t)v.acc_len, D, DP, len, tid, g0, g1, G0, G1, si_part);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -392,47 +383,14 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
   const double w_sigma = w_state[0];
 
   int od[NOTH];
-  {
-    int jj = 0;
-#pragma unroll
-    for (int d = 0; d < SSVI_MAX_ORDER; ++d)
-      if (d < N && d != dim && jj < NOTH) od[jj++] = d;
-  }
+  diag_other_modes<NOTH>(N, dim, od);
 
   const int my_cnt = (len - warp + 3) >> 2;             // this warp's entries: w, w+4, ...
-  double my_y = 0.0;
+  double my_y;
   int32_t my_col[NOTH];
-#pragma unroll
-  for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
-  if (lane < my_cnt) {
-    const int64_t eid = entry_ids[start + (int64_t)lane * 4 + warp];
-    my_y = v.vals[eid];
-#pragma unroll
-    for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
-  }
+  diag_fetch_entries<NOTH>(v, entry_ids, start, 0, my_cnt, lane, warp, od, my_y, my_col);
 
-  // ---- stage the slot's noise blocks as doubles, [blk][k][c] (pool layout is [c][k]), and the own-row sample ----------
-  for (int b = 0; b < N - 1; ++b) {
-    const ZT* src = z_other + ((int64_t)slot * (N - 1) + b) * v.zblk;
-    double* dst = zs + (size_t)b * blk_stride;
-    for (int idx = tid; idx < D * k1; idx += 128) {
-      const int cc = idx / k1, k = idx - cc * k1;
-      dst[k * DP + cc] = (double)src[idx];
-    }
-    if (DP != D)
-      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
-  }
-  {
-    const ZT* src = z_own + (int64_t)slot * v.zblk;
-    const double* own = v.sampler[dim] + row * (int64_t)v.srow_len;
-    double* dst = zs + (size_t)(N - 1) * blk_stride;
-    for (int idx = tid; idx < D * k1; idx += 128) {
-      const int cc = idx / k1, k = idx - cc * k1;
-      dst[k * DP + cc] = fma(own[D + cc], (double)src[idx], own[cc]);
-    }
-    if (DP != D)
-      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
-  }
+  diag_stage_chunk<ZT>(v, zs, z_other, z_own, slot, row, D, k1, DP, tid);
   // chunk constants: ws_k = w_sigma^2 * rayleigh draw (SSVI_TF_interface.py:258-261), ck_k = ws_k * mean_i z_f[i][k]
   for (int k = tid; k < k1; k += 128) {
     const ZT* zf = z_f + (int64_t)slot * v.k2 * k1 + k;
@@ -463,17 +421,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
     const int nb = min(32, my_cnt - b0);
-    if (b0 > 0) {
-      my_y = 0.0;
-#pragma unroll
-      for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
-      if (lane < nb) {
-        const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
-        my_y = v.vals[eid];
-#pragma unroll
-        for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
-      }
-    }
+    if (b0 > 0) diag_fetch_entries<NOTH>(v, entry_ids, start, b0, nb, lane, warp, od, my_y, my_col);
     double mn[PF ? E : 1][NOTH][2], sn[PF ? E : 1][NOTH][2];
     if (PF) {                                           // gathered (mean, sqrt S) rows of the first group
 #pragma unroll
@@ -568,27 +516,12 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_lin_kernel(
     G0 = (G0 + H0) * dwc;
     G1 = (G1 + H1) * dwc;
   }
-  double* rw = red + warp * (2 * DP + 2);
-  if (n0 < DP) {
-    rw[n0] = g0;
-    rw[n1] = g1;
-    rw[DP + n0] = G0;
-    rw[DP + n1] = G1;
-  }
-  if (lane == 0) {
-    // si takes mean_k2 snd * ws = -ws_k / s^2 of every (entry, sample): the same sum for each of this warp's entries
-    double wsum = 0.0;
+  // si takes mean_k2 snd * ws = -ws_k / s^2 of every (entry, sample): the same sum for each of this warp's entries
+  double wsum = 0.0;
+  if (lane == 0)
     for (int k = 0; k < k1; ++k) wsum += WSK[k];
-    rw[2 * DP] = -is2 * wsum * (double)max(my_cnt, 0);
-  }
-  __syncthreads();
-  double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;
-  const int rs = 2 * DP + 2;
-  for (int i = tid; i < 2 * D + 1; i += 128) {
-    const int src = i < D ? i : (i < 2 * D ? DP + (i - D) : 2 * DP);
-    out[i] = ((red[src] + red[rs + src]) + red[2 * rs + src]) + red[3 * rs + src];
-  }
-  if (tid == 0) out[2 * D + 1] = (double)len;
+  diag_write_record(v, red, partial_out + chunk_out[c] * (int64_t)v.acc_len, D, DP, len, tid, g0, g1, G0, G1,
+                    -is2 * wsum * (double)max(my_cnt, 0));
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -621,44 +554,12 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_d_kernel(
   const int len = chunk_len[c], slot = chunk_slot[c];
 
   int od[NOTH];
-  {
-    int jj = 0;
-#pragma unroll
-    for (int d = 0; d < SSVI_MAX_ORDER; ++d)
-      if (d < N && d != dim && jj < NOTH) od[jj++] = d;
-  }
+  diag_other_modes<NOTH>(N, dim, od);
   const int my_cnt = (len - warp + 3) >> 2;             // this warp's entries: w, w+4, ...
-  double my_y = 0.0;
+  double my_y;
   int32_t my_col[NOTH];
-#pragma unroll
-  for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
-  if (lane < my_cnt) {
-    const int64_t eid = entry_ids[start + (int64_t)lane * 4 + warp];
-    my_y = v.vals[eid];
-#pragma unroll
-    for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
-  }
-  for (int b = 0; b < N - 1; ++b) {
-    const ZT* src = z_other + ((int64_t)slot * (N - 1) + b) * v.zblk;
-    double* dst = zs + (size_t)b * blk_stride;
-    for (int idx = tid; idx < D * k1; idx += 128) {
-      const int cc = idx / k1, k = idx - cc * k1;
-      dst[k * DP + cc] = (double)src[idx];
-    }
-    if (DP != D)
-      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
-  }
-  {
-    const ZT* src = z_own + (int64_t)slot * v.zblk;
-    const double* own = v.sampler[dim] + row * (int64_t)v.srow_len;
-    double* dst = zs + (size_t)(N - 1) * blk_stride;
-    for (int idx = tid; idx < D * k1; idx += 128) {
-      const int cc = idx / k1, k = idx - cc * k1;
-      dst[k * DP + cc] = fma(own[D + cc], (double)src[idx], own[cc]);
-    }
-    if (DP != D)
-      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.0;
-  }
+  diag_fetch_entries<NOTH>(v, entry_ids, start, 0, my_cnt, lane, warp, od, my_y, my_col);
+  diag_stage_chunk<ZT>(v, zs, z_other, z_own, slot, row, D, k1, DP, tid);
   const int n0 = 2 * lane, n1 = 2 * lane + 1;
   const int zoff = n0 < DP ? n0 : 0;
   __syncthreads();
@@ -670,17 +571,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_d_kernel(
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
     const int nb = min(32, my_cnt - b0);
-    if (b0 > 0) {
-      my_y = 0.0;
-#pragma unroll
-      for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = 0;
-      if (lane < nb) {
-        const int64_t eid = entry_ids[start + (int64_t)(b0 + lane) * 4 + warp];
-        my_y = v.vals[eid];
-#pragma unroll
-        for (int jj = 0; jj < NOTH; ++jj) my_col[jj] = v.coords[eid * N + od[jj]];
-      }
-    }
+    if (b0 > 0) diag_fetch_entries<NOTH>(v, entry_ids, start, b0, nb, lane, warp, od, my_y, my_col);
     for (int el = 0; el < nb; el += E) {
       const double y_mine = __shfl_sync(0xffffffffu, my_y, min(el + e_mine, nb - 1));
       double m[E][NOTH][2], s[E][NOTH][2];
@@ -749,20 +640,5 @@ __global__ void __launch_bounds__(128, 2) accumulate_diag_d_kernel(
     }
   }
 
-  double* rw = red + warp * (2 * DP + 2);
-  if (n0 < DP) {
-    rw[n0] = g0;
-    rw[n1] = g1;
-    rw[DP + n0] = G0;
-    rw[DP + n1] = G1;
-  }
-  if (lane == 0) rw[2 * DP] = 0.0;
-  __syncthreads();
-  double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;
-  const int rs = 2 * DP + 2;
-  for (int i = tid; i < 2 * D + 1; i += 128) {
-    const int src = i < D ? i : (i < 2 * D ? DP + (i - D) : 2 * DP);
-    out[i] = ((red[src] + red[rs + src]) + red[2 * rs + src]) + red[3 * rs + src];
-  }
-  if (tid == 0) out[2 * D + 1] = (double)len;
+  diag_write_record(v, red, partial_out + chunk_out[c] * (int64_t)v.acc_len, D, DP, len, tid, g0, g1, G0, G1, 0.0);
 }

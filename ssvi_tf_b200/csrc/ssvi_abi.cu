@@ -391,7 +391,7 @@ static int launch_sweep_diag(SsviHandle* h, const DevView& v, int64_t n_chunks, 
     kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
                                                 entry_ids, rows, (const ZT*)h->z_other, (const ZT*)h->z_own, partial_out);
   } else {
-    auto kern = accumulate_diag_kernel<NOTH, ZT, SECOND>;
+    auto kern = accumulate_diag_kernel<NOTH, ZT>;
     CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
                                                 entry_ids, rows, w_state, (const ZT*)h->z_other, (const ZT*)h->z_own,
