@@ -238,6 +238,17 @@ int ssvi_hyper_reduce(SsviHandle* h, int32_t dim, double* out /*double[3]*/, voi
  * entries int32 [n][N]. */
 int ssvi_predict_mean(SsviHandle* h, const int32_t* entries, int64_t n, double* out, void* stream);
 
+/* Minibatch selection of update_natural_param_batch (:164-178) for a list of rows of ONE mode, drawn on the device:
+ * a row holding more than batch_size entries keeps batch_size of them -- a uniform random subset without replacement,
+ * np.random.choice(len, batch_size, replace=False) (:170-172) -- and a shorter row keeps all, in append order.
+ *   rowptr int64 [n_dim + 1], perm int64 [nnz]: the mode's inverted index (Tensor.find_observed_ui, Tensor.py:251-258)
+ *   rows int64 [n_rows];  seg_start int64 [n_rows]: where each row's picks begin in out;  out int64: entry ids
+ * Counter-based generator keyed by (seed, row): a call is reproducible, a new seed gives a fresh draw.
+ * batch_size <= 2048. */
+int ssvi_draw_minibatches(SsviHandle* h, int64_t n_rows, const int64_t* rows, const int64_t* rowptr,
+                          const int64_t* perm, int32_t batch_size, uint64_t seed, const int64_t* seg_start,
+                          int64_t* out, void* stream);
+
 /* Per-entry Monte-Carlo estimators of the report path, from the bound noise pool (entry e reads slot
  * (slot0 + e) mod P; mode 0 draws from z_own, mode d >= 1 from z_other[.][d-1]; k1 draws, k2 noise-layer draws):
  *   what = SSVI_EST_EXPECTED_OBS (0)  out[e] = mean link(fs)        estimate_expected_observation_via_sampling (:1168-1189)

@@ -62,6 +62,7 @@ SIGNATURES = {
     "ssvi_hyper_reduce": (ctypes.c_int, [_P, _I32, _P, _P]),
     "ssvi_estimate_entries": (ctypes.c_int, [_P, _I32, _P, _P, _I64, _I32, _P, _P, _P]),
     "ssvi_predict_mean": (ctypes.c_int, [_P, _P, _I64, _P, _P]),
+    "ssvi_draw_minibatches": (ctypes.c_int, [_P, _I64, _P, _P, _P, _I32, ctypes.c_uint64, _P, _P, _P]),
     "ssvi_check_flags": (ctypes.c_int, [_P, ctypes.POINTER(_I32), _P]),
 }
 

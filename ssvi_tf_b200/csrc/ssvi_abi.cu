@@ -718,6 +718,62 @@ extern "C" int ssvi_predict_mean(SsviHandle* h, const int32_t* entries, int64_t 
   return SSVI_OK;
 }
 
+// ---- minibatch selection on the device (SSVI_TF_interface.py:164-178) -------------------------------------------------------
+// One warp per row.  A row holding more than B entries keeps a uniform random B-subset of its list, drawn without
+// replacement by Floyd's algorithm (for j = len-B .. len-1: t uniform in [0, j]; take t, or j if t was taken already):
+// B sequential steps, the membership test spread over the lanes.  Counter-based RNG (splitmix64 of seed, row, step).
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+__global__ void __launch_bounds__(128) draw_minibatches_kernel(int64_t n_rows, const int64_t* __restrict__ rows,
+                                                               const int64_t* __restrict__ rowptr,
+                                                               const int64_t* __restrict__ perm, int B, uint64_t seed,
+                                                               const int64_t* __restrict__ seg_start,
+                                                               int64_t* __restrict__ out) {
+  extern __shared__ int32_t picks_all[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t r = (int64_t)blockIdx.x * 4 + warp;
+  if (r >= n_rows) return;
+  int32_t* picks = picks_all + warp * B;
+  const int64_t row = rows[r];
+  const int64_t lo = rowptr[row], len = rowptr[row + 1] - lo;
+  int64_t* dst = out + seg_start[r];
+  if (len <= B) {                                       // kept whole, in append order (:170-174)
+    for (int64_t i = lane; i < len; i += 32) dst[i] = perm[lo + i];
+    return;
+  }
+  const uint64_t key = splitmix64(seed ^ splitmix64((uint64_t)row));
+  int cnt = 0;
+  for (int64_t j = len - B; j < len; ++j, ++cnt) {
+    const uint64_t u = splitmix64(key + (uint64_t)cnt);
+    const int32_t t = (int32_t)__umul64hi(u, (uint64_t)(j + 1));          // uniform in [0, j]
+    bool hit = false;
+    for (int i = lane; i < cnt; i += 32) hit |= (picks[i] == t);
+    const bool taken = __any_sync(0xffffffffu, hit);
+    if (lane == 0) picks[cnt] = taken ? (int32_t)j : t;
+    __syncwarp();
+  }
+  for (int i = lane; i < B; i += 32) dst[i] = perm[lo + picks[i]];
+}
+
+extern "C" int ssvi_draw_minibatches(SsviHandle* h, int64_t n_rows, const int64_t* rows, const int64_t* rowptr,
+                                     const int64_t* perm, int32_t batch_size, uint64_t seed, const int64_t* seg_start,
+                                     int64_t* out, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (n_rows == 0) return SSVI_OK;
+  if (n_rows < 0 || !rows || !rowptr || !perm || !seg_start || !out) return fail(h, SSVI_E_INVALID, "draw_minibatches: null pointer%s");
+  if (batch_size < 1 || batch_size > 2048) return fail(h, SSVI_E_INVALID, "draw_minibatches: batch_size must be in [1, 2048]%s");
+  const size_t smem = (size_t)4 * batch_size * sizeof(int32_t);
+  draw_minibatches_kernel<<<(unsigned)((n_rows + 3) / 4), 128, smem, (cudaStream_t)stream>>>(
+      n_rows, rows, rowptr, perm, batch_size, seed, seg_start, out);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
 extern "C" int ssvi_estimate_entries(SsviHandle* h, int32_t what, const int32_t* entries, const double* ys, int64_t n,
                                      int32_t slot0, const double* w_state, double* out, void* stream) {
   if (!h) return SSVI_E_INVALID;

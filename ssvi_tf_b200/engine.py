@@ -443,9 +443,10 @@ class Engine(object):
 
     def plan_subsampled_sweep(self, dim, batch_size, generator=None):
         """The reference's minibatch rule (SSVI_TF_interface.py:170-174) for EVERY row of mode `dim` at once, drawn on
-        the device: rows holding more than batch_size entries keep batch_size of them, chosen uniformly without
-        replacement (one sort of the mode's entry list by (row, uniform key)); shorter rows keep all.  The chunk
-        tables depend on (dim, batch_size) only and are cached; every call draws a fresh subsample.  Single shard."""
+        the device by ssvi_draw_minibatches: rows holding more than batch_size entries keep batch_size of them, a
+        uniform random subset without replacement (one warp per row, no sort of the entry list); shorter rows keep
+        all, in append order.  The chunk tables depend on (dim, batch_size) only and are cached; every call draws a
+        fresh subsample (generator: its seed keys the draws).  Single shard."""
         B = int(batch_size)
         key = (dim, B)
         c = self._sub_plans.get(key)
@@ -457,19 +458,18 @@ class Engine(object):
             np.cumsum(seg_len[:-1], out=seg_start[1:])
             rows_h = np.arange(self.dims[dim], dtype=np.int64)
             tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len)
-            row_of_pos = torch.repeat_interleave(torch.arange(self.dims[dim], device=self.device),
-                                                 torch.as_tensor(lens).to(self.device))
-            pos_in_row = torch.arange(self.nnz, device=self.device) - torch.as_tensor(rp[:-1]).to(self.device)[row_of_pos]
-            lens_d = torch.as_tensor(lens).to(self.device)
-            whole = lens_d[row_of_pos] <= B                # rows kept whole stay in append order (:170-174)
-            c = dict(tabs=tabs, seg_len=seg_len, rows=torch.as_tensor(rows_h).to(self.device),
-                     n_obs=lens_d, row_key=row_of_pos.double(), whole=whole,
-                     frac=pos_in_row.double() / (B + 1), keep=torch.nonzero(pos_in_row < B).squeeze(1))
+            dev = self.device
+            c = dict(tabs=tabs, seg_len=seg_len, rows=torch.as_tensor(rows_h).to(dev),
+                     n_obs=torch.as_tensor(lens).to(dev), rowptr=torch.as_tensor(np.asarray(rp, dtype=np.int64)).to(dev),
+                     seg_start=torch.as_tensor(seg_start).to(dev), total=int(seg_len.sum()), calls=0)
             self._sub_plans[key] = c
-        u = torch.rand(self.nnz, device=self.device, dtype=torch.float64, generator=generator)
-        u = torch.where(c["whole"], c["frac"], u)
-        order = torch.argsort(c["row_key"] + u)            # by row; subsampled rows uniformly shuffled inside
-        entry_ids = self.perm[dim][order[c["keep"]]]
+        c["calls"] += 1
+        base = 319 if generator is None else int(generator.initial_seed())
+        seed = (base * 0x9E3779B1 + dim * 0x85EBCA6B + c["calls"]) & 0xFFFFFFFFFFFFFFFF
+        entry_ids = torch.empty((c["total"],), dtype=torch.int64, device=self.device)
+        self._call(self.lib.ssvi_draw_minibatches, self.dims[dim], _ptr(c["rows"]), _ptr(c["rowptr"]),
+                   _ptr(self.perm[dim]), B, seed, _ptr(c["seg_start"]), _ptr(entry_ids), self._stream())
+        self.launches += 1
         t = c["tabs"]
         return SweepPlan(dim, c["rows"], c["n_obs"], entry_ids, t[0], t[1], t[2], t[3], t[4], c["seg_len"])
 

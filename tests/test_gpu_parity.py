@@ -417,3 +417,39 @@ def test_subsampled_sweep_draws_reference_minibatches_on_device():
         so.rows_step(want, cfg, dim, rows, entries, tapes)
         assert_state_close(engine_dump_state(eng, st0), want, cfg, RTOL, what="subsampled mode %d" % dim)
     eng.close()
+
+
+def test_device_minibatch_draw_is_a_uniform_subset():
+    """ssvi_draw_minibatches: every position of a row's list is kept with probability B / len (2000 independent rows of 40
+    entries, B = 8: binomial(2000, 0.2) per position, five standard deviations), the picks of a row are distinct, and
+    the same seed reproduces the draw."""
+    rng = np.random.default_rng(8)
+    dims, D, B = [500, 8, 5], 4, 8
+    cfg = so.make_config("d", "normal", D, k1=16, k2=4, batch_size=B)
+    grid = np.stack(np.meshgrid(*[np.arange(n) for n in dims], indexing="ij"), axis=-1).reshape(-1, 3)
+    coords = grid[rng.permutation(len(grid))]
+    vals = rng.standard_normal(len(coords))
+    eng = _engine(cfg, dims, coords, vals, chunk_entries=4)
+    rowptr, perm = so.build_index(coords, dims)
+    counts = np.zeros(40, dtype=np.int64)
+    first = None
+    for call in range(4):
+        gen = torch.Generator(device=eng.device)
+        gen.manual_seed(100 + call)
+        ids = eng.plan_subsampled_sweep(0, B, gen).entry_ids.cpu().numpy().reshape(dims[0], B)
+        if call == 0:
+            first = ids.copy()
+        for row in range(dims[0]):
+            own = perm[0][rowptr[0][row]:rowptr[0][row + 1]]           # ascending entry ids (stable sort)
+            pos = np.searchsorted(own, ids[row])
+            assert np.array_equal(own[pos], ids[row]) and len(set(pos.tolist())) == B
+            counts[pos] += 1
+    n = 4 * dims[0]
+    sd = np.sqrt(n * 0.2 * 0.8)
+    assert np.all(np.abs(counts - 0.2 * n) < 5 * sd), counts
+    eng._sub_plans.clear()                                               # same seed, same call number: same draw
+    gen = torch.Generator(device=eng.device)
+    gen.manual_seed(100)
+    again = eng.plan_subsampled_sweep(0, B, gen).entry_ids.cpu().numpy().reshape(dims[0], B)
+    np.testing.assert_array_equal(again, first)
+    eng.close()
