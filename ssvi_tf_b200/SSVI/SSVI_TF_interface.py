@@ -121,6 +121,7 @@ class SSVI_TF(object):
         self._noise_slots = int(noise_slots) if noise_slots else max(int(batch_size), 1)
         self._noise_gen_seed = int(noise_seed)
         self._noise_draws = 0
+        self._minibatch_draws = 0
         self._np_rng = np.random.default_rng(noise_seed)
         self._sub_gen = torch.Generator(device=eng.device)
         self._sub_gen.manual_seed(int(noise_seed) + 7919)
@@ -233,8 +234,10 @@ class SSVI_TF(object):
         lens = np.minimum(rp[rows + 1] - rp[rows], self.batch_size)
         off, _ = self._shard_info(dim, rows, lens)
         _, n_obs = self._shard_info(dim, rows, rp[rows + 1] - rp[rows])
+        self._minibatch_draws += 1                      # the draw itself happens on the device (:170-174)
         plan = self.engine.plan_minibatch(dim, rows, self.batch_size, rng=self._np_rng, sub_idx=sub_idx,
-                                          slot_offset=off)
+                                          slot_offset=off,
+                                          device_seed=self._noise_gen_seed * 0x9E3779B1 + self._minibatch_draws)
         self._run_plan(plan, n_obs)
         return plan
 

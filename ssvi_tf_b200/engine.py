@@ -257,6 +257,7 @@ class Engine(object):
         self._full_plans = {}
         self._sweep_plans = {}
         self._sub_plans = {}
+        self._rowptr_d = {}
         self.sweep_supported = bool(self.lib.ssvi_sweep_supported(self.h))
         self._scratch = {}
         self.launches = 0          # kernels of libssvi_b200 launched through this engine
@@ -416,16 +417,31 @@ class Engine(object):
         self._full_plans[key] = plan
         return plan
 
-    def plan_minibatch(self, dim, rows, batch_size, rng=None, sub_idx=None, slot_offset=None):
+    def plan_minibatch(self, dim, rows, batch_size, rng=None, sub_idx=None, slot_offset=None, device_seed=None):
         """The reference's minibatch (SSVI_TF_interface.py:170-174): rows holding more than batch_size
         entries are subsampled without replacement.  sub_idx: optional {row: index array} (noise-tape
-        item #0) overriding the draw; rng: numpy Generator otherwise."""
+        item #0) overriding the draw; rng: numpy Generator for a host draw; device_seed: draw on the device instead
+        (ssvi_draw_minibatches keyed by this seed: nothing but the chunk tables crosses the bus, and no host copy of
+        the mode's inverted index is needed)."""
         rows_h = np.asarray(rows, dtype=np.int64)
         rp = self.rowptr_h[dim]
         lens = rp[rows_h + 1] - rp[rows_h]
         if not np.any(lens > batch_size):
             return self.plan_full(dim, rows_h, slot_offset)
-        ids, seg_len = [], np.minimum(lens, batch_size)
+        seg_len = np.minimum(lens, batch_size)
+        seg_start = np.zeros(len(rows_h), dtype=np.int64)
+        np.cumsum(seg_len[:-1], out=seg_start[1:])
+        if device_seed is not None and sub_idx is None and batch_size <= 2048:
+            tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset, extra=(rows_h, lens, seg_start))
+            if dim not in self._rowptr_d:
+                self._rowptr_d[dim] = torch.as_tensor(np.asarray(rp, dtype=np.int64)).to(self.device)
+            entry_ids = torch.empty((int(seg_len.sum()),), dtype=torch.int64, device=self.device)
+            self._call(self.lib.ssvi_draw_minibatches, len(rows_h), _ptr(tabs[5]), _ptr(self._rowptr_d[dim]),
+                       _ptr(self.perm[dim]), int(batch_size), int(device_seed) & 0xFFFFFFFFFFFFFFFF, _ptr(tabs[7]),
+                       _ptr(entry_ids), self._stream())
+            self.launches += 1
+            return SweepPlan(dim, tabs[5], tabs[6], entry_ids, tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
+        ids = []
         for r, row in enumerate(rows_h):
             seg = self.perm_h[dim][rp[row]:rp[row + 1]]
             if lens[r] > batch_size:
@@ -435,8 +451,6 @@ class Engine(object):
                     pick = (rng or np.random).choice(int(lens[r]), batch_size, replace=False)
                 seg = seg[pick]
             ids.append(seg)
-        seg_start = np.zeros(len(rows_h), dtype=np.int64)
-        np.cumsum(seg_len[:-1], out=seg_start[1:])
         entry_ids = np.concatenate(ids) if ids else np.zeros(0, np.int64)
         tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset, extra=(rows_h, lens, entry_ids))
         return SweepPlan(dim, tabs[5], tabs[6], tabs[7], tabs[0], tabs[1], tabs[2], tabs[3], tabs[4], seg_len)
