@@ -15,17 +15,20 @@
 //   d      (SSVI_TF_d.py:31-57, quirk Q3): derivatives averaged over k1, then broadcast
 //   simple (SSVI_TF_simple.py:23-40):      second-layer samples fs = f + ws * z_f
 //   robust (SSVI_TF_robust.py:67-169):     pdf ratios, Q6
-template <typename ZT>
+// MODEL / LIK >= 0: the model and the likelihood as compile-time constants (memo_weights_kernel: the k2 loop is then one
+// straight likelihood body whose constants stay in registers); -1: read them from the view.
+template <typename ZT, int MODEL = -1, int LIK = -1>
 __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* __restrict__ r_w,
                                                    const ZT* __restrict__ z_f, int slot, int k, bool active,
                                                    double y, double yfact, double f, double w_sigma,
                                                    double& aw, double& dw, double& si_part, bool& bad) {
   const int k1 = v.k1, k2 = v.k2;
+  const int model = MODEL >= 0 ? MODEL : v.model, lik = LIK >= 0 ? LIK : v.lik;
   const double s = v.lik_param;
   const double inv_k1 = 1.0 / (double)k1;
-  if (v.model == SSVI_MODEL_D) {
+  if (model == SSVI_MODEL_D) {
     double fst = 0.0, snd = 0.0;
-    if (active) log_pdf_derivs(v.lik, y, f, s, fst, snd);
+    if (active) log_pdf_derivs(lik, y, f, s, fst, snd);
     // warp-level partial sums are combined by the caller (needs all k); return raw values
     aw = fst;
     dw = snd;
@@ -38,7 +41,7 @@ __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* _
   const ZT* zf = z_f + (int64_t)slot * k2 * k1 + k;
   // second-layer samples fs = f + ws * z_f (Q2: the Rayleigh draw is the standard deviation); the k2 variates are
   // fetched 8 at a time so the loads are in flight together instead of one L2 round trip per sample
-  if (v.model == SSVI_MODEL_SIMPLE) {
+  if (model == SSVI_MODEL_SIMPLE) {
     double sf = 0.0, ss = 0.0;
     for (int i0 = 0; i0 < k2; i0 += 8) {
       double zz[8];
@@ -48,7 +51,7 @@ __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* _
       for (int j = 0; j < 8; ++j) {
         if (i0 + j < k2) {
           double a, b;
-          log_pdf_derivs(v.lik, y, f + ws * zz[j], s, a, b);
+          log_pdf_derivs(lik, y, f + ws * zz[j], s, a, b);
           sf += a;
           ss += b;
         }
@@ -68,7 +71,7 @@ __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* _
       for (int i2 = 0; i2 < v.quad_n; ++i2) {
         const double wq = __ldg(v.quad + v.quad_n + i2);
         double a, b, c;
-        pdf_derivs(v.lik, y, f + sw * __ldg(v.quad + i2), s, yfact, a, b, c);
+        pdf_derivs(lik, y, f + sw * __ldg(v.quad + i2), s, yfact, a, b, c);
         p += wq * a;
         p1 += wq * b;
         p2 += wq * c;
@@ -81,7 +84,7 @@ __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* _
       for (int i2 = 0; i2 < k2; ++i2) {                // (the pdf terms are too large a body to unroll profitably)
         double fs = f + ws * ldz(zf, (int64_t)i2 * k1);
         double a, b, c;
-        pdf_derivs(v.lik, y, fs, s, yfact, a, b, c);
+        pdf_derivs(lik, y, fs, s, yfact, a, b, c);
         p += a;
         p1 += b;
         p2 += c;

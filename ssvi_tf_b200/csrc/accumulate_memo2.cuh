@@ -171,22 +171,41 @@ __global__ void __launch_bounds__(128, 4) memo_f_kernel(DevView v, MemoView mv, 
 // ---------------------------------------------------------------------------------------------------------------------
 // pass 2: one thread per (entry, sample): the second-layer k2 loop
 // ---------------------------------------------------------------------------------------------------------------------
-template <typename ZT>
-__global__ void __launch_bounds__(256) memo_weights_kernel(DevView v, MemoWork wk, const double* __restrict__ w_state,
-                                                           const ZT* __restrict__ r_w, const ZT* __restrict__ z_f) {
+template <typename ZT, int MODEL, int LIK>
+__global__ void __launch_bounds__(256, 2) memo_weights_kernel(DevView v, MemoWork wk, const double* __restrict__ w_state,
+                                                              const ZT* __restrict__ r_w, const ZT* __restrict__ z_f) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= wk.n * 64) return;
   const int64_t loc = t >> 6;
   const int k = (int)(t & 63);
   const double y = wk.Y[loc];
   const int slot = wk.SL[loc];
-  const double yfact = (v.lik == SSVI_LIK_POISSON && v.model == SSVI_MODEL_ROBUST) ? 1.0 / factorial_ref(y) : 1.0;
+  const double yfact = (LIK == SSVI_LIK_POISSON && MODEL == SSVI_MODEL_ROBUST) ? 1.0 / factorial_ref(y) : 1.0;
   double aw, dw, si = 0.0;
   bool bad = false;
-  likelihood_weights<ZT>(v, r_w, z_f, slot, k, true, y, yfact, wk.F[t], w_state[0], aw, dw, si, bad);
+  likelihood_weights<ZT, MODEL, LIK>(v, r_w, z_f, slot, k, true, y, yfact, wk.F[t], w_state[0], aw, dw, si, bad);
   wk.W[t] = make_double2(aw, dw);
   wk.SI[t] = si;
   if (bad) atomicOr(v.flags, SSVI_FLAG_PHI_ZERO);
+}
+
+// the instance for the handle's (model, likelihood)
+template <typename ZT>
+static void launch_memo_weights(const DevView& v, const MemoWork& wk, const double* w_state, const ZT* r_w, const ZT* z_f,
+                                cudaStream_t st) {
+  const unsigned grid = (unsigned)((wk.n * 64 + 255) / 256);
+#define SSVI_W_CASE(M, L)                                                                                  \
+  if (v.model == M && v.lik == L) {                                                                        \
+    memo_weights_kernel<ZT, M, L><<<grid, 256, 0, st>>>(v, wk, w_state, r_w, z_f);                         \
+    return;                                                                                                \
+  }
+  SSVI_W_CASE(SSVI_MODEL_ROBUST, SSVI_LIK_POISSON)
+  SSVI_W_CASE(SSVI_MODEL_ROBUST, SSVI_LIK_BERNOULLI)
+  SSVI_W_CASE(SSVI_MODEL_ROBUST, SSVI_LIK_NORMAL)
+  SSVI_W_CASE(SSVI_MODEL_SIMPLE, SSVI_LIK_POISSON)
+  SSVI_W_CASE(SSVI_MODEL_SIMPLE, SSVI_LIK_BERNOULLI)
+  SSVI_W_CASE(SSVI_MODEL_SIMPLE, SSVI_LIK_NORMAL)
+#undef SSVI_W_CASE
 }
 
 __host__ __device__ inline int memo_c_smem(int NT, int D) { return 4 * (NT * (NT + 1) / 2) * 512 + 4 * (NT * 8 + 1) * 8; }

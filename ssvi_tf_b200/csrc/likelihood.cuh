@@ -152,6 +152,117 @@ __device__ __forceinline__ void log_pdf_derivs_pair(int lik, double y, double f0
   }
 }
 
+// ---- Poisson pdf terms for the robust model's k1 x k2 loop (4096 evaluations per observed entry at config 3) ------------
+// That loop is ISSUE bound, not FP64-pipe bound, when written with libm: ptxas materialises every 64-bit literal of the
+// inlined exp / log with two UMOVs right before its use (100 of ~490 instructions per evaluation,
+// profiles/r01z_ncu_memo_weights.txt).  Here the coefficients sit in constant memory and are read as instruction operands,
+// the reciprocals are seed + Newton without the slow-path call of a general division, and everything is straight-line:
+//   e = exp(-|f|) in (0, 1],  x = 1 + e in (1, 2],  r = 1/x,  L = log(x)
+//   f >= 0:  1/(1+e^f) = e r,  sigmoid(f) = r,    log(1+e^f) = f + L          f < 0:  r,  e r,  L
+// (for f < 0 that is the reference's log(fl(1 + e^f)) operation for operation; for f >= 0 it agrees to a few ulp).
+__constant__ double SSVI_EXPC[14] = {1.0, 1.0, 0.5, 1.0 / 6.0, 1.0 / 24.0, 1.0 / 120.0, 1.0 / 720.0, 1.0 / 5040.0,
+                                     1.0 / 40320.0, 1.0 / 362880.0, 1.0 / 3628800.0, 1.0 / 39916800.0,
+                                     1.0 / 479001600.0, 1.0 / 6227020800.0};
+// [0..9]: 2/(2n+3), n = 0..9 (atanh series of log);  [10] = ln 2,  [11] = sqrt 2,  [12] = log2(e),  [13] = magic 1.5*2^52
+__constant__ double SSVI_LOGC[16] = {2.0 / 3.0,  2.0 / 5.0,  2.0 / 7.0,  2.0 / 9.0,  2.0 / 11.0, 2.0 / 13.0,
+                                     2.0 / 15.0, 2.0 / 17.0, 2.0 / 19.0, 2.0 / 21.0, 6.93147180559945286227e-01,
+                                     1.41421356237309514547e+00, 1.4426950408889634, 6755399441055744.0,
+                                     -6.93147180369123816490e-01, -1.90821492927058770002e-10};
+
+// exp(x) for x in [-708, 0]: exp_nonpos with the coefficients as constant-bank operands
+__device__ __forceinline__ double exp_nonpos_c(double x) {
+  const double t = fma(x, SSVI_LOGC[12], SSVI_LOGC[13]);
+  const int n = __double2loint(t);
+  const double nd = t - SSVI_LOGC[13];
+  double r = fma(nd, SSVI_LOGC[14], x);
+  r = fma(nd, SSVI_LOGC[15], r);
+  const double r2 = r * r;
+  const double p01 = SSVI_EXPC[0] + r;
+  const double p23 = fma(r, SSVI_EXPC[3], SSVI_EXPC[2]);
+  const double p45 = fma(r, SSVI_EXPC[5], SSVI_EXPC[4]);
+  const double p67 = fma(r, SSVI_EXPC[7], SSVI_EXPC[6]);
+  const double p89 = fma(r, SSVI_EXPC[9], SSVI_EXPC[8]);
+  const double pab = fma(r, SSVI_EXPC[11], SSVI_EXPC[10]);
+  const double pcd = fma(r, SSVI_EXPC[13], SSVI_EXPC[12]);
+  const double r4 = r2 * r2;
+  const double q0 = fma(r2, p23, p01);
+  const double q1 = fma(r2, p67, p45);
+  const double q2 = fma(r2, pab, p89);
+  const double r8 = r4 * r4;
+  const double q3 = fma(r4, pcd, q2);
+  const double s0 = fma(r4, q1, q0);
+  const double p = fma(r8, q3, s0);
+  return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
+
+// 1 / a for a normal, positive a of moderate magnitude: hardware seed + two Newton steps (no special cases)
+__device__ __forceinline__ double rcp_pos(double a) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  double e = fma(-a, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-a, y, 1.0);
+  return fma(y, e, y);
+}
+
+// log(x) for x in [1, 2]: x > sqrt 2 is halved (log x = ln 2 + log(x/2)); with s = (x - 1) / (x + 1), |s| <= 0.1716,
+// log x = 2 atanh(s) = 2 s + s^3 (2/3 + 2/5 s^2 + ... + 2/21 s^18), truncation below 1e-18 relative.  x - 1 is exact.
+__device__ __forceinline__ double log_1to2(double x) {
+  const bool hi = x > SSVI_LOGC[11];
+  const double xr = hi ? 0.5 * x : x;
+  const double s = (xr - 1.0) * rcp_pos(xr + 1.0);
+  const double z = s * s;
+  const double a01 = fma(z, SSVI_LOGC[1], SSVI_LOGC[0]);
+  const double a23 = fma(z, SSVI_LOGC[3], SSVI_LOGC[2]);
+  const double a45 = fma(z, SSVI_LOGC[5], SSVI_LOGC[4]);
+  const double a67 = fma(z, SSVI_LOGC[7], SSVI_LOGC[6]);
+  const double a89 = fma(z, SSVI_LOGC[9], SSVI_LOGC[8]);
+  const double z2 = z * z;
+  const double b0 = fma(z2, a23, a01);
+  const double b1 = fma(z2, a67, a45);
+  const double z4 = z2 * z2;
+  const double c0 = fma(z4, b1, b0);
+  const double z8 = z4 * z4;
+  const double pz = fma(z8, a89, c0);
+  const double l = fma(s * z, pz, s + s);
+  return hi ? l + SSVI_LOGC[10] : l;
+}
+
+// pdf, d pdf / df, d2 pdf / df2 of the Poisson likelihood (poisson.py:19-57, Q7 included) for |f| < 700
+__device__ __forceinline__ void poisson_pdf_derivs_fast(double y, double f, double yfact, double& p, double& p1,
+                                                        double& p2) {
+  const double e = exp_nonpos_c(-fabs(f));
+  const double x = 1.0 + e;
+  const double r = rcp_1to2(x);
+  const double L = log_1to2(x);
+  const double er = e * r;
+  const bool pos = f >= 0.0;
+  const double rE1 = pos ? er : r;                    // 1 / (1 + e^f)
+  const double sg = pos ? r : er;                     // sigmoid(f)
+  const double A = fmax(pos ? f + L : L, 1e-8);       // poisson_link(f)
+  const double rA = rcp_pos(A);
+  // Q7: the second derivative evaluates pdf(y, poisson_link(m)) -- the link applied twice (poisson.py:42); A > 0
+  const double e2 = exp_nonpos_c(-A);
+  const double x2 = 1.0 + e2;
+  const double r2 = rcp_1to2(x2);
+  const double A2 = fmax(A + log_1to2(x2), 1e-8);
+  double pw = 1.0, pw2 = 1.0, b = A, b2 = A2;         // A^y and A2^y for the integral count y, one loop
+  for (int n = (int)y; n > 0; n >>= 1) {
+    if (n & 1) {
+      pw *= b;
+      pw2 *= b2;
+    }
+    b *= b;
+    b2 *= b2;
+  }
+  const double yA = y * rA, t = yA - 1.0;
+  p = fmax(pw * rE1 * yfact, 1e-8);
+  p1 = p * (sg * t);
+  const double pl = fmax(pw2 * (e2 * r2) * yfact, 1e-8);
+  const double temp = -(yA * rA) * (sg * sg) + t * (sg * (1.0 - sg));
+  p2 = p1 * (sg * t) + pl * temp;
+}
+
 // robust model: pdf and its first / second derivative w.r.t. f
 //   normal.py:16-27, bernoulli.py:16-36, poisson.py:19-57
 // (yfact: 1 / y! for the Poisson likelihood, unused otherwise)
@@ -168,6 +279,10 @@ __device__ __forceinline__ void pdf_derivs(int lik, double y, double f, double s
     p1 = (y * sg) * (1.0 - sg);
     p2 = sg * (1.0 - sg) * (1.0 - 2.0 * sg);
   } else {
+    if (fabs(f) < 700.0) {                            // everything a sane run produces; the rest keeps libm's edge cases
+      poisson_pdf_derivs_fast(y, f, yfact, p, p1, p2);
+      return;
+    }
     // Divisions are the expensive part here (about 25 instructions each in fp64): one reciprocal each of 1+e^f, A and
     // 1+e^A serves every quotient of poisson.py:19-57; yfact arrives as 1/y! (a few ulp from the reference's order).
     const double E = exp(f);

@@ -333,9 +333,7 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
       CUDA_TRY(h, cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc));                \
       kf<<<(unsigned)n_chunks, 128, smf, st>>>(v, mv, wk, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, \
                                                entry_ids, rows, h->z_own, z_f32);                                  \
-      memo_weights_kernel<ZT><<<(unsigned)((wk.n * 64 + 255) / 256), 256, 0, st>>>(v, wk, w_state,                 \
-                                                                                   (const ZT*)h->r_w,              \
-                                                                                   (const ZT*)h->z_f);             \
+      launch_memo_weights<ZT>(v, wk, w_state, (const ZT*)h->r_w, (const ZT*)h->z_f, st);                           \
       kc<<<(unsigned)n_chunks, 128, smc, st>>>(v, mv, wk, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, \
                                                chunk_out, entry_ids, partial_out);                                 \
     } while (0)
