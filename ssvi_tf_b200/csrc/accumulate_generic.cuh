@@ -17,6 +17,9 @@
 //   robust (SSVI_TF_robust.py:67-169):     pdf ratios, Q6
 // MODEL / LIK >= 0: the model and the likelihood as compile-time constants (memo_weights_kernel: the k2 loop is then one
 // straight likelihood body whose constants stay in registers); -1: read them from the view.
+#ifndef SSVI_W_UNROLL
+#define SSVI_W_UNROLL 1                                 // k2 draws of the robust model evaluated side by side (A/B knob)
+#endif
 template <typename ZT, int MODEL = -1, int LIK = -1>
 __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* __restrict__ r_w,
                                                    const ZT* __restrict__ z_f, int slot, int k, bool active,
@@ -81,7 +84,9 @@ __device__ __forceinline__ void likelihood_weights(const DevView& v, const ZT* _
       p1 /= sqrt_pi;
       p2 /= sqrt_pi;
     } else {
-      for (int i2 = 0; i2 < k2; ++i2) {                // (the pdf terms are too large a body to unroll profitably)
+      constexpr int WU = SSVI_W_UNROLL;
+#pragma unroll WU
+      for (int i2 = 0; i2 < k2; ++i2) {
         double fs = f + ws * ldz(zf, (int64_t)i2 * k1);
         double a, b, c;
         pdf_derivs(lik, y, fs, s, yfact, a, b, c);

@@ -171,8 +171,11 @@ __global__ void __launch_bounds__(128, 4) memo_f_kernel(DevView v, MemoView mv, 
 // ---------------------------------------------------------------------------------------------------------------------
 // pass 2: one thread per (entry, sample): the second-layer k2 loop
 // ---------------------------------------------------------------------------------------------------------------------
+#ifndef SSVI_W_MINB
+#define SSVI_W_MINB 3                                   // resident 256-thread blocks per SM asked of ptxas (A/B knob)
+#endif
 template <typename ZT, int MODEL, int LIK>
-__global__ void __launch_bounds__(256, 2) memo_weights_kernel(DevView v, MemoWork wk, const double* __restrict__ w_state,
+__global__ void __launch_bounds__(256, SSVI_W_MINB) memo_weights_kernel(DevView v, MemoWork wk, const double* __restrict__ w_state,
                                                               const ZT* __restrict__ r_w, const ZT* __restrict__ z_f) {
   const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= wk.n * 64) return;
