@@ -91,75 +91,6 @@ __device__ __forceinline__ double exp_nonpos(double x) {
   return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
 }
 
-// 1 / a for a in [1, 2]: hardware seed (MUFU.RCP64H, ~20 bits) + two Newton steps, no special cases to branch on
-__device__ __forceinline__ double rcp_1to2(double a) {
-  double y;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
-  double e = fma(-a, y, 1.0);
-  y = fma(y, e, y);
-  e = fma(-a, y, 1.0);
-  return fma(y, e, y);
-}
-
-// bernoulli.py:40-51: sigmoid(yf) and sigmoid(-yf) from ONE exponential: with e = exp(-|yf|) in (0, 1],
-// sigmoid(|yf|) = 1/(1+e) and sigmoid(-|yf|) = e/(1+e); equal to the reference's two evaluations to a few ulp, and
-// saturating to {1, 0} where 1/(1+exp(-x)) does.
-__device__ __forceinline__ void bernoulli_log_derivs(double y, double f, double& fst, double& snd) {
-  const double yf = y * f;
-  const double e = exp_nonpos(-fabs(yf));
-  const double hi = rcp_1to2(1.0 + e), lo = e * hi;
-  const bool pos = yf >= 0.0;
-  double sp = pos ? hi : lo, sm = pos ? lo : hi;
-  if (isnan(yf)) sp = sm = 0.0;                        // nan_to_num(sigmoid(nan)) = 0 (ProbFun.py:24)
-  fst = y * sm;
-  snd = -sp * sm;
-}
-
-// d / simple models: first and second derivative of log p(y|f) w.r.t. f
-//   normal.py:32-36, bernoulli.py:40-51, poisson.py:70-87
-__device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, double s, double& fst,
-                                               double& snd) {
-  if (lik == SSVI_LIK_NORMAL) {
-    double is2 = 1.0 / (s * s);
-    fst = is2 * (y - f);
-    snd = -is2;
-  } else if (lik == SSVI_LIK_BERNOULLI) {
-    bernoulli_log_derivs(y, f, fst, snd);
-  } else {
-    const PoissonTerms pt = poisson_terms(f);
-    const double sg = pt.sg, A = pt.A;
-    double t = y / A - 1.0;
-    fst = nan_to_num(sg * t);
-    snd = nan_to_num(sg * (1.0 - sg) * t - y * (sg * sg) / (A * A));
-  }
-}
-
-// Two evaluations at once (the memo / diag sweep kernels hold two samples per lane): the likelihood switch sits OUTSIDE
-// the pair, so the two chains are one basic block and ptxas interleaves them.
-__device__ __forceinline__ void log_pdf_derivs_pair(int lik, double y, double f0, double f1, double s, double& a0,
-                                                    double& b0, double& a1, double& b1) {
-  if (lik == SSVI_LIK_BERNOULLI) {
-    bernoulli_log_derivs(y, f0, a0, b0);
-    bernoulli_log_derivs(y, f1, a1, b1);
-  } else if (lik == SSVI_LIK_NORMAL) {
-    const double is2 = 1.0 / (s * s);
-    a0 = is2 * (y - f0);
-    a1 = is2 * (y - f1);
-    b0 = b1 = -is2;
-  } else {
-    log_pdf_derivs(lik, y, f0, s, a0, b0);
-    log_pdf_derivs(lik, y, f1, s, a1, b1);
-  }
-}
-
-// ---- Poisson pdf terms for the robust model's k1 x k2 loop (4096 evaluations per observed entry at config 3) ------------
-// That loop is ISSUE bound, not FP64-pipe bound, when written with libm: ptxas materialises every 64-bit literal of the
-// inlined exp / log with two UMOVs right before its use (100 of ~490 instructions per evaluation,
-// profiles/r01z_ncu_memo_weights.txt).  Here the coefficients sit in constant memory and are read as instruction operands,
-// the reciprocals are seed + Newton without the slow-path call of a general division, and everything is straight-line:
-//   e = exp(-|f|) in (0, 1],  x = 1 + e in (1, 2],  r = 1/x,  L = log(x)
-//   f >= 0:  1/(1+e^f) = e r,  sigmoid(f) = r,    log(1+e^f) = f + L          f < 0:  r,  e r,  L
-// (for f < 0 that is the reference's log(fl(1 + e^f)) operation for operation; for f >= 0 it agrees to a few ulp).
 __constant__ double SSVI_EXPC[14] = {1.0, 1.0, 0.5, 1.0 / 6.0, 1.0 / 24.0, 1.0 / 120.0, 1.0 / 720.0, 1.0 / 5040.0,
                                      1.0 / 40320.0, 1.0 / 362880.0, 1.0 / 3628800.0, 1.0 / 39916800.0,
                                      1.0 / 479001600.0, 1.0 / 6227020800.0};
@@ -169,7 +100,11 @@ __constant__ double SSVI_LOGC[16] = {2.0 / 3.0,  2.0 / 5.0,  2.0 / 7.0,  2.0 / 9
                                      1.41421356237309514547e+00, 1.4426950408889634, 6755399441055744.0,
                                      -6.93147180369123816490e-01, -1.90821492927058770002e-10};
 
-// exp(x) for x in [-708, 0]: exp_nonpos with the coefficients as constant-bank operands
+// exp_nonpos with its coefficients read from CONSTANT MEMORY, for the k2 loops of the simple / robust models: as literals
+// ptxas materialises each 64-bit coefficient with two UMOVs before every use, which made those loops issue bound
+// (profiles/r01z_ncu_memo_weights.txt).  The sweep kernels' per-entry epilogue keeps the literal version above: there
+// the issue slots are idle and the constant loads only add latency (C2: 4.33e8 with literals, 4.27e8 with loads).
+// Precondition: -708 <= x <= 0 (the callers bound |f| by 700).
 __device__ __forceinline__ double exp_nonpos_c(double x) {
   const double t = fma(x, SSVI_LOGC[12], SSVI_LOGC[13]);
   const int n = __double2loint(t);
@@ -193,6 +128,16 @@ __device__ __forceinline__ double exp_nonpos_c(double x) {
   const double s0 = fma(r4, q1, q0);
   const double p = fma(r8, q3, s0);
   return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+}
+
+// 1 / a for a in [1, 2]: hardware seed (MUFU.RCP64H, ~20 bits) + two Newton steps, no special cases to branch on
+__device__ __forceinline__ double rcp_1to2(double a) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  double e = fma(-a, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-a, y, 1.0);
+  return fma(y, e, y);
 }
 
 // 1 / a for a normal, positive a of moderate magnitude: hardware seed + two Newton steps (no special cases)
@@ -228,6 +173,87 @@ __device__ __forceinline__ double log_1to2(double x) {
   return hi ? l + SSVI_LOGC[10] : l;
 }
 
+// sigmoid(f), A = poisson_link(f) = max(log(1 + e^f), 1e-8) and 1/A for |f| < 700, from ONE exponential of a non-positive
+// argument: e = exp(-|f|), x = 1 + e in (1, 2]; f >= 0: sigmoid = 1/x, log(1+e^f) = f + log x; f < 0: e/x, log x
+// (ProbFun.py:22-28, 52-55; for f < 0 operation for operation the reference's log(fl(1 + e^f))).
+__device__ __forceinline__ void poisson_link_sigmoid_fast(double f, double& sg, double& A, double& rA) {
+  const double e = exp_nonpos_c(-fabs(f));
+  const double x = 1.0 + e;
+  const double r = rcp_1to2(x);
+  const double L = log_1to2(x);
+  const bool pos = f >= 0.0;
+  sg = pos ? r : e * r;
+  A = fmax(pos ? f + L : L, 1e-8);
+  rA = rcp_pos(A);
+}
+
+// bernoulli.py:40-51: sigmoid(yf) and sigmoid(-yf) from ONE exponential: with e = exp(-|yf|) in (0, 1],
+// sigmoid(|yf|) = 1/(1+e) and sigmoid(-|yf|) = e/(1+e); equal to the reference's two evaluations to a few ulp, and
+// saturating to {1, 0} where 1/(1+exp(-x)) does.
+__device__ __forceinline__ void bernoulli_log_derivs(double y, double f, double& fst, double& snd) {
+  const double yf = y * f;
+  const double e = exp_nonpos(-fabs(yf));
+  const double hi = rcp_1to2(1.0 + e), lo = e * hi;
+  const bool pos = yf >= 0.0;
+  double sp = pos ? hi : lo, sm = pos ? lo : hi;
+  if (isnan(yf)) sp = sm = 0.0;                        // nan_to_num(sigmoid(nan)) = 0 (ProbFun.py:24)
+  fst = y * sm;
+  snd = -sp * sm;
+}
+
+// d / simple models: first and second derivative of log p(y|f) w.r.t. f
+//   normal.py:32-36, bernoulli.py:40-51, poisson.py:70-87
+__device__ __forceinline__ void log_pdf_derivs(int lik, double y, double f, double s, double& fst,
+                                               double& snd) {
+  if (lik == SSVI_LIK_NORMAL) {
+    double is2 = 1.0 / (s * s);
+    fst = is2 * (y - f);
+    snd = -is2;
+  } else if (lik == SSVI_LIK_BERNOULLI) {
+    bernoulli_log_derivs(y, f, fst, snd);
+  } else {
+    if (fabs(f) < 700.0) {                            // the straight-line form of poisson_pdf_derivs_fast (below)
+      double sg, A, rA;
+      poisson_link_sigmoid_fast(f, sg, A, rA);
+      const double yA = y * rA, t = yA - 1.0;
+      fst = sg * t;
+      snd = sg * (1.0 - sg) * t - (yA * rA) * (sg * sg);
+      return;
+    }
+    const PoissonTerms pt = poisson_terms(f);
+    const double sg = pt.sg, A = pt.A;
+    double t = y / A - 1.0;
+    fst = nan_to_num(sg * t);
+    snd = nan_to_num(sg * (1.0 - sg) * t - y * (sg * sg) / (A * A));
+  }
+}
+
+// Two evaluations at once (the memo / diag sweep kernels hold two samples per lane): the likelihood switch sits OUTSIDE
+// the pair, so the two chains are one basic block and ptxas interleaves them.
+__device__ __forceinline__ void log_pdf_derivs_pair(int lik, double y, double f0, double f1, double s, double& a0,
+                                                    double& b0, double& a1, double& b1) {
+  if (lik == SSVI_LIK_BERNOULLI) {
+    bernoulli_log_derivs(y, f0, a0, b0);
+    bernoulli_log_derivs(y, f1, a1, b1);
+  } else if (lik == SSVI_LIK_NORMAL) {
+    const double is2 = 1.0 / (s * s);
+    a0 = is2 * (y - f0);
+    a1 = is2 * (y - f1);
+    b0 = b1 = -is2;
+  } else {
+    log_pdf_derivs(lik, y, f0, s, a0, b0);
+    log_pdf_derivs(lik, y, f1, s, a1, b1);
+  }
+}
+
+// ---- Poisson pdf terms for the robust model's k1 x k2 loop (4096 evaluations per observed entry at config 3) ------------
+// That loop is ISSUE bound, not FP64-pipe bound, when written with libm: ptxas materialises every 64-bit literal of the
+// inlined exp / log with two UMOVs right before its use (100 of ~490 instructions per evaluation,
+// profiles/r01z_ncu_memo_weights.txt).  Here the coefficients sit in constant memory and are read as instruction operands,
+// the reciprocals are seed + Newton without the slow-path call of a general division, and everything is straight-line:
+//   e = exp(-|f|) in (0, 1],  x = 1 + e in (1, 2],  r = 1/x,  L = log(x)
+//   f >= 0:  1/(1+e^f) = e r,  sigmoid(f) = r,    log(1+e^f) = f + L          f < 0:  r,  e r,  L
+// (for f < 0 that is the reference's log(fl(1 + e^f)) operation for operation; for f >= 0 it agrees to a few ulp).
 // pdf, d pdf / df, d2 pdf / df2 of the Poisson likelihood (poisson.py:19-57, Q7 included) for |f| < 700
 __device__ __forceinline__ void poisson_pdf_derivs_fast(double y, double f, double yfact, double& p, double& p1,
                                                         double& p2) {
