@@ -21,7 +21,8 @@ def run(iters, rpi, seed=319):
     covs = [np.eye(D) * 0.1] * 3
     with contextlib.redirect_stdout(io.StringIO()):
         t.synthesize_data(dims, means, covs, D, 0.8, 1, 0.1)
-        m = pkg.SSVI_TF_d(t, D, mean0=np.ones(D), cov0=np.eye(D) * 0.1, k1=64, k2=128, batch_size=128, randstart=True)
+        m = pkg.SSVI_TF_d(t, D, mean0=np.ones(D), cov0=np.eye(D) * 0.1, k1=64, k2=128, batch_size=128, randstart=True,
+                          chunk_entries=int(os.environ.get("SSVI_CHUNK", "16")))
         m.factorize(report=10 ** 9, max_iteration=20, detailed_report=False, rows_per_iteration=rpi)    # warm-up
         torch.cuda.synchronize()
         t0 = time.perf_counter()
