@@ -145,6 +145,16 @@ def case_list():
     # BASELINE.json config 1 at full per-row size: 50^3, D=10, k1=64, k2=128, B=128, SSVI_TF_d full
     cases.append(dict(name="config1_d_normal_full", model="d", lik="normal", diag=False, dims=[50, 50, 50],
                       nnz=12000, D=10, k1=64, k2=128, batch_size=128, seed=408, n_rows=1))
+    # the kernel instances of BASELINE.json configs 2-5 (rank, k1, k2, model, likelihood, covariance kind, order) on small
+    # index spaces, one subsampled row step each (B = 32 keeps the noise tape of a fixture near 1-2 MB)
+    cases.append(dict(name="config2_shape_d_bernoulli_full", model="d", lik="bernoulli", diag=False, dims=[12, 10, 8],
+                      nnz=600, D=20, k1=64, k2=64, batch_size=32, seed=420, n_rows=1))
+    cases.append(dict(name="config3_shape_robust_poisson_full", model="robust", lik="poisson", diag=False,
+                      dims=[12, 10, 8], nnz=600, D=30, k1=64, k2=64, batch_size=32, seed=421, cov_eta=0.001, n_rows=1))
+    cases.append(dict(name="config4_shape_simple_normal_diag_4way", model="simple", lik="normal", diag=True,
+                      dims=[6, 5, 4, 4], nnz=350, D=50, k1=64, k2=64, batch_size=32, seed=422, n_rows=1))
+    cases.append(dict(name="config5_shape_d_normal_full", model="d", lik="normal", diag=False, dims=[12, 10, 8],
+                      nnz=600, D=32, k1=64, k2=64, batch_size=32, seed=423, n_rows=1))
     return cases
 
 
