@@ -81,7 +81,7 @@ typedef struct SsviConfig {
   int32_t cov_update;       /* SSVI_UPDATE_*   "S" | "N"                         (:33)  */
   int32_t noise_dtype;      /* SSVI_NOISE_*    element type of the noise pool           */
   int32_t kernel_path;      /* 0 = auto; 1 = force the generic CUDA-core accumulate path (testing)  */
-  int32_t reserved1;
+  int32_t tuning;           /* bit set of SSVI_TUNE_* kernel options (0 = defaults); results do not depend on it */
   double eta;               /* (:85)  */
   double cov_eta;           /* (:86)  */
   double sigma_eta;         /* (:88)  */
@@ -108,9 +108,15 @@ int64_t ssvi_sampler_row_len(const SsviConfig* cfg);
 int64_t ssvi_noise_block_len(const SsviConfig* cfg);
 int64_t ssvi_noise_offset(const SsviConfig* cfg, int32_t c, int32_t k);
 
+/* Kernel options (cfg.tuning / ssvi_set_tuning): launch-order and prefetch choices that never change a result. */
+enum {
+  SSVI_TUNE_NO_L2_PREFETCH = 1   /* sweep kernels: do not prefetch the next entry's table records into L2 */
+};
+
 /* The library itself allocates only the device flag word of a handle. */
 int ssvi_create(const SsviConfig* cfg /*HOST*/, SsviHandle** out /*HOST*/);
 void ssvi_destroy(SsviHandle* h);
+int ssvi_set_tuning(SsviHandle* h, int32_t tuning);   /* replaces cfg.tuning for the calls that follow */
 const char* ssvi_last_error(const SsviHandle* h); /* HOST string; h may be NULL for create errors */
 
 /* Observed TRAIN entries in COO form: Tensor.train_entries / train_vals (Tensor/Tensor.py:66-67,
@@ -248,6 +254,15 @@ int ssvi_predict_mean(SsviHandle* h, const int32_t* entries, int64_t n, double* 
 int ssvi_draw_minibatches(SsviHandle* h, int64_t n_rows, const int64_t* rows, const int64_t* rowptr,
                           const int64_t* perm, int32_t batch_size, uint64_t seed, const int64_t* seg_start,
                           int64_t* out, void* stream);
+
+/* Variate generation on the device: the stand-in for the reference's draws from numpy's global RNG
+ * (np.random.multivariate_normal SSVI_TF_interface.py:252-254, :743-745; np.random.rayleigh :260 and
+ * SSVI_TF_robust.py:53; np.random.normal SSVI_TF_simple.py:35, SSVI_TF_robust.py:163).  Fills the four pool arrays
+ * (layouts and element type as in ssvi_bind_noise; r_w / z_f may be NULL for SSVI_MODEL_D) with standard normal
+ * variates (r_w: unit Rayleigh) from a counter-based generator keyed by (seed, draw): the same pair always gives the
+ * same pool, a new `draw` a fresh one.  The pool still has to be bound with ssvi_bind_noise. */
+int ssvi_fill_noise(SsviHandle* h, void* z_other, void* z_own, void* r_w, void* z_f, int32_t pool_slots,
+                    uint64_t seed, uint64_t draw, void* stream);
 
 /* Per-entry Monte-Carlo estimators of the report path, from the bound noise pool (entry e reads slot
  * (slot0 + e) mod P; mode 0 draws from z_own, mode d >= 1 from z_other[.][d-1]; k1 draws, k2 noise-layer draws):

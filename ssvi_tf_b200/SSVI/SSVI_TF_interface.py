@@ -19,6 +19,7 @@ from ..Probability import ProbFun as probs
 from ..Probability.bernoulli import BernoulliDistribution
 from ..Probability.normal import NormalDistribution
 from ..Probability.poisson import PoissonDistribution
+from .true_model import TrueModelMixin
 
 EST_EXPECTED_OBS, EST_LOG_PDF, EST_PDF, EST_ROBUST_VLB = 0, 1, 2, 3      # include/ssvi_b200.h: SSVI_EST_*
 
@@ -30,7 +31,25 @@ class _RowBlock(object):
         self.dim, self.rows, self.n_rows, self.n_obs = dim, rows, int(rows.numel()), None
 
 
-class SSVI_TF(object):
+class _DeviceMirror(np.ndarray):
+    """Host copy of a small device vector whose item assignment also writes the device tensor (the reference keeps
+    pSigma as a numpy array that callers may modify in place, SSVI_TF_interface.py:56)."""
+
+    def __new__(cls, dev):
+        obj = np.asarray(dev.cpu().numpy()).view(cls)
+        obj._dev = dev
+        return obj
+
+    def __array_finalize__(self, obj):
+        self._dev = None                   # copies, slices and results of arithmetic are plain host arrays
+
+    def __setitem__(self, key, value):
+        np.ndarray.__setitem__(self, key, value)
+        if self._dev is not None and self.shape == tuple(self._dev.shape):
+            self._dev.copy_(torch.as_tensor(np.asarray(self, dtype=np.float64)))
+
+
+class SSVI_TF(TrueModelMixin):
     _model = "d"          # "d" | "simple" | "robust"; set by the subclasses
 
     def __init__(self, tensor, rank, mean_update="S", cov_update="N", noise_update="N",
@@ -121,6 +140,8 @@ class SSVI_TF(object):
         self._noise_slots = int(noise_slots) if noise_slots else max(int(batch_size), 1)
         self._noise_gen_seed = int(noise_seed)
         self._noise_draws = 0
+        self._own_pool = None
+        self.keep_noise = False            # True: the bound pool is reused by every update (set by set_noise())
         self._minibatch_draws = 0
         self._np_rng = np.random.default_rng(noise_seed)
         self._sub_gen = torch.Generator(device=eng.device)
@@ -139,8 +160,8 @@ class SSVI_TF(object):
         return [a.t() for a in self.engine.ada_cov]
 
     @property
-    def pSigma(self):                  # (:56)
-        return self.engine.pSigma.cpu().numpy()
+    def pSigma(self):                  # (:56); item assignment (model.pSigma[d] = v) writes through to the device
+        return _DeviceMirror(self.engine.pSigma)
 
     @pSigma.setter
     def pSigma(self, v):
@@ -169,17 +190,26 @@ class SSVI_TF(object):
     # noise
     # ---------------------------------------------------------------------------------------------
     def set_noise(self, pool):
-        """Supply the Monte-Carlo variates explicitly (a NoisePool, e.g. NoisePool.from_tape)."""
+        """Supply the Monte-Carlo variates explicitly (a NoisePool, e.g. NoisePool.from_tape).  The pool then stays
+        bound -- every later update reads the same variates -- until fresh_noise() is called or keep_noise is
+        cleared (parity tests, replays of a noise tape)."""
         self.engine.set_noise(pool)
+        self.keep_noise = True
 
     def fresh_noise(self):
-        """Draw a new pool of standard variates on the device (the stand-in for the reference's global
-        numpy RNG): batch_size slots, so every entry of a row's minibatch has its own draws."""
+        """Draw a new pool of standard variates on the device (ssvi_fill_noise; the stand-in for the reference's
+        global numpy RNG, which draws afresh in every update_natural_param_batch call): noise_slots slots
+        (default batch_size, so every entry of a row's minibatch has its own draws).  Called by every update unless
+        keep_noise is set; one kernel launch, nothing crosses the bus."""
         self._noise_draws += 1
         e = self.engine
-        self.engine.set_noise(NoisePool.random(self._noise_slots, self.order, self.D, self.k1, self.k2,
-                                               self.noise_added, e.device, e.noise_dtype,
-                                               seed=self._noise_gen_seed + self._noise_draws, diag=self.diag))
+        if self._own_pool is None:
+            self._own_pool = NoisePool.empty(self._noise_slots, self.order, self.D, self.k1, self.k2,
+                                             self.noise_added, e.device, e.noise_dtype, diag=self.diag)
+        e.fill_noise(self._own_pool, self._noise_gen_seed, self._noise_draws)
+        if e.noise is not self._own_pool:
+            e.set_noise(self._own_pool)
+        self.keep_noise = False
 
     # ---------------------------------------------------------------------------------------------
     # the hot path
@@ -196,15 +226,19 @@ class SSVI_TF(object):
             self._n_obs_global[key] = (off.cpu().numpy(), tot)
         return self._n_obs_global[key]
 
-    def _run_plan(self, plan, n_obs_global=None):
+    def _run_plan(self, plan, n_obs_global=None, full_sweep=False):
         eng = self.engine
-        if eng.noise is None:
-            self.fresh_noise()
+        if eng.noise is None or not self.keep_noise:
+            self.fresh_noise()                                      # the reference draws afresh in every call
+        if getattr(self, "_hyper_fresh", None):
+            self._hyper_fresh[plan.dim] = False                     # check_stop_cond must re-reduce this mode
         acc = eng.accumulate(plan)
         if self.process_group is not None:
             from .. import dist as sdist
             sdist.allreduce_accumulators(acc, self.process_group)   # the exchange step: (di, Di, si, count)
-            own = sdist.owned_rows(plan.n_rows, self.process_group) if plan.n_rows == self.dims[plan.dim] else None
+            # row-block stage 4 only for sweep plans: their rows are arange(n), so block [lo, hi) of the plan IS rows
+            # lo..hi-1 of the state arrays that allgather_rows exchanges
+            own = sdist.owned_rows(plan.n_rows, self.process_group) if full_sweep else None
             if own is not None and self._model == "d" and self.shard_row_update:
                 # full sweep: stage 4 on this rank's block of rows, then the updated rows of every state array
                 lo, hi = own
@@ -226,16 +260,26 @@ class SSVI_TF(object):
         if noise is not None:
             self.set_noise(noise)
         rows = np.atleast_1d(np.asarray(rows, dtype=np.int64))
-        if self.process_group is None:
-            rp = self.engine.rowptr_h[dim]
-            for r in rows[rp[rows + 1] == rp[rows]]:
-                self.missing[(dim, int(r))] = True
         rp = self.engine.rowptr_h[dim]
-        lens = np.minimum(rp[rows + 1] - rp[rows], self.batch_size)
+        full = rp[rows + 1] - rp[rows]
+        B = int(self.batch_size)
+        if self.process_group is None:
+            total = full
+        else:
+            # sharded: this rank's share of every row's minibatch is proportional to its share of the row's entries
+            # (largest-remainder rounding in rank order), so the global minibatch holds min(len, batch_size) entries
+            # as the reference's does (:170-174)
+            from .. import dist as sdist
+            _, n_obs_t = self._shard_info(dim, rows, full)
+            total = n_obs_t.cpu().numpy() if torch.is_tensor(n_obs_t) else np.asarray(n_obs_t)
+            B = sdist.local_batch_sizes(full, self.batch_size, self.process_group)
+        for r in rows[total == 0]:
+            self.missing[(dim, int(r))] = True                      # :166-168 (no observation on any shard)
+        lens = np.minimum(full, B)
         off, _ = self._shard_info(dim, rows, lens)
-        _, n_obs = self._shard_info(dim, rows, rp[rows + 1] - rp[rows])
+        _, n_obs = self._shard_info(dim, rows, full)
         self._minibatch_draws += 1                      # the draw itself happens on the device (:170-174)
-        plan = self.engine.plan_minibatch(dim, rows, self.batch_size, rng=self._np_rng, sub_idx=sub_idx,
+        plan = self.engine.plan_minibatch(dim, rows, B, rng=self._np_rng, sub_idx=sub_idx,
                                           slot_offset=off,
                                           device_seed=self._noise_gen_seed * 0x9E3779B1 + self._minibatch_draws)
         self._run_plan(plan, n_obs)
@@ -274,7 +318,7 @@ class SSVI_TF(object):
             if self.engine.noise is None:
                 self.fresh_noise()
             plan, n_obs = self.engine.plan_subsampled_sweep(dim, batch_size, self._sub_gen), None
-        self._run_plan(plan, n_obs)
+        self._run_plan(plan, n_obs, full_sweep=True)
         return plan
 
     def update_hyper_parameter(self, dim):
@@ -286,7 +330,7 @@ class SSVI_TF(object):
         eng = self.engine
         for d in range(self.order):
             if not getattr(self, "_hyper_fresh", {}).get(d, False):
-                eng.hyper_reduce(d)
+                eng.hyper_reduce(d, update_psigma=False)
         mx = eng.hyper_out[:, 1:3].max(dim=0).values.cpu().numpy()
         self.d_mean, self.d_cov = float(mx[0]), float(mx[1])
         return self.d_mean, self.d_cov
@@ -315,7 +359,6 @@ class SSVI_TF(object):
         update_column_pointer = [0 for _ in range(self.order)]
         start = time.time()
         for iteration in range(self.max_iteration + 1):
-            self.fresh_noise()
             self._hyper_fresh = {}
             advance = []
             for dim in range(self.order):
@@ -342,6 +385,7 @@ class SSVI_TF(object):
                     self.report_metrics_mini(iteration, start, mean_change, cov_change, output_folder)
             if max(mean_change, cov_change) < self.epsilon:                          # :142
                 break
+        self._hyper_fresh = {}             # a later manual update + check_stop_cond() must reduce again
         self.engine.check_flags()
 
     # ---------------------------------------------------------------------------------------------

@@ -1,7 +1,7 @@
 """ctypes binding of libssvi_b200.so (include/ssvi_b200.h).
 
 There is NO CPU fallback: if the shared library is missing, importing the compute path raises.
-Build it with `python __graft_entry__.py` (or ssvi_tf_b200/build.py).
+Build it with `python __graft_entry__.py` (nvcc, sm_100a; the driver's build() entry point).
 """
 import ctypes
 import os
@@ -18,6 +18,8 @@ LIK_NORMAL, LIK_BERNOULLI, LIK_POISSON = 0, 1, 2
 UPDATE_S, UPDATE_N = 0, 1
 NOISE_F64, NOISE_F32 = 0, 1
 
+TUNE_NO_L2_PREFETCH = 1
+
 FLAG_NONFINITE_ACC, FLAG_NONFINITE_COV, FLAG_PHI_ZERO, FLAG_CHOL_FAIL, FLAG_EIG_NOCONV = 1, 2, 4, 8, 16
 
 
@@ -26,7 +28,7 @@ class SsviConfig(ctypes.Structure):
         ("order", ctypes.c_int32), ("rank", ctypes.c_int32), ("cov_kind", ctypes.c_int32),
         ("model", ctypes.c_int32), ("likelihood", ctypes.c_int32), ("k1", ctypes.c_int32),
         ("k2", ctypes.c_int32), ("mean_update", ctypes.c_int32), ("cov_update", ctypes.c_int32),
-        ("noise_dtype", ctypes.c_int32), ("kernel_path", ctypes.c_int32), ("reserved1", ctypes.c_int32),
+        ("noise_dtype", ctypes.c_int32), ("kernel_path", ctypes.c_int32), ("tuning", ctypes.c_int32),
         ("eta", ctypes.c_double), ("cov_eta", ctypes.c_double), ("sigma_eta", ctypes.c_double),
         ("poisson_eta", ctypes.c_double), ("min_eigenval", ctypes.c_double), ("cov_floor", ctypes.c_double),
         ("likelihood_param", ctypes.c_double), ("dims", ctypes.c_int64 * MAX_ORDER),
@@ -44,6 +46,7 @@ SIGNATURES = {
     "ssvi_noise_offset": (_I64, [ctypes.POINTER(SsviConfig), _I32, _I32]),
     "ssvi_create": (ctypes.c_int, [ctypes.POINTER(SsviConfig), ctypes.POINTER(_P)]),
     "ssvi_destroy": (None, [_P]),
+    "ssvi_set_tuning": (ctypes.c_int, [_P, _I32]),
     "ssvi_last_error": (ctypes.c_char_p, [_P]),
     "ssvi_bind_data": (ctypes.c_int, [_P, _P, _P, _I64]),
     "ssvi_bind_state": (ctypes.c_int, [_P] + [ctypes.POINTER(_P)] * 6),
@@ -63,6 +66,7 @@ SIGNATURES = {
     "ssvi_estimate_entries": (ctypes.c_int, [_P, _I32, _P, _P, _I64, _I32, _P, _P, _P]),
     "ssvi_predict_mean": (ctypes.c_int, [_P, _P, _I64, _P, _P]),
     "ssvi_draw_minibatches": (ctypes.c_int, [_P, _I64, _P, _P, _P, _I32, ctypes.c_uint64, _P, _P, _P]),
+    "ssvi_fill_noise": (ctypes.c_int, [_P, _P, _P, _P, _P, _I32, ctypes.c_uint64, ctypes.c_uint64, _P]),
     "ssvi_check_flags": (ctypes.c_int, [_P, ctypes.POINTER(_I32), _P]),
 }
 

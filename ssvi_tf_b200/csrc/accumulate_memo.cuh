@@ -130,6 +130,7 @@ __host__ __device__ inline int memo_warp_bytes(int NT) { return ((NT * (NT + 1) 
 __host__ __device__ inline int memo_cta_smem(int NT, int D) { return memo_region_bytes(NT, D) + 4 * memo_warp_bytes(NT); }
 
 __device__ __forceinline__ double2 ld_tab(const double2* p) { return __ldcg(p); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.
@@ -226,6 +227,9 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
 
   // ---- main loop -----------------------------------------------------------------------------------------------------
   const double inv_k1 = 1.0 / (double)(8 * KT);
+  // A table larger than L2 (config 5) makes the first touch of a record an HBM miss, and only one k-tile of a record is
+  // in flight per warp: the whole next record (NT * 4 KB, 32 lanes x 128-byte lines) is asked into L2 an entry ahead.
+  const bool l2_prefetch = !(v.tuning & SSVI_TUNE_NO_L2_PREFETCH);
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
     const int nb = min(32, my_cnt - b0);
@@ -261,6 +265,14 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
       for (int jj = 0; jj < NOTH; ++jj) {
         pc[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], el) * rec2 + lane;
         pn[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], eln) * rec2 + lane;
+      }
+      if (l2_prefetch && eln != el) {                   // next entry's records -> L2, one entry (8 k-tiles) ahead of use
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj) {
+          const char* r0 = reinterpret_cast<const char*>(pn[jj] - lane) + lane * 128;
+#pragma unroll
+          for (int i = 0; i < NT; ++i) prefetch_l2(r0 + i * 4096);
+        }
       }
       double acc[NP][2];
 #pragma unroll

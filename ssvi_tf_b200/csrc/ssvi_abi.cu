@@ -94,6 +94,12 @@ extern "C" void ssvi_destroy(SsviHandle* h) {
   delete h;
 }
 
+extern "C" int ssvi_set_tuning(SsviHandle* h, int32_t tuning) {
+  if (!h) return SSVI_E_INVALID;
+  h->cfg.tuning = tuning;
+  return SSVI_OK;
+}
+
 extern "C" int ssvi_bind_data(SsviHandle* h, const int32_t* coords, const double* vals, int64_t nnz) {
   if (!h) return SSVI_E_INVALID;
   if (nnz < 0 || (nnz > 0 && (!coords || !vals))) return fail(h, SSVI_E_INVALID, "bind_data: null pointer%s");
@@ -167,6 +173,7 @@ static DevView make_view(const SsviHandle* h, int dim) {
   v.cov_len = cov_len_of(c);
   v.acc_len = (int32_t)h->acc_len;
   v.pool_slots = h->pool_slots;
+  v.tuning = h->cfg.tuning;
   v.lik_param = c.likelihood_param;
   v.coords = h->coords;
   v.vals = h->vals;
@@ -720,7 +727,7 @@ extern "C" int ssvi_predict_mean(SsviHandle* h, const int32_t* entries, int64_t 
 // One warp per row.  A row holding more than B entries keeps a uniform random B-subset of its list, drawn without
 // replacement by Floyd's algorithm (for j = len-B .. len-1: t uniform in [0, j]; take t, or j if t was taken already):
 // B sequential steps, the membership test spread over the lanes.  Counter-based RNG (splitmix64 of seed, row, step).
-__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+__host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
   x += 0x9E3779B97F4A7C15ull;
   x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
   x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
@@ -768,6 +775,55 @@ extern "C" int ssvi_draw_minibatches(SsviHandle* h, int64_t n_rows, const int64_
   const size_t smem = (size_t)4 * batch_size * sizeof(int32_t);
   draw_minibatches_kernel<<<(unsigned)((n_rows + 3) / 4), 128, smem, (cudaStream_t)stream>>>(
       n_rows, rows, rowptr, perm, batch_size, seed, seg_start, out);
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+// ---- variate generation on the device ---------------------------------------------------------------------------------
+// Stand-in for the reference's draws from numpy's global RNG (np.random.multivariate_normal SSVI_TF_interface.py:252-254,
+// :743-745; np.random.rayleigh :260 / SSVI_TF_robust.py:53; np.random.normal SSVI_TF_simple.py:35 / SSVI_TF_robust.py:163):
+// fills a noise pool with STANDARD variates.  Counter-based (splitmix64 of key + element index, Box-Muller), so a
+// (seed, draw) pair always gives the same pool and nothing but the two counters crosses the bus.
+template <typename ZT>
+__global__ void fill_noise_kernel(ZT* __restrict__ z_other, int64_t n_other, ZT* __restrict__ z_own, int64_t n_own,
+                                  ZT* __restrict__ r_w, int64_t n_rw, ZT* __restrict__ z_f, int64_t n_zf, uint64_t key) {
+  const int64_t total = n_other + n_own + n_rw + n_zf;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint64_t a = splitmix64(key + 2ull * (uint64_t)i), b = splitmix64(key + 2ull * (uint64_t)i + 1ull);
+    const double u1 = ((double)(a >> 11) + 0.5) * (1.0 / 9007199254740992.0);      // (0, 1)
+    const double u2 = ((double)(b >> 11) + 0.5) * (1.0 / 9007199254740992.0);
+    const double r = sqrt(-2.0 * log(u1));
+    int64_t j = i;
+    if (j < n_other) { z_other[j] = (ZT)(r * cospi(2.0 * u2)); continue; }
+    j -= n_other;
+    if (j < n_own) { z_own[j] = (ZT)(r * cospi(2.0 * u2)); continue; }
+    j -= n_own;
+    if (j < n_rw) { r_w[j] = (ZT)r; continue; }                                    // unit Rayleigh
+    j -= n_rw;
+    z_f[j] = (ZT)(r * cospi(2.0 * u2));
+  }
+}
+
+extern "C" int ssvi_fill_noise(SsviHandle* h, void* z_other, void* z_own, void* r_w, void* z_f, int32_t pool_slots,
+                               uint64_t seed, uint64_t draw, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (!z_other || !z_own || pool_slots < 1) return fail(h, SSVI_E_INVALID, "fill_noise: null pointer or empty pool%s");
+  const SsviConfig& c = h->cfg;
+  const bool second = c.model != SSVI_MODEL_D;
+  if (second && (!r_w || !z_f)) return fail(h, SSVI_E_INVALID, "fill_noise: r_w and z_f required for simple/robust%s");
+  const int64_t blk = smp_zblk(c.rank, c.k1, c.cov_kind == SSVI_COV_DIAG);
+  const int64_t n_own = (int64_t)pool_slots * blk, n_other = n_own * (c.order - 1);
+  const int64_t n_rw = second ? (int64_t)pool_slots * c.k1 : 0, n_zf = second ? n_rw * c.k2 : 0;
+  const int64_t total = n_other + n_own + n_rw + n_zf;
+  const uint64_t key = splitmix64(seed ^ splitmix64(draw + 0x5851F42D4C957F2Dull));
+  const unsigned grid = (unsigned)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c.noise_dtype == SSVI_NOISE_F32)
+    fill_noise_kernel<float><<<grid, 256, 0, st>>>((float*)z_other, n_other, (float*)z_own, n_own, (float*)r_w, n_rw,
+                                                   (float*)z_f, n_zf, key);
+  else
+    fill_noise_kernel<double><<<grid, 256, 0, st>>>((double*)z_other, n_other, (double*)z_own, n_own, (double*)r_w, n_rw,
+                                                    (double*)z_f, n_zf, key);
   CUDA_TRY(h, cudaGetLastError());
   return SSVI_OK;
 }

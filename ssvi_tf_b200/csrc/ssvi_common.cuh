@@ -49,6 +49,7 @@ struct DevView {
   int32_t cov_len;       // D*D or D
   int32_t acc_len;
   int32_t pool_slots;
+  int32_t tuning;        // SSVI_TUNE_* bits
   double lik_param;
   const int32_t* coords;
   const double* vals;

@@ -84,6 +84,16 @@ class NoisePool(object):
         return cls(z_other, z_own, r_w, z_f)
 
     @classmethod
+    def empty(cls, slots, N, D, k1, k2, need_second_layer, device, dtype=torch.float32, diag=False):
+        """Uninitialised pool of the right shapes (Engine.fill_noise draws into it on the device)."""
+        blk = noise_block_len(D, k1, diag)
+        z_other = torch.empty((slots, N - 1, blk), device=device, dtype=dtype)
+        z_own = torch.empty((slots, blk), device=device, dtype=dtype)
+        r_w = torch.empty((slots, k1), device=device, dtype=dtype) if need_second_layer else None
+        z_f = torch.empty((slots, k2, k1), device=device, dtype=dtype) if need_second_layer else None
+        return cls(z_other, z_own, r_w, z_f)
+
+    @classmethod
     def from_tape(cls, tape, device, dtype=torch.float64, diag=False):
         """tape: numpy-natural layout (z_other (B,N-1,k1,D), z_own (B,k1,D), r_w (B,k1), z_f (B,k2,k1))."""
         k1, D = tape.z_own.shape[1], tape.z_own.shape[2]
@@ -150,7 +160,7 @@ class Engine(object):
 
     def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16,
                  kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64, sweep_streams=2,
-                 sweep_tile_blocks=0, sweep_tile_min_entries=24.0, record_budget_bytes=256 << 20):
+                 sweep_tile_blocks=0, sweep_tile_min_entries=24.0, record_budget_bytes=256 << 20, tuning=0):
         """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
         cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
         if not torch.cuda.is_available():
@@ -185,6 +195,7 @@ class Engine(object):
         c.mean_update, c.cov_update = UPDATE_IDS[cfg["mean_update"]], UPDATE_IDS[cfg["cov_update"]]
         c.noise_dtype = _lib.NOISE_F32 if noise_dtype == torch.float32 else _lib.NOISE_F64
         c.kernel_path = int(kernel_path)      # 0 auto, 1 force the generic CUDA-core accumulate path
+        c.tuning = int(tuning)                # SSVI_TUNE_* bits (include/ssvi_b200.h); never changes a result
         c.eta, c.cov_eta, c.sigma_eta = float(cfg["eta"]), float(cfg["cov_eta"]), float(cfg["sigma_eta"])
         c.poisson_eta = float(cfg.get("poisson_eta", 0.1))
         c.min_eigenval = float(cfg.get("min_eigenval", 0.01))
@@ -359,6 +370,18 @@ class Engine(object):
         self._call(self.lib.ssvi_bind_noise, _ptr(pool.z_other), _ptr(pool.z_own),
                    _ptr(pool.r_w if need2 else None), _ptr(pool.z_f if need2 else None), pool.slots)
 
+    def fill_noise(self, pool, seed, draw):
+        """Fresh standard variates into `pool` (ssvi_fill_noise: counter-based generator keyed by (seed, draw)); one
+        launch on the caller's stream.  The stand-in for the reference's numpy RNG draws."""
+        self._call(self.lib.ssvi_fill_noise, _ptr(pool.z_other), _ptr(pool.z_own), _ptr(pool.r_w), _ptr(pool.z_f),
+                   int(pool.slots), int(seed) & 0xFFFFFFFFFFFFFFFF, int(draw) & 0xFFFFFFFFFFFFFFFF, self._stream())
+        self.launches += 1
+
+    def set_tuning(self, tuning):
+        """SSVI_TUNE_* kernel options for the calls that follow (A/B timing inside one process)."""
+        self._c.tuning = int(tuning)
+        self._call(self.lib.ssvi_set_tuning, int(tuning))
+
     def set_quadrature(self, degree):
         """SSVI_TF_robust(quadrature=True), SSVI_TF_robust.py:22-25: Gauss-Hermite rule of `degree` nodes in place of
         the k2 second-layer draws (degree 0 / None: back to Monte Carlo)."""
@@ -430,12 +453,14 @@ class Engine(object):
         rows_h = np.asarray(rows, dtype=np.int64)
         rp = self.rowptr_h[dim]
         lens = rp[rows_h + 1] - rp[rows_h]
-        if not np.any(lens > batch_size):
+        scalar = np.ndim(batch_size) == 0          # an array gives every row its own size (a shard's share, dist.py)
+        bs = np.broadcast_to(np.asarray(batch_size, dtype=np.int64), lens.shape)
+        if not np.any(lens > bs):
             return self.plan_full(dim, rows_h, slot_offset)
-        seg_len = np.minimum(lens, batch_size)
+        seg_len = np.minimum(lens, bs)
         seg_start = np.zeros(len(rows_h), dtype=np.int64)
         np.cumsum(seg_len[:-1], out=seg_start[1:])
-        if device_seed is not None and sub_idx is None and batch_size <= 2048:
+        if device_seed is not None and sub_idx is None and scalar and batch_size <= 2048:
             tabs = self._chunk_tables(dim, rows_h, seg_start, seg_len, slot_offset, extra=(rows_h, lens, seg_start))
             if dim not in self._rowptr_d:
                 self._rowptr_d[dim] = torch.as_tensor(np.asarray(rp, dtype=np.int64)).to(self.device)
@@ -448,11 +473,11 @@ class Engine(object):
         ids = []
         for r, row in enumerate(rows_h):
             seg = self.perm_h[dim][rp[row]:rp[row + 1]]
-            if lens[r] > batch_size:
+            if lens[r] > bs[r]:
                 if sub_idx is not None and int(row) in sub_idx:
                     pick = np.asarray(sub_idx[int(row)], dtype=np.int64)
                 else:
-                    pick = (rng or np.random).choice(int(lens[r]), batch_size, replace=False)
+                    pick = (rng or np.random).choice(int(lens[r]), int(bs[r]), replace=False)
                 seg = seg[pick]
             ids.append(seg)
         entry_ids = np.concatenate(ids) if ids else np.zeros(0, np.int64)
@@ -799,11 +824,13 @@ class Engine(object):
         acc = self.accumulate(plan)
         self.row_update(plan, acc, fixed_covariance)
 
-    def hyper_reduce(self, dim):
+    def hyper_reduce(self, dim, update_psigma=True):
         """update_hyper_parameter(dim) (:146-160): refreshes pSigma[dim]; also leaves the mode's maximum
-        mean / covariance change in hyper_out[dim, 1:3] for check_stop_cond (:967-984)."""
+        mean / covariance change in hyper_out[dim, 1:3] for check_stop_cond (:967-984), which calls this with
+        update_psigma=False (the reference's check_stop_cond does not touch pSigma)."""
         self._call(self.lib.ssvi_hyper_reduce, dim, _ptr(self.hyper_out[dim]), self._stream())
-        self.pSigma[dim:dim + 1].copy_(self.hyper_out[dim, 0:1])
+        if update_psigma:
+            self.pSigma[dim:dim + 1].copy_(self.hyper_out[dim, 0:1])
         self.launches += 1
 
     def estimate_entries(self, what, entries, ys=None, slot0=0):

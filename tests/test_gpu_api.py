@@ -99,3 +99,32 @@ def test_reset_and_errors():
     np.testing.assert_array_equal(m.posterior.get_vector_distribution(0, 0)[0], np.ones(3))
     rs, err = m.evaluate_train_error()
     assert 0.0 <= err <= 1.0
+
+
+def test_true_param_reports_and_state_mirrors(capsys):
+    """The drivers' post-factorize report (synthetic_test.py:152 -> evaluate_true_params, :1213-1320), the pSigma
+    write-through mirror and a stale-free check_stop_cond after a manual update."""
+    import ssvi_tf_b200 as pkg
+    np.random.seed(7)
+    D = 4
+    t = pkg.RV_tensor()
+    t.synthesize_data([9, 8, 7], [np.ones(D) * m for m in (0.5, 1.0, 0.2)], [np.eye(D) * 0.1] * 3, D=D,
+                      train=0.8, sparsity=0.7, noise=0.05)
+    m = pkg.SSVI_TF_d(t, D, mean0=np.ones(D), cov0=np.eye(D) * 0.1, k1=16, k2=16, batch_size=32)
+    m.factorize(report=10 ** 9, max_iteration=6, detailed_report=False, rows_per_iteration="all")
+    out = m.evaluate_true_params()
+    assert "Evaluation for true params" in capsys.readouterr().out
+    test_rsme, train_rsme = out[0], out[1]
+    assert np.isfinite(out).all() and test_rsme < 0.5 and train_rsme < 0.5      # the generating factors fit their own data
+    f = t.matrices[0][1] * t.matrices[1][2] * t.matrices[2][3]
+    assert m.true_model_predict([1, 2, 3], t.matrices) == pytest.approx(float(f.sum()))
+    mean, var = m.compute_posterior_param([1, 2, 3])
+    assert mean == pytest.approx(float(m.predict_entry([1, 2, 3]))) and var > 0
+    # pSigma: item assignment writes through to the device; the returned array itself is a host copy
+    m.pSigma[1] = 2.5
+    assert float(m.engine.pSigma[1]) == 2.5 and float(m.pSigma[1]) == 2.5
+    # a manual update after factorize must not leave check_stop_cond with the loop's stale reductions
+    m.check_stop_cond()
+    m.update_natural_param_batch(0, 0)
+    m.engine.norm_changes[0][0, 0] = 123.0
+    assert m.check_stop_cond()[0] == 123.0
