@@ -110,7 +110,11 @@ int64_t ssvi_noise_offset(const SsviConfig* cfg, int32_t c, int32_t k);
 
 /* Kernel options (cfg.tuning / ssvi_set_tuning): launch-order and prefetch choices that never change a result. */
 enum {
-  SSVI_TUNE_NO_L2_PREFETCH = 1   /* sweep kernels: do not prefetch the next entry's table records into L2 */
+  SSVI_TUNE_L2_PREFETCH = 1,     /* sweep kernels: ask the next entry's table records into L2 an entry ahead */
+  SSVI_TUNE_LIN = 2,             /* SSVI_TF_d + normal likelihood sweeps: the linear-weight kernel (contraction accumulated
+                                    across the chunk) instead of the general one */
+  SSVI_TUNE_PF2 = 4,             /* rank 25..32, order 3 sweeps: two k-tiles of table records in flight, 2 CTAs per SM */
+  SSVI_TUNE_PF3 = 8              /* ... three k-tiles in flight */
 };
 
 /* The library itself allocates only the device flag word of a handle. */
@@ -280,6 +284,40 @@ int ssvi_fill_noise(SsviHandle* h, void* z_other, void* z_own, void* r_w, void* 
 #define SSVI_EST_ROBUST_VLB 3
 int ssvi_estimate_entries(SsviHandle* h, int32_t what, const int32_t* entries, const double* ys, int64_t n,
                           int32_t slot0, const double* w_state, double* out, void* stream);
+
+/* A block of iterations of factorize()'s loop (SSVI_TF_interface.py:117-143) in the reference's schedule: per
+ * iteration, for every mode, update_natural_param_batch(dim, col[dim]) (:124) + update_hyper_parameter(dim) (:125), then
+ * the pointer / time_step advance (:128-133) and check_stop_cond (:135-142).  Everything is enqueued on `stream` from C:
+ * the row's minibatch is planned on the device (the draw of ssvi_draw_minibatches keyed by minibatch_seed +
+ * minibatch_draws, chunk tables), fresh variates are drawn into the pool (ssvi_fill_noise keyed by noise_seed,
+ * noise_draws) and the same kernels as ssvi_accumulate / ssvi_reduce_chunks / ssvi_row_update / ssvi_sigma_update /
+ * ssvi_hyper_reduce run.  When the stop condition fires at iteration i the device word stop[0] is latched to 1
+ * (stop[1] = i) and the state-writing kernels of the iterations enqueued behind it do nothing: the final state is the
+ * one the reference's `break` leaves.  The call never synchronises; the caller reads `stop` when it wants to.
+ * HOST struct; the counters, col and time_step are advanced in place (for every enqueued iteration: after a stop the
+ * caller recomputes them from stop[1]).  Single GPU (no process group). */
+typedef struct SsviLoop {
+  const int64_t* rowptr[SSVI_MAX_ORDER];        /* DEVICE int64 [n_d + 1] per mode: the inverted index (Tensor.py:251-258) */
+  const int64_t* perm[SSVI_MAX_ORDER];          /* DEVICE int64 [nnz] per mode */
+  const int64_t* rowptr_host[SSVI_MAX_ORDER];   /* HOST copies of rowptr */
+  void* z_other; void* z_own; void* r_w; void* z_f;   /* DEVICE noise pool (layouts of ssvi_bind_noise); bound by the call */
+  double* pSigma;                               /* DEVICE [N]    (:56, :146-160) */
+  double* w_state;                              /* DEVICE [3]    simple / robust */
+  double* hyper_out;                            /* DEVICE [N][3] ssvi_hyper_reduce outputs of every mode */
+  int32_t* stop;                                /* DEVICE int32[2], zeroed by the caller before the first block */
+  void* workspace;                              /* DEVICE, >= ssvi_loop_workspace_bytes(h, batch_size) */
+  int64_t workspace_bytes;
+  double epsilon;                               /* stop when max(d_mean, d_cov) < epsilon (:142; the reference uses 1e-4) */
+  uint64_t noise_seed, noise_draws;             /* in/out */
+  uint64_t minibatch_seed, minibatch_draws;     /* in/out */
+  int64_t col[SSVI_MAX_ORDER];                  /* in/out: update_column_pointer (:115) */
+  int64_t launches;                             /* out: kernels enqueued (added to) */
+  int32_t time_step[SSVI_MAX_ORDER];            /* in/out (:79, :130) */
+  int32_t pool_slots, batch_size, chunk_entries, fixed_covariance;
+} SsviLoop;
+int64_t ssvi_loop_workspace_bytes(const SsviHandle* h, int32_t batch_size);
+int ssvi_factorize_iterations(SsviHandle* h, SsviLoop* loop /*HOST*/, int64_t first_iteration, int64_t n_iterations,
+                              void* stream);
 
 /* Reads and clears the device flag word (synchronises `stream`).  flags_out HOST. */
 int ssvi_check_flags(SsviHandle* h, int32_t* flags_out /*HOST*/, void* stream);

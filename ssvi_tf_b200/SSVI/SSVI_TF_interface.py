@@ -119,6 +119,7 @@ class SSVI_TF(TrueModelMixin):
         self.rows_per_iteration = 1
         self.process_group = process_group
         self.shard_row_update = True       # multi-GPU full sweeps of SSVI_TF_d: stage 4 on row blocks + all-gather
+        self.device_loop = True            # factorize(): enqueue the reference's schedule from C (ssvi_factorize_iterations)
 
         cfg = dict(model=self._model, likelihood=self.likelihood_type, D=rank, diag=diag, k1=k1, k2=k2,
                    batch_size=batch_size, mean_update=mean_update, cov_update=cov_update, eta=eta,
@@ -358,6 +359,9 @@ class SSVI_TF(TrueModelMixin):
 
         update_column_pointer = [0 for _ in range(self.order)]
         start = time.time()
+        if (rpi == 1 and self.process_group is None and not self.keep_noise and int(self.batch_size) <= 2048
+                and self.device_loop):
+            return self._factorize_device_loop(start)
         for iteration in range(self.max_iteration + 1):
             self._hyper_fresh = {}
             advance = []
@@ -387,6 +391,55 @@ class SSVI_TF(TrueModelMixin):
                 break
         self._hyper_fresh = {}             # a later manual update + check_stop_cond() must reduce again
         self.engine.check_flags()
+
+    def _factorize_device_loop(self, start):
+        """The reference's schedule (one row per mode per iteration) with the loop body enqueued from C
+        (ssvi_factorize_iterations): no per-row host work, no per-iteration read of the stop condition.  Blocks end at
+        the iterations where a report is due; the device latches the stop condition and freezes the state at the
+        iteration the reference would `break` at (:142), so the result equals the per-call loop's."""
+        eng = self.engine
+        total = self.max_iteration + 1
+        if self._own_pool is None:
+            self.fresh_noise()
+            self._noise_draws -= 1                       # the pool only had to exist; the loop draws from here on
+        lp = eng.loop_begin(self._own_pool, self.batch_size, self.fixed_covariance, self.epsilon, self._noise_gen_seed,
+                            self._noise_draws, self._noise_gen_seed * 0x9E3779B1, self._minibatch_draws,
+                            [0] * self.order)
+        ts0 = list(eng.time_step)
+        due = lambda i: (i != 0 and i % self.report == 0) or i in self.to_report          # noqa: E731
+        it, done = 0, total
+        while it < total:
+            end = it
+            while end < total - 1 and not due(end) and end - it < 255:
+                end += 1
+            eng.factorize_iterations(lp, it, end - it + 1)
+            fired, at = eng.loop_stop_state()
+            last = at if fired else end
+            if due(last):
+                mean_change, cov_change = self._loop_changes()
+                eng.check_flags()
+                if self.detailed_report:
+                    self.report_metrics(last, start, mean_change, cov_change)
+                else:
+                    self.report_metrics_mini(last, start, mean_change, cov_change, self.output_folder)
+            if fired:
+                done = at + 1
+                break
+            it = end + 1
+        # pointers / time steps after `done` iterations (:128-133); the counters keep what the loop consumed
+        eng.time_step = [ts0[d] + done // self.dims[d] for d in range(self.order)]
+        self._noise_draws, self._minibatch_draws = int(lp.noise_draws), int(lp.minibatch_draws)
+        for d in range(self.order):                      # :166-168: visited rows without observations
+            rp = eng.rowptr_h[d]
+            for r in np.nonzero(rp[1:min(done, self.dims[d]) + 1] == rp[:min(done, self.dims[d])])[0]:
+                self.missing[(d, int(r))] = True
+        self.d_mean, self.d_cov = self._loop_changes()
+        self._hyper_fresh = {}
+        eng.check_flags()
+
+    def _loop_changes(self):
+        mx = self.engine.hyper_out[:, 1:3].max(dim=0).values.cpu().numpy()
+        return float(mx[0]), float(mx[1])
 
     # ---------------------------------------------------------------------------------------------
     # prediction / evaluation (:987-1059)

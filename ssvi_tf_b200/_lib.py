@@ -18,7 +18,7 @@ LIK_NORMAL, LIK_BERNOULLI, LIK_POISSON = 0, 1, 2
 UPDATE_S, UPDATE_N = 0, 1
 NOISE_F64, NOISE_F32 = 0, 1
 
-TUNE_NO_L2_PREFETCH = 1
+TUNE_L2_PREFETCH, TUNE_LIN, TUNE_PF2, TUNE_PF3 = 1, 2, 4, 8
 
 FLAG_NONFINITE_ACC, FLAG_NONFINITE_COV, FLAG_PHI_ZERO, FLAG_CHOL_FAIL, FLAG_EIG_NOCONV = 1, 2, 4, 8, 16
 
@@ -32,6 +32,24 @@ class SsviConfig(ctypes.Structure):
         ("eta", ctypes.c_double), ("cov_eta", ctypes.c_double), ("sigma_eta", ctypes.c_double),
         ("poisson_eta", ctypes.c_double), ("min_eigenval", ctypes.c_double), ("cov_floor", ctypes.c_double),
         ("likelihood_param", ctypes.c_double), ("dims", ctypes.c_int64 * MAX_ORDER),
+    ]
+
+
+class SsviLoop(ctypes.Structure):
+    """include/ssvi_b200.h: SsviLoop (argument block of ssvi_factorize_iterations)."""
+    _fields_ = [
+        ("rowptr", ctypes.c_void_p * MAX_ORDER), ("perm", ctypes.c_void_p * MAX_ORDER),
+        ("rowptr_host", ctypes.c_void_p * MAX_ORDER),
+        ("z_other", ctypes.c_void_p), ("z_own", ctypes.c_void_p), ("r_w", ctypes.c_void_p), ("z_f", ctypes.c_void_p),
+        ("pSigma", ctypes.c_void_p), ("w_state", ctypes.c_void_p), ("hyper_out", ctypes.c_void_p),
+        ("stop", ctypes.c_void_p), ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_int64),
+        ("epsilon", ctypes.c_double),
+        ("noise_seed", ctypes.c_uint64), ("noise_draws", ctypes.c_uint64),
+        ("minibatch_seed", ctypes.c_uint64), ("minibatch_draws", ctypes.c_uint64),
+        ("col", ctypes.c_int64 * MAX_ORDER), ("launches", ctypes.c_int64),
+        ("time_step", ctypes.c_int32 * MAX_ORDER),
+        ("pool_slots", ctypes.c_int32), ("batch_size", ctypes.c_int32), ("chunk_entries", ctypes.c_int32),
+        ("fixed_covariance", ctypes.c_int32),
     ]
 
 
@@ -67,6 +85,8 @@ SIGNATURES = {
     "ssvi_predict_mean": (ctypes.c_int, [_P, _P, _I64, _P, _P]),
     "ssvi_draw_minibatches": (ctypes.c_int, [_P, _I64, _P, _P, _P, _I32, ctypes.c_uint64, _P, _P, _P]),
     "ssvi_fill_noise": (ctypes.c_int, [_P, _P, _P, _P, _P, _I32, ctypes.c_uint64, ctypes.c_uint64, _P]),
+    "ssvi_loop_workspace_bytes": (_I64, [_P, _I32]),
+    "ssvi_factorize_iterations": (ctypes.c_int, [_P, ctypes.POINTER(SsviLoop), _I64, _I64, _P]),
     "ssvi_check_flags": (ctypes.c_int, [_P, ctypes.POINTER(_I32), _P]),
 }
 

@@ -136,9 +136,19 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 // One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.
 //   ONES: D % 8 != 0, the table carries a row of ones at n == D and di comes out of the contraction (row D of V V^T);
 //         otherwise the row sums are accumulated with DADDs.
+//   LIN:  normal likelihood (configs 1 and 5).  The k1-averaged derivatives of SSVI_TF_d.py:31-57 are then
+//           mean_k dlogp = (y - mean_k f_k) / s^2      mean_k d2logp = -1 / s^2   (normal.py:20-24)
+//         i.e. the Di weight is the same for every entry and the di weight needs only SUM_k f_k.  The contraction
+//         therefore accumulates straight across the chunk in the DMMA accumulators (no per-entry scaling, no
+//         shared-memory read-modify-write of G), SUM_k f_k is one register per lane + one warp sum (no per-sample f, no
+//         shared-memory transpose), and di accumulates in registers from the row sums.
 // ---------------------------------------------------------------------------------------------------------------------
-template <int NT, int NOTH, bool ONES>
-__global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulate_memo_kernel(
+//   PF / MINB: k-tiles of table records in flight ahead of the one in use, and the resident CTAs per SM asked of ptxas.
+//         What paces this kernel when the table does not sit in L2 (config 5) is the bytes a warp keeps in flight
+//         (one 4 KB k-tile at PF = 1, 12 warps per SM): deeper prefetch costs 32 registers per k-tile at NT = 4, paid
+//         for with fewer resident CTAs.
+template <int NT, int NOTH, bool ONES, bool LIN, int PF = SSVI_MEMO_PF, int MINB = (NT <= 3 ? SSVI_MEMO_MINB : 3)>
+__global__ void __launch_bounds__(128, MINB) accumulate_memo_kernel(
     DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
     const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
     const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
@@ -181,7 +191,6 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
     for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
   }
 
-  constexpr int PF = SSVI_MEMO_PF;
   double2 cur[NOTH][NT];                                // first k-tile of the first entry: in flight during the prologue
   double2 pf[PF - 1 > 0 ? PF - 1 : 1][NOTH][NT];        // k-tiles 1 .. PF-1 (deeper prefetch only)
 #pragma unroll
@@ -229,7 +238,14 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
   const double inv_k1 = 1.0 / (double)(8 * KT);
   // A table larger than L2 (config 5) makes the first touch of a record an HBM miss, and only one k-tile of a record is
   // in flight per warp: the whole next record (NT * 4 KB, 32 lanes x 128-byte lines) is asked into L2 an entry ahead.
-  const bool l2_prefetch = !(v.tuning & SSVI_TUNE_NO_L2_PREFETCH);
+  const bool l2_prefetch = (v.tuning & SSVI_TUNE_L2_PREFETCH) != 0;
+  double acc[NP][2];                                    // LIN: lives across the whole chunk
+  double dacc[NT];                                      // LIN: di partials of this lane's (row, samples)
+#pragma unroll
+  for (int p = 0; p < NP; ++p) acc[p][0] = acc[p][1] = 0.0;
+#pragma unroll
+  for (int i = 0; i < NT; ++i) dacc[i] = 0.0;
+  const double is2 = 1.0 / (v.lik_param * v.lik_param);
 
   for (int b0 = 0; b0 < my_cnt; b0 += 32) {
     const int nb = min(32, my_cnt - b0);
@@ -274,12 +290,14 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
           for (int i = 0; i < NT; ++i) prefetch_l2(r0 + i * 4096);
         }
       }
-      double acc[NP][2];
+      if (!LIN) {
 #pragma unroll
-      for (int p = 0; p < NP; ++p) acc[p][0] = acc[p][1] = 0.0;
+        for (int p = 0; p < NP; ++p) acc[p][0] = acc[p][1] = 0.0;
+      }
       double rs[NT];
 #pragma unroll
       for (int i = 0; i < NT; ++i) rs[i] = 0.0;
+      double fsum = 0.0;                                // LIN: this lane's share of SUM_k f_k
 #pragma unroll
       for (int t = 0; t < KT; ++t) {
         double2 nxt[NOTH][NT];                          // PF k-tiles ahead (the next entry's first tiles at t >= KT-PF)
@@ -299,16 +317,19 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
             vv[i].y *= cur[jj][i].y;
           }
           const double2 u = Us[(i * KT + t) * 32 + lane];
-          if (i == 0) {
+          if (LIN) {
+            fsum = fma(u.x, vv[i].x, fsum);
+            fsum = fma(u.y, vv[i].y, fsum);
+          } else if (i == 0) {
             fpt.x = u.x * vv[i].x;
             fpt.y = u.y * vv[i].y;
           } else {
             fpt.x += u.x * vv[i].x;
             fpt.y += u.y * vv[i].y;
           }
-          if (!ONES) rs[i] += vv[i].x + vv[i].y;
+          if (!ONES || LIN) rs[i] += vv[i].x + vv[i].y;
         }
-        FP[t * 32 + (lane ^ (t << 2))] = fpt;           // row-group index XOR-swizzled: the read below is conflict-free
+        if (!LIN) FP[t * 32 + (lane ^ (t << 2))] = fpt; // row-group index XOR-swizzled: the read below is conflict-free
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
           int p = 0;
@@ -337,6 +358,12 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
               pf[PF - 2 >= 0 ? PF - 2 : 0][jj][i] = nxt[jj][i];
             }
           }
+      }
+      if (LIN) {                                        // di weight from SUM_k f_k alone; Di weight is a chunk constant
+        const double aw = is2 * (y - warp_sum(fsum) * inv_k1) * inv_k1;
+#pragma unroll
+        for (int i = 0; i < NT; ++i) dacc[i] = fma(aw, rs[i], dacc[i]);
+        continue;
       }
       // ---- f_k = u_k . v_k: sum over the 8 row groups through shared memory; lane (g, q) ends with the samples
       //      k = 8g + 2q + {0,1}, i.e. it reads the partials of k-tile t = g held by the lanes (g', q), g' = 0..7 -----------
@@ -390,8 +417,15 @@ __global__ void __launch_bounds__(128, (NT <= 3 ? SSVI_MEMO_MINB : 3)) accumulat
   }
 
   // ---- CTA reduction (fixed warp order => deterministic) and the chunk record [di | Di | si_sum | count] ------------
+  if (LIN) {                                            // mean_k d2logp = -1/s^2 for every entry: one scaling per chunk
+    const double dw = -0.5 * is2 * inv_k1;
+#pragma unroll
+    for (int p = 0; p < NP; ++p) Gs[p * 32 + lane] = make_double2(dw * acc[p][0], dw * acc[p][1]);
+#pragma unroll
+    for (int i = 0; i < NT; ++i) Ga[i * 32 + lane] = make_double2(dacc[i], 0.0);
+  }
   __syncthreads();                                      // every warp is done reading U
-  if (ONES) {                                           // lanes of row group g == D % 8 hold di[8 i2 + 2q + {0,1}]
+  if (ONES && !LIN) {                                           // lanes of row group g == D % 8 hold di[8 i2 + 2q + {0,1}]
     if (g == (D & 7)) {
 #pragma unroll
       for (int i = 0; i < NT; ++i)

@@ -32,6 +32,7 @@ struct RowUpdateArgs {
   const double* w_state;
   double* si_out;
   int32_t* flags;
+  const int32_t* stop;   // device word of ssvi_factorize_iterations: non-zero = the stop condition has fired, leave the state alone
 };
 
 // block-wide sum; `red` holds >= 32 doubles of shared memory. All threads must call.
@@ -46,88 +47,102 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
   return t;
 }
 
-// Cyclic two-sided Jacobi with the round-robin (tournament) parallel ordering.
-// On exit A is (numerically) diagonal with the eigenvalues on its diagonal and the columns of Vm are
-// the eigenvectors.  A, Vm: D*D doubles of shared memory; scratch: 4*(D/2+1) + 32 doubles.
-__device__ void jacobi_eigh(double* A, double* Vm, int D, double* scratch, int32_t* flags) {
+// Cyclic two-sided Jacobi with the round-robin (tournament) parallel ordering: A <- J^T A J, V <- V J, where J is the
+// product of the n/2 disjoint plane rotations of the round.
+//   buf   four work matrices of D * LD doubles, LD = D | 1 (an odd stride keeps the column walks of a rotation off a
+//         single shared-memory bank: stride D = 32 was a 16-way conflict, 38.7 ms per sweep of 10k rank-32 rows).
+//         buf[3] holds the input on entry: D x D row-major with stride D, symmetric; it is copied out first.
+//   lam   out  D eigenvalues
+//   returns the eigenvector matrix (columns; row-major with stride LD; lam[k] belongs to column k), one of buf[2], buf[3]
+//   scratch  3 * (D + 1) + 32 doubles
+// One round = every thread forms its elements of J^T A J from four entries of the current A and writes them to the
+// OTHER buffer (ping-pong), so a round costs two barriers (rotations known; new matrix written) instead of three passes.
+__host__ __device__ inline int jacobi_ld(int D) { return D | 1; }
+
+__device__ const double* jacobi_eigh(double* const buf[4], double* lam, int D, double* scratch, int32_t* flags) {
   const int tid = threadIdx.x, nt = blockDim.x;
+  const int LD = jacobi_ld(D);
   const int n = (D + 1) & ~1;                 // players (even); index D is a bye when D is odd
   const int np = n / 2;
-  double* cs_c = scratch;
-  double* cs_s = scratch + np;
-  int* pp = (int*)(scratch + 2 * np);
-  int* qq = pp + np;
-  double* red = scratch + 4 * (np + 1);
-  for (int i = tid; i < D * D; i += nt) Vm[i] = (i / D == i % D) ? 1.0 : 0.0;
-  __syncthreads();
+  double* rc = scratch;                       // [D] cosine of the rotation that touches index j
+  double* rs = rc + (D + 1);                  // [D] signed sine: new_j = rc[j] x_j + rs[j] x_partner
+  int* part = (int*)(rs + (D + 1));           // [D] partner index (itself: no rotation)
+  double* red = scratch + 3 * (D + 1);
+  double* Ac = buf[0];
+  double* An = buf[1];
+  double* Vc = buf[2];
+  double* Vn = buf[3];
+  double tot = 0.0;
+  for (int idx = tid; idx < D * D; idx += nt) {
+    const int i = idx / D, j = idx % D;
+    const double a = buf[3][idx];
+    Ac[i * LD + j] = a;
+    Vc[i * LD + j] = (i == j) ? 1.0 : 0.0;
+    tot += a * a;
+  }
+  tot = block_sum(tot, red);                  // Frobenius norm: invariant under the rotations; buf[3] is free from here
   const int max_sweeps = 40;
   int sweep = 0;
-  for (; sweep < max_sweeps; ++sweep) {
-    double off = 0.0, tot = 0.0;
-    for (int i = tid; i < D * D; i += nt) {
-      double a = A[i];
-      tot += a * a;
-      if (i / D != i % D) off += a * a;
-    }
-    off = block_sum(off, red);
-    tot = block_sum(tot, red);
-    // converged: off-diagonal Frobenius mass at the rounding floor (about D eps^2 of the total after a sweep)
-    if (off <= 1e-27 * tot || tot == 0.0) break;
+  bool done = (tot == 0.0);
+  for (; sweep < max_sweeps && !done; ++sweep) {
+    double off = 0.0;
     for (int r = 0; r < n - 1; ++r) {
       // tournament pairing of round r: player n-1 fixed, the others rotate
       if (tid < np) {
-        int a = (tid == 0) ? n - 1 : (r + tid) % (n - 1);
-        int b = (r + n - 1 - tid) % (n - 1);
-        int p = min(a, b), q = max(a, b);
-        double c = 1.0, s = 0.0;
+        const int a = (tid == 0) ? n - 1 : (r + tid) % (n - 1);
+        const int b = (r + n - 1 - tid) % (n - 1);
+        const int p = min(a, b), q = max(a, b);
         if (q < D) {
-          double apq = A[p * D + q];
+          double c = 1.0, sn = 0.0;
+          const double apq = Ac[p * LD + q];
           if (apq != 0.0) {
-            double app = A[p * D + p], aqq = A[q * D + q];
-            double tau = (aqq - app) / (2.0 * apq);
-            double t = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
-            c = 1.0 / sqrt(1.0 + t * t);
-            s = t * c;
+            const double app = Ac[p * LD + p], aqq = Ac[q * LD + q];
+            const double tau = (aqq - app) / (2.0 * apq);
+            const double t = (tau >= 0.0 ? 1.0 : -1.0) / (fabs(tau) + sqrt(1.0 + tau * tau));
+            c = rsqrt(1.0 + t * t);
+            sn = t * c;
           }
-        } else {
-          q = -1;
+          rc[p] = c;
+          rc[q] = c;
+          rs[p] = -sn;
+          rs[q] = sn;
+          part[p] = (sn == 0.0) ? p : q;
+          part[q] = (sn == 0.0) ? q : p;
+        } else {                              // bye
+          rc[p] = 1.0;
+          rs[p] = 0.0;
+          part[p] = p;
         }
-        pp[tid] = p;
-        qq[tid] = q;
-        cs_c[tid] = c;
-        cs_s[tid] = s;
       }
       __syncthreads();
-      // columns: A <- A J, Vm <- Vm J
-      for (int w = tid; w < np * D; w += nt) {
-        int t = w / D, i = w % D;
-        int p = pp[t], q = qq[t];
-        if (q < 0) continue;
-        double c = cs_c[t], s = cs_s[t];
-        if (s == 0.0) continue;
-        double ap = A[i * D + p], aq = A[i * D + q];
-        A[i * D + p] = c * ap - s * aq;
-        A[i * D + q] = s * ap + c * aq;
-        double vp = Vm[i * D + p], vq = Vm[i * D + q];
-        Vm[i * D + p] = c * vp - s * vq;
-        Vm[i * D + q] = s * vp + c * vq;
+      const bool last = (r == n - 2);
+      for (int idx = tid; idx < D * D; idx += nt) {
+        const int i = idx / D, j = idx % D;
+        const int pi = part[i], pj = part[j];
+        const double ci = rc[i], si = rs[i], cj = rc[j], sj = rs[j];
+        const double b0 = cj * Ac[i * LD + j] + sj * Ac[i * LD + pj];      // (A J)[i][j]
+        const double b1 = cj * Ac[pi * LD + j] + sj * Ac[pi * LD + pj];    // (A J)[pi][j]
+        const double x = ci * b0 + si * b1;                                // (J^T A J)[i][j]
+        An[i * LD + j] = x;
+        Vn[i * LD + j] = cj * Vc[i * LD + j] + sj * Vc[i * LD + pj];
+        if (last && i != j) off += x * x;
       }
       __syncthreads();
-      // rows: A <- J^T A
-      for (int w = tid; w < np * D; w += nt) {
-        int t = w / D, j = w % D;
-        int p = pp[t], q = qq[t];
-        if (q < 0) continue;
-        double c = cs_c[t], s = cs_s[t];
-        if (s == 0.0) continue;
-        double ap = A[p * D + j], aq = A[q * D + j];
-        A[p * D + j] = c * ap - s * aq;
-        A[q * D + j] = s * ap + c * aq;
-      }
-      __syncthreads();
+      double* t0 = Ac;
+      Ac = An;
+      An = t0;
+      t0 = Vc;
+      Vc = Vn;
+      Vn = t0;
     }
+    // converged: off-diagonal Frobenius mass at the rounding floor (about D eps^2 of the total after a sweep)
+    off = block_sum(off, red);
+    done = off <= 1e-27 * tot;
   }
-  if (sweep == max_sweeps && tid == 0) atomicOr(flags, SSVI_FLAG_EIG_NOCONV);
+  if (!done && tid == 0) atomicOr(flags, SSVI_FLAG_EIG_NOCONV);
+  for (int i = tid; i < D; i += nt) lam[i] = Ac[i * LD + i];
+  __syncthreads();
+  return Vc;
 }
 
 // In-place Cholesky of the symmetric matrix in Sx (shared, row-major) into its lower triangle;
@@ -209,6 +224,7 @@ __device__ __forceinline__ double finalize_si(const RowUpdateArgs& a, double si_
 __global__ void row_update_diag_kernel(RowUpdateArgs a) {
   __shared__ double red[32];
   const int r = blockIdx.x, n = threadIdx.x, D = a.D;
+  if (a.stop && *a.stop) return;
   const double* acc = a.acc + (int64_t)r * a.acc_len;
   const double count = acc[D + a.cov_len + 1];
   if (count == 0.0) return;                                   // :166-168 nothing observed
@@ -278,28 +294,32 @@ __global__ void row_update_diag_kernel(RowUpdateArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// Full covariance: one CTA per row.  Shared memory (doubles): 5*D*D + 6*D + scratch.
+// Full covariance: one CTA per row.  Shared memory (doubles): 5 matrices of D*LD (LD = D | 1: four of them double as the
+// eigen-solver's work matrices) + 6*D + scratch.
 // ------------------------------------------------------------------------------------------------
 __host__ __device__ inline size_t row_update_full_doubles(int D) {
-  return (size_t)5 * D * D + 6 * D + 4 * ((D + 1) / 2 + 1) + 32;
+  return (size_t)5 * D * jacobi_ld(D) + 6 * D + 3 * (D + 1) + 32;
 }
 
 __global__ void __launch_bounds__(128) row_update_full_kernel(RowUpdateArgs a) {
   extern __shared__ double sm[];
   const int D = a.D, DD = D * D, tid = threadIdx.x, nt = blockDim.x;
+  if (a.stop && *a.stop) return;
+  const int MS = D * jacobi_ld(D);   // doubles per matrix slot (the code outside the eigen-solver uses stride D inside it)
   double* Sold = sm;             // S before the update
-  double* Lm = Sold + DD;        // cached Cholesky factor of S; later chol(S_next)
-  double* Li = Lm + DD;          // inv(L); later S_next
-  double* A = Li + DD;           // matrix handed to the eigen-solver
-  double* Vm = A + DD;           // eigenvectors
-  double* mv = Vm + DD;          // m
+  double* Lm = Sold + MS;        // cached Cholesky factor of S; eigen-solver work; later chol(S_next)
+  double* Li = Lm + MS;          // inv(L); eigen-solver work; later S_next
+  double* A = Li + MS;           // matrix handed to the eigen-solver
+  double* Vm = A + MS;           // eigen-solver work
+  double* mv = Vm + MS;          // m
   double* gv = mv + D;           // mean gradient
   double* tv = gv + D;           // temp vector
   double* cv = tv + D;           // C = inv(S) m
   double* wv = cv + D;           // transformed eigenvalues
   double* mn = wv + D;           // m_next
   double* scratch = mn + D;
-  double* red = scratch + 4 * ((D + 1) / 2 + 1);
+  double* red = scratch + 3 * (D + 1);
+  double* const jbuf[4] = {Lm, Li, Vm, A};
 
   const int r = blockIdx.x;
   const double* acc = a.acc + (int64_t)r * a.acc_len;
@@ -422,9 +442,10 @@ __global__ void __launch_bounds__(128) row_update_full_kernel(RowUpdateArgs a) {
   for (int i = tid; i < D; i += nt) dm2 += (mn[i] - mv[i]) * (mn[i] - mv[i]);
 
   // eigen-decomposition + clamp (:634-636)
-  jacobi_eigh(A, Vm, D, scratch, a.flags);
+  const double* Ev = jacobi_eigh(jbuf, tv, D, scratch, a.flags);   // eigenvectors: stride LD
+  const int LD = jacobi_ld(D);
   for (int i = tid; i < D; i += nt) {
-    const double lam = A[i * D + i];
+    const double lam = tv[i];
     const double w = (a.cov_update == SSVI_UPDATE_N) ? 1.0 / lam : lam;
     wv[i] = fmax(w, a.min_eigenval);                           // NaN -> min_eigenval, like np.maximum? no:
     if (isnan(w)) wv[i] = w;                                   // np.maximum propagates NaN
@@ -436,7 +457,7 @@ __global__ void __launch_bounds__(128) row_update_full_kernel(RowUpdateArgs a) {
     const int i = idx / D, j = idx % D;
     if (j > i) continue;
     double s = 0.0;
-    for (int k = 0; k < D; ++k) s += Vm[i * D + k] * wv[k] * Vm[j * D + k];
+    for (int k = 0; k < D; ++k) s += Ev[i * LD + k] * wv[k] * Ev[j * LD + k];
     if (!isfinite(s)) badS = true;
     Sn[i * D + j] = s;
     Sn[j * D + i] = s;

@@ -354,23 +354,43 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
     return SSVI_OK;
   }
   const size_t smem = (size_t)memo_cta_smem(NT, v.D);
-#define SSVI_MEMO_LAUNCH(NOTH, ONES)                                                                               \
+#define SSVI_MEMO_LAUNCH_K(KERN)                                                                                   \
   do {                                                                                                             \
-    auto kern = accumulate_memo_kernel<NT, NOTH, ONES>;                                                            \
+    auto kern = KERN;                                                                                              \
     CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));               \
     kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot,    \
                                                 chunk_out, entry_ids, rows, h->z_own, z_f32, partial_out);         \
   } while (0)
+#define SSVI_MEMO_LAUNCH(NOTH, ONES, LIN) SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<NT, NOTH, ONES, LIN>))
+  // config 5's instances (four row tiles, two other modes) with a deeper register prefetch at two CTAs per SM
+  if constexpr (NT == 4) {
+    const int pfv = (h->cfg.tuning >> 2) & 3;
+    if (mv.n_oth == 2 && pfv && (v.D & 7) == 0) {
+      const bool lin4 = h->cfg.likelihood == SSVI_LIK_NORMAL && (h->cfg.tuning & SSVI_TUNE_LIN);
+      if (lin4 && pfv == 1) SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<4, 2, false, true, 2, 2>));
+      else if (lin4) SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<4, 2, false, true, 3, 2>));
+      else if (pfv == 1) SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<4, 2, false, false, 2, 2>));
+      else SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<4, 2, false, false, 3, 2>));
+      CUDA_TRY(h, cudaGetLastError());
+      return SSVI_OK;
+    }
+  }
   const bool ones = (v.D & 7) != 0;
-  switch (mv.n_oth * 2 + (ones ? 1 : 0)) {
-    case 2: SSVI_MEMO_LAUNCH(1, false); break;
-    case 3: SSVI_MEMO_LAUNCH(1, true); break;
-    case 4: SSVI_MEMO_LAUNCH(2, false); break;
-    case 5: SSVI_MEMO_LAUNCH(2, true); break;
-    case 6: SSVI_MEMO_LAUNCH(3, false); break;
-    default: SSVI_MEMO_LAUNCH(3, true); break;
+  // normal likelihood: weights linear in f, contraction accumulated across the chunk (accumulate_memo.cuh, LIN)
+  const bool lin = h->cfg.likelihood == SSVI_LIK_NORMAL && (h->cfg.tuning & SSVI_TUNE_LIN);
+  switch (lin ? 10 + mv.n_oth : mv.n_oth * 2 + (ones ? 1 : 0)) {
+    case 2: SSVI_MEMO_LAUNCH(1, false, false); break;
+    case 3: SSVI_MEMO_LAUNCH(1, true, false); break;
+    case 4: SSVI_MEMO_LAUNCH(2, false, false); break;
+    case 5: SSVI_MEMO_LAUNCH(2, true, false); break;
+    case 6: SSVI_MEMO_LAUNCH(3, false, false); break;
+    case 7: SSVI_MEMO_LAUNCH(3, true, false); break;
+    case 11: SSVI_MEMO_LAUNCH(1, false, true); break;
+    case 12: SSVI_MEMO_LAUNCH(2, false, true); break;
+    default: SSVI_MEMO_LAUNCH(3, false, true); break;
   }
 #undef SSVI_MEMO_LAUNCH
+#undef SSVI_MEMO_LAUNCH_K
   CUDA_TRY(h, cudaGetLastError());
   return SSVI_OK;
 }
@@ -592,6 +612,7 @@ extern "C" int ssvi_row_update(SsviHandle* h, int32_t dim, int64_t n_rows, const
   a.w_state = w_state;
   a.si_out = si_out;
   a.flags = h->d_flags;
+  a.stop = h->stop;
   cudaStream_t st = (cudaStream_t)stream;
   if (a.diag) {
     const int threads = ((c.rank + 31) / 32) * 32;
@@ -608,8 +629,10 @@ extern "C" int ssvi_row_update(SsviHandle* h, int32_t dim, int64_t n_rows, const
 
 // update_sigma_param (SSVI_TF_interface.py:684-691; robust: SSVI_TF_robust.py:216-232) replayed in row order.
 __global__ void sigma_update_kernel(int64_t n_rows, int acc_len, int model, double sigma_eta,
-                                    const double* __restrict__ si, const double* __restrict__ acc, double* w_state) {
+                                    const double* __restrict__ si, const double* __restrict__ acc, double* w_state,
+                                    const int32_t* stop) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  if (stop && *stop) return;
   double w_sigma = w_state[0], w_ada = w_state[1];
   const double w_tau = w_state[2];
   for (int64_t r = 0; r < n_rows; ++r) {
@@ -631,7 +654,8 @@ extern "C" int ssvi_sigma_update(SsviHandle* h, int64_t n_rows, const double* si
   if (!h) return SSVI_E_INVALID;
   if (h->cfg.model == SSVI_MODEL_D || n_rows == 0) return SSVI_OK;
   if (n_rows < 0 || !si || !acc || !w_state) return fail(h, SSVI_E_INVALID, "sigma_update: null pointer%s");
-  sigma_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(n_rows, (int)h->acc_len, h->cfg.model, h->cfg.sigma_eta, si, acc, w_state);
+  sigma_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(n_rows, (int)h->acc_len, h->cfg.model, h->cfg.sigma_eta, si, acc, w_state,
+                                                          h->stop);
   CUDA_TRY(h, cudaGetLastError());
   return SSVI_OK;
 }
@@ -639,8 +663,10 @@ extern "C" int ssvi_sigma_update(SsviHandle* h, int64_t n_rows, const double* si
 // update_hyper_parameter (:146-160) + per-mode check_stop_cond (:967-984).  Single CTA: deterministic.
 __global__ void __launch_bounds__(1024) hyper_reduce_kernel(const double* __restrict__ params,
                                                             const double* __restrict__ norm_changes, int64_t n_rows,
-                                                            int D, int diag, double* out) {
+                                                            int D, int diag, double* out, double* psigma_out,
+                                                            const int32_t* stop) {
   __shared__ double s_sum[32], s_m[32], s_c[32];
+  if (stop && *stop) return;
   const int row_len = diag ? 2 * D : (D + 1) * D;
   double sum = 0.0, mm = 0.0, mc = 0.0;
   for (int64_t t = threadIdx.x; t < n_rows * D; t += blockDim.x) {
@@ -677,17 +703,22 @@ __global__ void __launch_bounds__(1024) hyper_reduce_kernel(const double* __rest
     out[0] = t / ((double)n_rows * (double)D);
     out[1] = a;
     out[2] = b;
+    if (psigma_out) *psigma_out = out[0];
   }
 }
 
-extern "C" int ssvi_hyper_reduce(SsviHandle* h, int32_t dim, double* out, void* stream) {
+static int hyper_reduce_impl(SsviHandle* h, int32_t dim, double* out, double* psigma_out, void* stream) {
   if (!h) return SSVI_E_INVALID;
   if (!h->state_bound) return fail(h, SSVI_E_STATE, "hyper_reduce: state not bound%s");
   if (dim < 0 || dim >= h->cfg.order || !out) return fail(h, SSVI_E_INVALID, "hyper_reduce: bad argument%s");
   hyper_reduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(h->params[dim], h->norm_changes[dim], h->cfg.dims[dim], h->cfg.rank,
-                                                            h->cfg.cov_kind == SSVI_COV_DIAG, out);
+                                                            h->cfg.cov_kind == SSVI_COV_DIAG, out, psigma_out, h->stop);
   CUDA_TRY(h, cudaGetLastError());
   return SSVI_OK;
+}
+
+extern "C" int ssvi_hyper_reduce(SsviHandle* h, int32_t dim, double* out, void* stream) {
+  return hyper_reduce_impl(h, dim, out, nullptr, stream);
 }
 
 // predict_entry, posterior-mean predictor (:1039-1052): sum_D prod_modes m
@@ -734,28 +765,23 @@ __host__ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
   return x ^ (x >> 31);
 }
 
-__global__ void __launch_bounds__(128) draw_minibatches_kernel(int64_t n_rows, const int64_t* __restrict__ rows,
-                                                               const int64_t* __restrict__ rowptr,
-                                                               const int64_t* __restrict__ perm, int B, uint64_t seed,
-                                                               const int64_t* __restrict__ seg_start,
-                                                               int64_t* __restrict__ out) {
-  extern __shared__ int32_t picks_all[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t r = (int64_t)blockIdx.x * 4 + warp;
-  if (r >= n_rows) return;
-  int32_t* picks = picks_all + warp * B;
-  const int64_t row = rows[r];
+// one warp draws one row's minibatch into dst; picks: >= 2 B int32 of shared memory owned by the warp (picks | draws)
+__device__ __forceinline__ void draw_row_minibatch(int lane, int32_t* picks, int64_t row, const int64_t* __restrict__ rowptr,
+                                                   const int64_t* __restrict__ perm, int B, uint64_t seed,
+                                                   int64_t* __restrict__ dst) {
   const int64_t lo = rowptr[row], len = rowptr[row + 1] - lo;
-  int64_t* dst = out + seg_start[r];
   if (len <= B) {                                       // kept whole, in append order (:170-174)
     for (int64_t i = lane; i < len; i += 32) dst[i] = perm[lo + i];
     return;
   }
   const uint64_t key = splitmix64(seed ^ splitmix64((uint64_t)row));
+  int32_t* draws = picks + B;                           // the B uniform draws, evaluated lane-parallel up front: the
+  for (int c = lane; c < B; c += 32)                    // sequential part below is then only the membership test
+    draws[c] = (int32_t)__umul64hi(splitmix64(key + (uint64_t)c), (uint64_t)(len - B + c + 1));   // uniform in [0, j]
+  __syncwarp();
   int cnt = 0;
   for (int64_t j = len - B; j < len; ++j, ++cnt) {
-    const uint64_t u = splitmix64(key + (uint64_t)cnt);
-    const int32_t t = (int32_t)__umul64hi(u, (uint64_t)(j + 1));          // uniform in [0, j]
+    const int32_t t = draws[cnt];
     bool hit = false;
     for (int i = lane; i < cnt; i += 32) hit |= (picks[i] == t);
     const bool taken = __any_sync(0xffffffffu, hit);
@@ -765,6 +791,18 @@ __global__ void __launch_bounds__(128) draw_minibatches_kernel(int64_t n_rows, c
   for (int i = lane; i < B; i += 32) dst[i] = perm[lo + picks[i]];
 }
 
+__global__ void __launch_bounds__(128) draw_minibatches_kernel(int64_t n_rows, const int64_t* __restrict__ rows,
+                                                               const int64_t* __restrict__ rowptr,
+                                                               const int64_t* __restrict__ perm, int B, uint64_t seed,
+                                                               const int64_t* __restrict__ seg_start,
+                                                               int64_t* __restrict__ out) {
+  extern __shared__ int32_t picks_all[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t r = (int64_t)blockIdx.x * 4 + warp;
+  if (r >= n_rows) return;
+  draw_row_minibatch(lane, picks_all + warp * 2 * B, rows[r], rowptr, perm, B, seed, out + seg_start[r]);
+}
+
 extern "C" int ssvi_draw_minibatches(SsviHandle* h, int64_t n_rows, const int64_t* rows, const int64_t* rowptr,
                                      const int64_t* perm, int32_t batch_size, uint64_t seed, const int64_t* seg_start,
                                      int64_t* out, void* stream) {
@@ -772,7 +810,9 @@ extern "C" int ssvi_draw_minibatches(SsviHandle* h, int64_t n_rows, const int64_
   if (n_rows == 0) return SSVI_OK;
   if (n_rows < 0 || !rows || !rowptr || !perm || !seg_start || !out) return fail(h, SSVI_E_INVALID, "draw_minibatches: null pointer%s");
   if (batch_size < 1 || batch_size > 2048) return fail(h, SSVI_E_INVALID, "draw_minibatches: batch_size must be in [1, 2048]%s");
-  const size_t smem = (size_t)4 * batch_size * sizeof(int32_t);
+  const size_t smem = (size_t)4 * 2 * batch_size * sizeof(int32_t);
+  if (smem > 48 * 1024)
+    CUDA_TRY(h, cudaFuncSetAttribute(draw_minibatches_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   draw_minibatches_kernel<<<(unsigned)((n_rows + 3) / 4), 128, smem, (cudaStream_t)stream>>>(
       n_rows, rows, rowptr, perm, batch_size, seed, seg_start, out);
   CUDA_TRY(h, cudaGetLastError());
@@ -863,4 +903,150 @@ extern "C" int ssvi_check_flags(SsviHandle* h, int32_t* flags_out, void* stream)
   CUDA_TRY(h, cudaMemsetAsync(h->d_flags, 0, sizeof(int32_t), st));
   CUDA_TRY(h, cudaStreamSynchronize(st));
   return SSVI_OK;
+}
+
+// ---- factorize()'s inner loop on the host side of the library (SSVI_TF_interface.py:117-143) --------------------------------
+// The reference's schedule updates ONE row per mode per iteration; driven from Python that is ~10 library calls, a chunk
+// table upload and a blocking read of the stop condition per row.  Here a whole block of iterations is enqueued from C:
+// per (iteration, mode) one warp plans the row's minibatch on the device (draw + chunk tables), then the same kernels as
+// the per-call path run (variates, stages 1-3, chunk reduction, stage 4, w_sigma, pSigma / max-change reduction), and a
+// one-thread kernel evaluates check_stop_cond (:967-984) after every iteration.  When it fires it latches a device word
+// that the state-writing kernels honour, so the iterations enqueued behind it leave the state exactly as the reference's
+// `break` (:142) does; the caller reads the word whenever it likes.  Nothing crosses the bus inside the loop.
+__global__ void plan_row_kernel(int64_t row, const int64_t* __restrict__ rowptr, const int64_t* __restrict__ perm, int B,
+                                int W, uint64_t seed, int64_t* __restrict__ entry_ids, int32_t* __restrict__ chunk_row,
+                                int64_t* __restrict__ chunk_start, int32_t* __restrict__ chunk_len,
+                                int32_t* __restrict__ chunk_slot0, int64_t* __restrict__ rcp, int64_t* __restrict__ rows,
+                                int64_t* __restrict__ n_obs) {
+  extern __shared__ int32_t picks[];
+  const int lane = threadIdx.x;
+  const int64_t len = rowptr[row + 1] - rowptr[row];
+  const int n = (int)(len < B ? len : B);
+  draw_row_minibatch(lane, picks, row, rowptr, perm, B, seed, entry_ids);
+  const int nch = (n + W - 1) / W;
+  for (int c = lane; c < nch; c += 32) {
+    chunk_row[c] = 0;
+    chunk_start[c] = (int64_t)c * W;
+    chunk_len[c] = min(W, n - c * W);
+    chunk_slot0[c] = c * W;
+  }
+  if (lane == 0) {
+    rcp[0] = 0;
+    rcp[1] = nch;
+    rows[0] = row;
+    n_obs[0] = len;
+  }
+}
+
+__global__ void stop_check_kernel(const double* __restrict__ hyper_out, int N, double eps, int64_t iteration,
+                                  int32_t* stop) {
+  if (threadIdx.x != 0 || blockIdx.x != 0 || stop[0]) return;
+  double dm = 0.0, dc = 0.0;
+  for (int d = 0; d < N; ++d) {
+    dm = fmax(dm, hyper_out[d * 3 + 1]);
+    dc = fmax(dc, hyper_out[d * 3 + 2]);
+  }
+  if (fmax(dm, dc) < eps) {                            // :142
+    stop[0] = 1;
+    stop[1] = (int32_t)iteration;
+  }
+}
+
+static inline int64_t align16(int64_t x) { return (x + 15) & ~(int64_t)15; }
+
+struct LoopWs {
+  int64_t* entry_ids;
+  int32_t *chunk_row, *chunk_len, *chunk_slot0;
+  int64_t *chunk_start, *rcp, *rows, *n_obs;
+  double *partial, *acc, *si;
+  int64_t bytes;
+};
+
+static LoopWs loop_ws_layout(const SsviHandle* h, int32_t B, unsigned char* base) {
+  const int64_t nch = (B + 1) / 2;                      // chunks are >= 2 entries long
+  LoopWs w;
+  int64_t o = 0;
+  auto take = [&](int64_t bytes) { unsigned char* p = base + o; o += align16(bytes); return p; };
+  w.entry_ids = (int64_t*)take(8 * (int64_t)B);
+  w.chunk_row = (int32_t*)take(4 * nch);
+  w.chunk_len = (int32_t*)take(4 * nch);
+  w.chunk_slot0 = (int32_t*)take(4 * nch);
+  w.chunk_start = (int64_t*)take(8 * nch);
+  w.rcp = (int64_t*)take(16);
+  w.rows = (int64_t*)take(8);
+  w.n_obs = (int64_t*)take(8);
+  w.partial = (double*)take(8 * nch * h->acc_len);
+  w.acc = (double*)take(8 * h->acc_len);
+  w.si = (double*)take(8);
+  w.bytes = o;
+  return w;
+}
+
+extern "C" int64_t ssvi_loop_workspace_bytes(const SsviHandle* h, int32_t batch_size) {
+  if (!h || batch_size < 1) return 0;
+  return loop_ws_layout(h, batch_size, nullptr).bytes;
+}
+
+extern "C" int ssvi_factorize_iterations(SsviHandle* h, SsviLoop* lp, int64_t first_iteration, int64_t n_iterations,
+                                         void* stream) {
+  if (!h || !lp) return SSVI_E_INVALID;
+  if (!h->data_bound || !h->state_bound) return fail(h, SSVI_E_STATE, "factorize_iterations: bind data and state first%s");
+  const SsviConfig& c = h->cfg;
+  const int N = c.order;
+  if (lp->batch_size < 1 || lp->batch_size > 2048) return fail(h, SSVI_E_INVALID, "factorize_iterations: batch_size must be in [1, 2048]%s");
+  if (!lp->pSigma || !lp->hyper_out || !lp->stop || !lp->workspace || !lp->z_other || !lp->z_own)
+    return fail(h, SSVI_E_INVALID, "factorize_iterations: null pointer%s");
+  if (c.model != SSVI_MODEL_D && !lp->w_state) return fail(h, SSVI_E_INVALID, "factorize_iterations: w_state required for simple/robust%s");
+  if (lp->workspace_bytes < ssvi_loop_workspace_bytes(h, lp->batch_size)) return fail(h, SSVI_E_INVALID, "factorize_iterations: workspace too small (ssvi_loop_workspace_bytes)%s");
+  for (int d = 0; d < N; ++d)
+    if (!lp->rowptr[d] || !lp->perm[d] || !lp->rowptr_host[d]) return fail(h, SSVI_E_INVALID, "factorize_iterations: index of every mode required%s");
+  int rc = ssvi_bind_noise(h, lp->z_other, lp->z_own, lp->r_w, lp->z_f, lp->pool_slots);
+  if (rc != SSVI_OK) return rc;
+  const LoopWs w = loop_ws_layout(h, lp->batch_size, (unsigned char*)lp->workspace);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int B = lp->batch_size;
+  h->stop = lp->stop;
+  rc = SSVI_OK;
+  for (int64_t it = first_iteration; it < first_iteration + n_iterations && rc == SSVI_OK; ++it) {
+    for (int d = 0; d < N && rc == SSVI_OK; ++d) {
+      const int64_t row = lp->col[d];
+      const int64_t len = lp->rowptr_host[d][row + 1] - lp->rowptr_host[d][row];
+      const int n = (int)(len < B ? len : B);
+      ++lp->minibatch_draws;
+      ++lp->noise_draws;                                 // every call of the reference draws, observed row or not
+      if (n > 0) {
+        // same chunking rule as the per-call path (engine.py:_chunk_tables): short plans are cut fine enough to spread
+        int per = (n + 8 * h->sm_count - 1) / (8 * h->sm_count);
+        if (per < 2) per = 2;
+        const int W = lp->chunk_entries < per ? lp->chunk_entries : per;
+        const int nch = (n + W - 1) / W;
+        plan_row_kernel<<<1, 32, (size_t)2 * B * sizeof(int32_t), st>>>(
+            row, lp->rowptr[d], lp->perm[d], B, W, lp->minibatch_seed + lp->minibatch_draws, w.entry_ids, w.chunk_row,
+            w.chunk_start, w.chunk_len, w.chunk_slot0, w.rcp, w.rows, w.n_obs);
+        rc = ssvi_fill_noise(h, lp->z_other, lp->z_own, lp->r_w, lp->z_f, lp->pool_slots, lp->noise_seed, lp->noise_draws, stream);
+        if (rc == SSVI_OK)
+          rc = ssvi_accumulate(h, d, nch, w.chunk_row, w.chunk_start, w.chunk_len, w.chunk_slot0, w.entry_ids, w.rows,
+                               lp->w_state, w.partial, stream);
+        if (rc == SSVI_OK) rc = ssvi_reduce_chunks(h, 1, w.rcp, w.partial, w.acc, stream);
+        if (rc == SSVI_OK)
+          rc = ssvi_row_update(h, d, 1, w.rows, w.acc, w.n_obs, lp->pSigma, lp->w_state, lp->time_step[d],
+                               lp->fixed_covariance, w.si, stream);
+        if (rc == SSVI_OK && c.model != SSVI_MODEL_D) rc = ssvi_sigma_update(h, 1, w.si, w.acc, lp->w_state, stream);
+        lp->launches += 5 + (c.model != SSVI_MODEL_D ? 1 : 0);
+      }
+      if (rc == SSVI_OK) rc = hyper_reduce_impl(h, d, lp->hyper_out + 3 * d, lp->pSigma + d, stream);   // :125
+      lp->launches += 1;
+    }
+    for (int d = 0; d < N; ++d) {                        // :128-133
+      if (++lp->col[d] >= c.dims[d]) {
+        lp->col[d] = 0;
+        ++lp->time_step[d];
+      }
+    }
+    stop_check_kernel<<<1, 32, 0, st>>>(lp->hyper_out, N, lp->epsilon, it, lp->stop);                    // :135-142
+    lp->launches += 1;
+  }
+  h->stop = nullptr;
+  if (rc == SSVI_OK) CUDA_TRY(h, cudaGetLastError());
+  return rc;
 }

@@ -33,6 +33,7 @@ struct SsviHandle {
   int32_t quad_n;
   // device flag word
   int32_t* d_flags;
+  const int32_t* stop;   // set only while ssvi_factorize_iterations runs: device stop word honoured by the state-writing kernels
   int sm_count;
   int max_smem_optin;
   char err[512];

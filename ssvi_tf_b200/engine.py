@@ -377,6 +377,52 @@ class Engine(object):
                    int(pool.slots), int(seed) & 0xFFFFFFFFFFFFFFFF, int(draw) & 0xFFFFFFFFFFFFFFFF, self._stream())
         self.launches += 1
 
+    # ---- factorize()'s loop enqueued from C (ssvi_factorize_iterations) ---------------------------------------------------
+    def loop_begin(self, pool, batch_size, fixed_covariance, epsilon, noise_seed, noise_draws, minibatch_seed,
+                   minibatch_draws, col):
+        """Argument block for factorize_iterations(): the reference's one-row-per-mode schedule, single GPU."""
+        lp = _lib.SsviLoop()
+        self._loop_keep = []
+        for d in range(self.N):
+            if d not in self._rowptr_d:
+                self._rowptr_d[d] = torch.as_tensor(np.asarray(self.rowptr_h[d], dtype=np.int64)).to(self.device)
+            rp_h = np.ascontiguousarray(self.rowptr_h[d], dtype=np.int64)
+            self._loop_keep.append(rp_h)
+            lp.rowptr[d] = self._rowptr_d[d].data_ptr()
+            lp.perm[d] = self.perm[d].data_ptr()
+            lp.rowptr_host[d] = rp_h.ctypes.data
+            lp.col[d] = int(col[d])
+            lp.time_step[d] = int(self.time_step[d])
+        lp.z_other, lp.z_own = pool.z_other.data_ptr(), pool.z_own.data_ptr()
+        lp.r_w = pool.r_w.data_ptr() if pool.r_w is not None else None
+        lp.z_f = pool.z_f.data_ptr() if pool.z_f is not None else None
+        lp.pool_slots = int(pool.slots)
+        lp.pSigma, lp.w_state, lp.hyper_out = self.pSigma.data_ptr(), self.w_state.data_ptr(), self.hyper_out.data_ptr()
+        self._loop_stop = torch.zeros((2,), dtype=torch.int32, device=self.device)
+        lp.stop = self._loop_stop.data_ptr()
+        nbytes = int(self.lib.ssvi_loop_workspace_bytes(self.h, int(batch_size)))
+        self._loop_ws = torch.empty((nbytes + 15,), dtype=torch.uint8, device=self.device)
+        lp.workspace = (self._loop_ws.data_ptr() + 15) & ~15
+        lp.workspace_bytes = nbytes
+        lp.epsilon = float(epsilon)
+        lp.noise_seed, lp.noise_draws = int(noise_seed) & (2 ** 64 - 1), int(noise_draws)
+        lp.minibatch_seed, lp.minibatch_draws = int(minibatch_seed) & (2 ** 64 - 1), int(minibatch_draws)
+        lp.batch_size, lp.chunk_entries = int(batch_size), int(self.chunk_entries)
+        lp.fixed_covariance = int(bool(fixed_covariance))
+        self.noise = pool
+        return lp
+
+    def factorize_iterations(self, lp, first, count):
+        """Enqueue `count` iterations (no synchronisation); lp's counters, col and time_step advance in place."""
+        before = int(lp.launches)
+        self._call(self.lib.ssvi_factorize_iterations, ctypes.byref(lp), int(first), int(count), self._stream())
+        self.launches += int(lp.launches) - before
+
+    def loop_stop_state(self):
+        """(fired, iteration) of the device stop word -- synchronises."""
+        s = self._loop_stop.cpu().numpy()
+        return bool(s[0]), int(s[1])
+
     def set_tuning(self, tuning):
         """SSVI_TUNE_* kernel options for the calls that follow (A/B timing inside one process)."""
         self._c.tuning = int(tuning)

@@ -114,3 +114,45 @@ def test_shard_range_partitions():
             assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
             sizes = [b - a for a, b in spans]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_split_batch_keeps_the_global_minibatch_at_batch_size():
+    """Sharded per-row updates: the ranks' shares of a row's minibatch add up to min(len, batch_size)
+    (SSVI_TF_interface.py:170-174) and follow the ranks' shares of the row's entries."""
+    from ssvi_tf_b200.dist import split_batch
+    rng = np.random.default_rng(3)
+    counts = rng.integers(0, 400, size=(4, 50))
+    counts[:, 0] = 0
+    counts[:, 1] = [3, 0, 1, 2]
+    q = split_batch(counts, 128)
+    total = counts.sum(axis=0)
+    np.testing.assert_array_equal(q.sum(axis=0), np.minimum(total, 128))
+    assert (q <= counts).all() and (q >= 0).all()
+    big = total > 128
+    ideal = counts[:, big] * 128.0 / total[big]
+    assert np.abs(q[:, big] - ideal).max() < 1.0 + 1e-9
+
+
+def _batch_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from ssvi_tf_b200 import dist as sdist
+    local = np.array([[300, 10, 0, 5], [100, 200, 0, 200]][rank], dtype=np.int64)
+    q.put((rank, sdist.local_batch_sizes(local, 128, None)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_local_batch_sizes_over_gloo():
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_batch_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    np.testing.assert_array_equal(got[0] + got[1], [128, 128, 0, 128])
+    np.testing.assert_array_equal(got[0], [96, 6, 0, 3])

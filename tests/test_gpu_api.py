@@ -128,3 +128,48 @@ def test_true_param_reports_and_state_mirrors(capsys):
     m.update_natural_param_batch(0, 0)
     m.engine.norm_changes[0][0, 0] = 123.0
     assert m.check_stop_cond()[0] == 123.0
+
+
+@pytest.mark.parametrize("model,datatype,diag", [("d", "real", False), ("simple", "binary", True), ("robust", "count", False)])
+def test_device_loop_equals_per_call_loop_including_the_stop(model, datatype, diag):
+    """factorize() in the reference's schedule: the loop enqueued from C (ssvi_factorize_iterations) must leave exactly
+    the state of the per-call Python loop -- same minibatch draws, same variates, same pointer / time_step advance
+    (:117-133) -- also when check_stop_cond fires in the middle of an enqueued block (:135-142)."""
+    import ssvi_tf_b200 as pkg
+    np.random.seed(11)
+    D = 4
+    t = {"real": pkg.RV_tensor, "binary": pkg.binary_tensor, "count": pkg.count_tensor}[datatype]()
+    means = None if datatype != "real" else [np.ones(D) * m for m in (0.5, 1.0, 0.2)]
+    covs = None if datatype != "real" else [np.eye(D) * 0.1] * 3
+    t.synthesize_data([7, 40, 5], means, covs, D=D, train=0.8, sparsity=0.9)
+    cls = {"d": pkg.SSVI_TF_d, "simple": pkg.SSVI_TF_simple, "robust": pkg.SSVI_TF_robust}[model]
+
+    def run(device_loop, epsilon, iters, trace=None):
+        np.random.seed(3)
+        m = cls(t, D, diag=diag, mean0=np.ones(D) if datatype == "real" else np.zeros(D), cov0=np.eye(D) * 0.1,
+                k1=16, k2=8, batch_size=32, noise_dtype=torch.float64, noise_seed=5)
+        m.device_loop, m.epsilon = device_loop, epsilon
+        if trace is not None:
+            orig = m.check_stop_cond
+            m.check_stop_cond = lambda: trace.append(orig()) or trace[-1]
+        m.factorize(report=10 ** 9, max_iteration=iters, detailed_report=False)
+        st = [p.cpu().numpy().copy() for p in m.engine.params] + [m.engine.ada_mean[0].cpu().numpy().copy(),
+                                                                  m.engine.w_state.cpu().numpy().copy(), np.asarray(m.pSigma)]
+        return st, list(m.time_step), (m.d_mean, m.d_cov), dict(m.missing)
+
+    trace = []
+    a = run(False, 1e-4, 23, trace)
+    b = run(True, 1e-4, 23)
+    for x, y in zip(a[0], b[0]):
+        np.testing.assert_array_equal(x, y)
+    assert a[1:] == b[1:]
+    # a stop in the middle of an enqueued block: epsilon just above the smallest change seen in iterations 1..15
+    eps = min(max(tr) for tr in trace[1:16]) * (1 + 1e-9)
+    stop_at = next(i for i, tr in enumerate(trace) if max(tr) < eps)
+    assert stop_at <= 15
+    a = run(False, eps, 23)
+    b = run(True, eps, 23)
+    for x, y in zip(a[0], b[0]):
+        np.testing.assert_array_equal(x, y)
+    assert a[1:] == b[1:]
+    assert a[1] == [(stop_at + 1) // n for n in (7, 40, 5)]

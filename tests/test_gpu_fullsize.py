@@ -79,6 +79,31 @@ def test_config2_full_size_properties():
         _close(acc16, acc, "c2 mode %d: 16-entry chunks vs 64" % dim)
         eng.sweep_chunk_entries = 64
         eng._sweep_plans.clear()
+    # ---- one FULL-LENGTH row of every mode against the CPU oracle (the reference's own arithmetic, pinned by
+    #      tests/golden): ~8000 entries, entry b of the row reading pool slot b mod P, accumulator record compared -------
+    from oracle import ssvi_oracle as so
+    from ssvi_tf_b200.engine import noise_offsets
+    D, k1, P = c["D"], c["k1"], int(eng.noise.slots)
+    off = noise_offsets(D, k1, False)                                       # [c, k] -> position inside a noise block
+    z_other = eng.noise.z_other.double().cpu().numpy()[:, :, off]           # [P, N-1, D, k1]
+    z_own = eng.noise.z_own.double().cpu().numpy()[:, off]                  # [P, D, k1]
+    z_other, z_own = np.swapaxes(z_other, -1, -2), np.swapaxes(z_own, -1, -2)    # numpy-natural (.., k1, D)
+    ocfg = so.make_config("d", "bernoulli", D, k1=k1, k2=c["k2"], batch_size=10 ** 9)
+    ost = dict(params=[p.cpu().numpy() for p in eng.params])
+    coords_h, vals_h = eng.coords.cpu().numpy().astype(np.int64), eng.vals.cpu().numpy()
+    for dim in range(eng.N):
+        acc = eng.accumulate(eng.plan_sweep(dim)).clone()
+        rp = np.asarray(eng.rowptr_h[dim])
+        row = int(np.argmax(rp[1:] - rp[:-1]))                              # the mode's longest row
+        ids = eng.perm[dim][int(rp[row]):int(rp[row + 1])].cpu().numpy()
+        sl = np.arange(len(ids)) % P
+        tape = so.Tape(z_other[sl], z_own[sl])
+        di, Di, si, scale, B = so.row_accumulate(ost, ocfg, dim, row, coords_h[ids], vals_h[ids], tape)
+        got = acc[row].cpu().numpy()
+        assert B == len(ids) == int(got[-1]) and scale == 1.0
+        np.testing.assert_allclose(got[:D], di, rtol=1e-5, atol=1e-5 * np.abs(di).max(), err_msg="c2 mode %d di" % dim)
+        np.testing.assert_allclose(got[D:D + D * D].reshape(D, D), Di, rtol=1e-5, atol=1e-5 * np.abs(Di).max(),
+                                   err_msg="c2 mode %d Di" % dim)
     # additivity over two entry shards (mode 1)
     from ssvi_tf_b200.engine import Engine
     dim = 1

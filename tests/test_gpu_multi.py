@@ -96,3 +96,33 @@ def test_two_gpu_sweeps_match_one_gpu_and_row_block_stage4():
     for mode in (False, True):
         for a, b in zip(got[0][mode][0], got[1][mode][0]):        # replicas identical
             np.testing.assert_array_equal(a, b)
+
+
+def _selfcheck_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda:%d" % rank))
+    from ssvi_tf_b200 import dist as sdist
+    q.put((rank, sdist.selfcheck(dist.group.WORLD, "cuda:%d" % rank)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_in_run_selfcheck_of_bench_passes_on_every_rank():
+    """ssvi_tf_b200.dist.selfcheck is what `bench.py --gpus N` runs before timing (multi_gpu_parity in its JSON line)."""
+    import torch.multiprocessing as mp
+    world = min(torch.cuda.device_count(), 8)
+    world = 1 << (world.bit_length() - 1)
+    port = _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_selfcheck_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=300) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert got == {r: "ok" for r in range(world)}

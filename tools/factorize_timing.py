@@ -23,6 +23,7 @@ def run(iters, rpi, seed=319):
         t.synthesize_data(dims, means, covs, D, 0.8, 1, 0.1)
         m = pkg.SSVI_TF_d(t, D, mean0=np.ones(D), cov0=np.eye(D) * 0.1, k1=64, k2=128, batch_size=128, randstart=True,
                           chunk_entries=int(os.environ.get("SSVI_CHUNK", "16")))
+        m.device_loop = os.environ.get("SSVI_DEVICE_LOOP", "1") != "0"     # 0: the per-call Python loop
         m.factorize(report=10 ** 9, max_iteration=20, detailed_report=False, rows_per_iteration=rpi)    # warm-up
         torch.cuda.synchronize()
         t0 = time.perf_counter()
@@ -31,7 +32,8 @@ def run(iters, rpi, seed=319):
         dt = time.perf_counter() - t0
         rmse, err = m.evaluate_test_error()
     rows = 3 if rpi == 1 else sum(dims)
-    return dict(schedule="one row per mode" if rpi == 1 else "all rows", iterations=iters + 1, seconds=round(dt, 3),
+    return dict(schedule="one row per mode" if rpi == 1 else "all rows", device_loop=bool(m.device_loop and rpi == 1),
+                iterations=iters + 1, seconds=round(dt, 3),
                 iterations_per_s=round((iters + 1) / dt, 1), row_updates_per_s=round((iters + 1) * rows / dt, 1),
                 entry_updates_per_s=round((iters + 1) * rows * 128 / dt, 1), test_rmse=round(float(rmse), 4))
 

@@ -1,7 +1,11 @@
 #!/usr/bin/env python
-"""Print the metrics that matter from an .ncu-rep (raw page): usage ncu_summary.py file.ncu-rep"""
+"""Print the metrics that matter from an .ncu-rep (raw page) or from the raw page exported on the GPU box by
+tools/ncu_export.sh: usage ncu_summary.py file.ncu-rep | file.raw.csv"""
 import csv, subprocess, sys
-out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+if sys.argv[1].endswith(".csv"):
+    out = open(sys.argv[1]).read()
+else:
+    out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hdr, units = rows[0], rows[1]
 keys = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
