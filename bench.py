@@ -65,6 +65,8 @@ SIDE_RUNS = [
     ("c3", "c3", 0.25, {}),
     ("c3_quadrature", "c3", 0.25, {"quadrature": 30}),
     ("c4", "c4", 1.0, {}),
+    # the contract's fp32 option on the headline workload: sample table stored as floats (arithmetic stays fp64)
+    ("c5_table_f32", "c5", 1.0, {"table_f32": True}),
 ]
 
 
@@ -238,6 +240,7 @@ def owned_fine_blocks(dims, rank, world):
 
 
 def build_model(c, data, device, group, chunk_entries, noise_slots, engine_kwargs=None, quadrature=None):
+    """The reference's constructor call (synthetic_test.py:139) on a device-resident tensor."""
     import torch
     import ssvi_tf_b200 as pkg
     cls = {"d": pkg.SSVI_TF_d, "simple": pkg.SSVI_TF_simple, "robust": pkg.SSVI_TF_robust}[c["model"]]
@@ -276,7 +279,7 @@ def hbm_peak():
 # ------------------------------------------------------------------------------------------------
 class Workload(object):
     def __init__(self, args, cfg_id, c, device, rank, world, group, scale=1.0, batch_size=None, quadrature=None,
-                 sharded=False):
+                 sharded=False, table_f32=False):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -297,7 +300,9 @@ class Workload(object):
         self.model = build_model(c, data, device, group if sharded else None, args.chunk_entries, args.noise_slots,
                                  dict(table_budget_bytes=int(args.table_mb * (1 << 20)),
                                       sweep_chunk_entries=args.sweep_chunk, sweep_streams=args.sweep_streams,
-                                      sweep_tile_blocks=args.tile_blocks, tuning=args.tuning), quadrature=quadrature)
+                                      sweep_tile_blocks=args.tile_blocks, tuning=args.tuning,
+                                      table_dtype=torch.float32 if table_f32 else torch.float64),
+                                 quadrature=quadrature)
         self.eng = self.model.engine
         self.N = self.model.order
         n = torch.tensor([self.eng.nnz], device=device, dtype=torch.int64)
@@ -674,6 +679,7 @@ def main():
     ap.add_argument("--tuning", type=int, default=0, help="SSVI_TUNE_* bits for the headline run (include/ssvi_b200.h)")
     ap.add_argument("--ab-tunings", default="", help="comma-separated SSVI_TUNE_* values timed after the headline, same "
                                                      "process and plans (details.ab_tunings); diagnostic")
+    ap.add_argument("--table-f32", action="store_true", help="headline with the sample table stored as floats (fp32 option)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="diagnostic runs only")
     ap.add_argument("--no-configs", action="store_true", help="skip the side measurements of the other configs (N = 1)")
@@ -702,7 +708,7 @@ def main():
         parity = sdist.selfcheck(group, device)
 
     wl = Workload(args, args.config, c, device, rank, world, group, scale=args.scale,
-                  batch_size=args.batch_size or None, sharded=True)
+                  batch_size=args.batch_size or None, sharded=True, table_f32=args.table_f32)
     res = wl.run_resident(args.steps, args.warmup, sample_clocks=True)
     ab = {}
     for t in [int(x) for x in args.ab_tunings.split(",") if x]:
@@ -739,13 +745,14 @@ def main():
             t0 = time.time()
             try:
                 w2 = Workload(args, cid, cc, device, 0, 1, None, scale=scale, batch_size=opt.get("batch_size"),
-                              quadrature=opt.get("quadrature"))
+                              quadrature=opt.get("quadrature"), table_f32=opt.get("table_f32", False))
                 r2 = w2.run_resident(2 * Nm, Nm)
                 side[key] = {"workload": cc["desc"] + (" at %.3g of its nnz" % scale if scale != 1.0 else ""),
                              "schedule": ("reference minibatches: every row takes <= %d entries drawn on the device each "
                                           "sweep, scale = len/B" % opt["batch_size"]) if opt.get("batch_size") else
                              "full-row Jacobi sweeps (scale = 1)" + (", 30-node Gauss-Hermite second layer "
-                                                                    "(SSVI_TF_robust quadrature=True)" if opt.get("quadrature") else ""),
+                                                                    "(SSVI_TF_robust quadrature=True)" if opt.get("quadrature") else "")
+                             + (", sample table stored as float32 (SSVI_TABLE_F32), arithmetic fp64" if opt.get("table_f32") else ""),
                              "nnz_train": w2.eng.nnz, "steps": 2 * Nm, "warmup": Nm, "value": r2["value"], "unit": UNIT,
                              "ms_per_step": r2["ms_per_step"], "roofline_frac": r2["roofline"]["frac"],
                              "algorithmic_bytes_per_unit": r2["roofline"]["algorithmic_bytes_per_unit"],
@@ -766,7 +773,8 @@ def main():
         print(json.dumps({
             "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64" if not args.table_f32 else "f64 (f32 sample table)",
+            "data": "synthetic",
             "config": workload_config(args, c, world), "details": details, "multi_gpu_parity": parity,
             "roofline": res["roofline"], "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": res["launches"],
             "clocks": res["clocks"], "configs": side, "wall_s": round(time.time() - t_start, 1)}))

@@ -51,6 +51,11 @@ enum { SSVI_MODEL_D = 0, SSVI_MODEL_SIMPLE = 1, SSVI_MODEL_ROBUST = 2 };
 enum { SSVI_LIK_NORMAL = 0, SSVI_LIK_BERNOULLI = 1, SSVI_LIK_POISSON = 2 };
 enum { SSVI_UPDATE_S = 0, SSVI_UPDATE_N = 1 };
 enum { SSVI_NOISE_F64 = 0, SSVI_NOISE_F32 = 1 };
+/* Sample table of ssvi_sweep_accumulate.  F64 (default): the tabulated samples X(j, s) = m_j + L_j Z(s) are the doubles the
+ * direct kernels compute.  F32: they are rounded to float when they are written (relative 6e-8) and widened again when
+ * read; every sum, product and likelihood term is still fp64.  Halves the bytes a sweep gathers.  The fp32 option of
+ * the contract (tolerance 1e-4); measured deviation of the updated rows from the F64 table: see DESIGN.md 3.5. */
+enum { SSVI_TABLE_F64 = 0, SSVI_TABLE_F32 = 1 };
 
 enum {
   SSVI_OK = 0,
@@ -82,6 +87,8 @@ typedef struct SsviConfig {
   int32_t noise_dtype;      /* SSVI_NOISE_*    element type of the noise pool           */
   int32_t kernel_path;      /* 0 = auto; 1 = force the generic CUDA-core accumulate path (testing)  */
   int32_t tuning;           /* bit set of SSVI_TUNE_* kernel options (0 = defaults); results do not depend on it */
+  int32_t table_dtype;      /* SSVI_TABLE_*: element type of the sweep path's sample table (SSVI_TF_d, full covariance) */
+  int32_t reserved2;
   double eta;               /* (:85)  */
   double cov_eta;           /* (:86)  */
   double sigma_eta;         /* (:88)  */

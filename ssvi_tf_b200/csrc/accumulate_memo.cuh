@@ -25,6 +25,7 @@ struct MemoView {
   int32_t n_oth;                          // N - 1
   int32_t rec_len;                        // doubles per table record = NT * KT * 64
   int32_t slot_lo, n_slots;               // slots [slot_lo, slot_lo + n_slots) are in the table
+  int32_t tab32;                          // records hold FLOATS: [NT][KT/2][32] float4 = (x, y of k-tile 2p | x, y of 2p+1)
   int32_t od[SSVI_MEMO_MAX_OTH];          // other modes, ascending
   int64_t n_rows[SSVI_MEMO_MAX_OTH];      // rows of each other mode
   int64_t rec_base[SSVI_MEMO_MAX_OTH + 1];// first record of each other mode's block; [n_oth] = total records
@@ -86,6 +87,21 @@ __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView m
   // Padding rows (n >= D) come out as exact zeros (zero mean, zero factor rows); row n == D is set to ONE so that the
   // contraction V V^T of the accumulate kernel also delivers the row sums sum_k V[n][k] (its row D) for free.
   const int64_t rec = memo_rec(mv, jj, sl, j);
+  if (mv.tab32) {                                       // SSVI_TABLE_F32: half the bytes, two k-tiles per 16-byte load
+    float4* out = reinterpret_cast<float4*>(mv.tab) + rec * (int64_t)(NT * (KT >> 1) * 32);
+#pragma unroll
+    for (int i = 0; i < NT; ++i) {
+      const bool one = (8 * i + g) == D;
+#pragma unroll
+      for (int tp = 0; tp < 4; ++tp)
+        if (2 * tp < KT)
+          out[(i * (KT >> 1) + tp) * 32 + lane] =
+              one ? make_float4(1.f, 1.f, 1.f, 1.f)
+                  : make_float4((float)vv[i][2 * tp][0], (float)vv[i][2 * tp][1], (float)vv[i][2 * tp + 1][0],
+                                (float)vv[i][2 * tp + 1][1]);
+    }
+    return;
+  }
   double2* out = reinterpret_cast<double2*>(mv.tab + rec * (int64_t)mv.rec_len);
 #pragma unroll
   for (int i = 0; i < NT; ++i) {
@@ -131,6 +147,16 @@ __host__ __device__ inline int memo_cta_smem(int NT, int D) { return memo_region
 
 __device__ __forceinline__ double2 ld_tab(const double2* p) { return __ldcg(p); }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ float4 ld_tab4(const float4* p) { return __ldcg(p); }
+// float -> double on the INTEGER pipe (an F2F.F64.F32 occupies the FP64 pipe like four DFMAs, and that pipe is what the
+// DMMAs need): sign | (exponent + 896) << 20 | mantissa >> 3 in the high word, mantissa << 29 in the low word; zeros and
+// denormals (exponent field 0) become +-0.
+__device__ __forceinline__ double f2d_int(float f) {
+  const uint32_t u = __float_as_uint(f);
+  const bool tiny = (u & 0x7f800000u) == 0u;
+  const uint32_t hi = (u & 0x80000000u) | (tiny ? 0u : (((u >> 3) & 0x0fffffffu) + 0x38000000u));
+  return __hiloint2double((int)hi, tiny ? 0 : (int)(u << 29));
+}
 
 // ---------------------------------------------------------------------------------------------------------------------
 // One CTA (4 warps) per chunk = run of entries of ONE row that share ONE noise slot.
@@ -147,7 +173,11 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 //         What paces this kernel when the table does not sit in L2 (config 5) is the bytes a warp keeps in flight
 //         (one 4 KB k-tile at PF = 1, 12 warps per SM): deeper prefetch costs 32 registers per k-tile at NT = 4, paid
 //         for with fewer resident CTAs.
-template <int NT, int NOTH, bool ONES, bool LIN, int PF = SSVI_MEMO_PF, int MINB = (NT <= 3 ? SSVI_MEMO_MINB : 3)>
+//   T32:  the table holds floats (MemoView::tab32): one 16-byte load per lane brings TWO k-tiles of a row tile, so the
+//         same registers keep twice the k-range in flight and the L2 -> SM bytes per entry halve; the values are widened
+//         on the integer pipe (f2d_int) and everything downstream is the fp64 arithmetic of the other instances.
+template <int NT, int NOTH, bool ONES, bool LIN, int PF = SSVI_MEMO_PF, int MINB = (NT <= 3 ? SSVI_MEMO_MINB : 3),
+          bool T32 = false>
 __global__ void __launch_bounds__(128, MINB) accumulate_memo_kernel(
     DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
     const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
@@ -178,8 +208,11 @@ __global__ void __launch_bounds__(128, MINB) accumulate_memo_kernel(
   // ---- this warp's entries (w, w+4, ...): value and table records, fetched lane-parallel before the prologue so the
   //      index -> coordinate -> table chain of loads overlaps the own-row sampling ------------------------------------
   const int my_cnt = (len - warp + 3) >> 2;             // may be 0 for high warps of a short chunk
+  static_assert(!T32 || (PF == 1 && !LIN), "the float table comes with the base kernel only");
   const double2* tab2 = reinterpret_cast<const double2*>(mv.tab);
   const int rec2 = mv.rec_len >> 1;                     // double2 per record
+  const float4* tab4 = reinterpret_cast<const float4*>(mv.tab);
+  constexpr int REC4 = NT * (KT / 2) * 32;              // float4 per record (T32)
   double my_y = 0.0;
   int32_t my_rec[NOTH];
 #pragma unroll
@@ -193,8 +226,17 @@ __global__ void __launch_bounds__(128, MINB) accumulate_memo_kernel(
 
   double2 cur[NOTH][NT];                                // first k-tile of the first entry: in flight during the prologue
   double2 pf[PF - 1 > 0 ? PF - 1 : 1][NOTH][NT];        // k-tiles 1 .. PF-1 (deeper prefetch only)
+  float4 cur4[T32 ? NOTH : 1][T32 ? NT : 1];            // T32: first PAIR of k-tiles
+  if constexpr (T32) {
 #pragma unroll
-  for (int jj = 0; jj < NOTH; ++jj) {
+    for (int jj = 0; jj < NOTH; ++jj) {
+      const float4* p = tab4 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * REC4 + lane;
+#pragma unroll
+      for (int i = 0; i < NT; ++i) cur4[jj][i] = ld_tab4(p + (i * (KT / 2)) * 32);
+    }
+  }
+#pragma unroll
+  for (int jj = 0; jj < (T32 ? 0 : NOTH); ++jj) {
     const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
 #pragma unroll
     for (int i = 0; i < NT; ++i) cur[jj][i] = ld_tab(p + (i * KT) * 32);
@@ -260,7 +302,17 @@ __global__ void __launch_bounds__(128, MINB) accumulate_memo_kernel(
         for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
       }
     }
-    if (b0 > 0) {
+    if constexpr (T32) {
+      if (b0 > 0) {
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj) {
+          const float4* p = tab4 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * REC4 + lane;
+#pragma unroll
+          for (int i = 0; i < NT; ++i) cur4[jj][i] = ld_tab4(p + (i * (KT / 2)) * 32);
+        }
+      }
+    }
+    if (b0 > 0 && !T32) {
 #pragma unroll
       for (int jj = 0; jj < NOTH; ++jj) {
         const double2* p = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * rec2 + lane;
@@ -282,7 +334,15 @@ __global__ void __launch_bounds__(128, MINB) accumulate_memo_kernel(
         pc[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], el) * rec2 + lane;
         pn[jj] = tab2 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], eln) * rec2 + lane;
       }
-      if (l2_prefetch && eln != el) {                   // next entry's records -> L2, one entry (8 k-tiles) ahead of use
+      const float4* pc4[NOTH];
+      const float4* pn4[NOTH];
+      float4 nxt4[T32 ? NOTH : 1][T32 ? NT : 1];        // T32: the next pair of k-tiles (the next entry's first pair at the end)
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) {
+        pc4[jj] = tab4 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], el) * REC4 + lane;
+        pn4[jj] = tab4 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], eln) * REC4 + lane;
+      }
+      if (l2_prefetch && eln != el && !T32) {                   // next entry's records -> L2, one entry (8 k-tiles) ahead of use
 #pragma unroll
         for (int jj = 0; jj < NOTH; ++jj) {
           const char* r0 = reinterpret_cast<const char*>(pn[jj] - lane) + lane * 128;
@@ -301,11 +361,28 @@ __global__ void __launch_bounds__(128, MINB) accumulate_memo_kernel(
 #pragma unroll
       for (int t = 0; t < KT; ++t) {
         double2 nxt[NOTH][NT];                          // PF k-tiles ahead (the next entry's first tiles at t >= KT-PF)
+        if constexpr (T32) {
+          if ((t & 1) == 0) {
 #pragma unroll
-        for (int jj = 0; jj < NOTH; ++jj) {
-          const double2* p = (t + PF < KT) ? pc[jj] + (t + PF) * 32 : pn[jj] + (t + PF - KT) * 32;
+            for (int jj = 0; jj < NOTH; ++jj) {
+              const float4* p = (t + 2 < KT) ? pc4[jj] + (t / 2 + 1) * 32 : pn4[jj];
 #pragma unroll
-          for (int i = 0; i < NT; ++i) nxt[jj][i] = ld_tab(p + (i * KT) * 32);
+              for (int i = 0; i < NT; ++i) nxt4[jj][i] = ld_tab4(p + (i * (KT / 2)) * 32);
+            }
+          }
+#pragma unroll
+          for (int jj = 0; jj < NOTH; ++jj)
+#pragma unroll
+            for (int i = 0; i < NT; ++i)
+              cur[jj][i] = (t & 1) ? make_double2(f2d_int(cur4[jj][i].z), f2d_int(cur4[jj][i].w))
+                                   : make_double2(f2d_int(cur4[jj][i].x), f2d_int(cur4[jj][i].y));
+        } else {
+#pragma unroll
+          for (int jj = 0; jj < NOTH; ++jj) {
+            const double2* p = (t + PF < KT) ? pc[jj] + (t + PF) * 32 : pn[jj] + (t + PF - KT) * 32;
+#pragma unroll
+            for (int i = 0; i < NT; ++i) nxt[jj][i] = ld_tab(p + (i * KT) * 32);
+          }
         }
         double2 vv[NT], fpt;
 #pragma unroll
@@ -349,7 +426,9 @@ __global__ void __launch_bounds__(128, MINB) accumulate_memo_kernel(
         for (int jj = 0; jj < NOTH; ++jj)
 #pragma unroll
           for (int i = 0; i < NT; ++i) {
-            if (PF == 1) {
+            if constexpr (T32) {
+              if (t & 1) cur4[jj][i] = nxt4[jj][i];
+            } else if constexpr (PF == 1) {
               cur[jj][i] = nxt[jj][i];
             } else {
               cur[jj][i] = pf[0][jj][i];

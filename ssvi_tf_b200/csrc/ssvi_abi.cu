@@ -63,6 +63,7 @@ extern "C" int ssvi_create(const SsviConfig* cfg, SsviHandle** out) {
   if (cfg->mean_update != SSVI_UPDATE_S && cfg->mean_update != SSVI_UPDATE_N) return fail(nullptr, SSVI_E_INVALID, "Unidentified update formula for mean param%s");
   if (cfg->cov_update != SSVI_UPDATE_S && cfg->cov_update != SSVI_UPDATE_N) return fail(nullptr, SSVI_E_INVALID, "Unidentified update formula for covariance param%s");
   if (cfg->noise_dtype != SSVI_NOISE_F64 && cfg->noise_dtype != SSVI_NOISE_F32) return fail(nullptr, SSVI_E_INVALID, "bad noise_dtype%s");
+  if (cfg->table_dtype != SSVI_TABLE_F64 && cfg->table_dtype != SSVI_TABLE_F32) return fail(nullptr, SSVI_E_INVALID, "bad table_dtype%s");
   for (int d = 0; d < cfg->order; ++d)
     if (cfg->dims[d] < 1) return fail(nullptr, SSVI_E_INVALID, "dims must be >= 1%s");
   int ndev = 0;
@@ -299,6 +300,10 @@ static bool sweep_full_ok(const SsviConfig& c) {
   return c.cov_kind == SSVI_COV_FULL && c.rank <= 32 && c.k1 == 8 * SSVI_MEMO_KT && c.order >= 2 &&
          c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
 }
+// the float table is built for the kernels of SSVI_TF_d (the three-pass path of simple / robust keeps doubles)
+static bool table_f32(const SsviConfig& c) {
+  return c.table_dtype == SSVI_TABLE_F32 && c.model == SSVI_MODEL_D && c.cov_kind == SSVI_COV_FULL;
+}
 static bool sweep_ok(const SsviHandle* h) { return sweep_full_ok(h->cfg) || sweep_diag_ok(h->cfg, h->max_smem_optin); }
 
 extern "C" int ssvi_sweep_supported(const SsviHandle* h) { return (h && sweep_ok(h)) ? 1 : 0; }
@@ -308,7 +313,7 @@ extern "C" int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int3
   int64_t recs = 0;
   for (int d = 0; d < h->cfg.order; ++d)
     if (d != dim) recs += h->cfg.dims[d] * (int64_t)n_slots;
-  return recs * memo_rec_len(h->cfg.rank, h->cfg.k1) * (int64_t)sizeof(double);
+  return recs * memo_rec_len(h->cfg.rank, h->cfg.k1) * (int64_t)(table_f32(h->cfg) ? sizeof(float) : sizeof(double));
 }
 
 extern "C" int64_t ssvi_sweep_work_bytes(const SsviHandle* h, int64_t n_entries) {
@@ -365,7 +370,7 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
   // config 5's instances (four row tiles, two other modes) with a deeper register prefetch at two CTAs per SM
   if constexpr (NT == 4) {
     const int pfv = (h->cfg.tuning >> 2) & 3;
-    if (mv.n_oth == 2 && pfv && (v.D & 7) == 0) {
+    if (mv.n_oth == 2 && pfv && (v.D & 7) == 0 && !mv.tab32) {
       const bool lin4 = h->cfg.likelihood == SSVI_LIK_NORMAL && (h->cfg.tuning & SSVI_TUNE_LIN);
       if (lin4 && pfv == 1) SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<4, 2, false, true, 2, 2>));
       else if (lin4) SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<4, 2, false, true, 3, 2>));
@@ -374,6 +379,20 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
       CUDA_TRY(h, cudaGetLastError());
       return SSVI_OK;
     }
+  }
+  if (mv.tab32) {                                       // SSVI_TABLE_F32: the base kernel over a float table
+    constexpr int MB = (NT <= 3 ? SSVI_MEMO_MINB : 3);
+    const bool ones32 = (v.D & 7) != 0;
+    switch (mv.n_oth * 2 + (ones32 ? 1 : 0)) {
+      case 2: SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<NT, 1, false, false, 1, MB, true>)); break;
+      case 3: SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<NT, 1, true, false, 1, MB, true>)); break;
+      case 4: SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<NT, 2, false, false, 1, MB, true>)); break;
+      case 5: SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<NT, 2, true, false, 1, MB, true>)); break;
+      case 6: SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<NT, 3, false, false, 1, MB, true>)); break;
+      default: SSVI_MEMO_LAUNCH_K((accumulate_memo_kernel<NT, 3, true, false, 1, MB, true>)); break;
+    }
+    CUDA_TRY(h, cudaGetLastError());
+    return SSVI_OK;
   }
   const bool ones = (v.D & 7) != 0;
   // normal likelihood: weights linear in f, contraction accumulated across the chunk (accumulate_memo.cuh, LIN)
@@ -483,6 +502,7 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
   mv.slot_lo = slot_lo;
   mv.n_slots = n_slots;
   mv.tab = (double*)table_ws;
+  mv.tab32 = table_f32(h->cfg) ? 1 : 0;
   int jj = 0;
   int64_t base = 0, blocks = 0;
   for (int d = 0; d < h->cfg.order; ++d) {

@@ -160,7 +160,8 @@ class Engine(object):
 
     def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16,
                  kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64, sweep_streams=2,
-                 sweep_tile_blocks=0, sweep_tile_min_entries=24.0, record_budget_bytes=256 << 20, tuning=0):
+                 sweep_tile_blocks=0, sweep_tile_min_entries=24.0, record_budget_bytes=256 << 20, tuning=0,
+                 table_dtype=torch.float64):
         """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
         cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
         if not torch.cuda.is_available():
@@ -196,6 +197,9 @@ class Engine(object):
         c.noise_dtype = _lib.NOISE_F32 if noise_dtype == torch.float32 else _lib.NOISE_F64
         c.kernel_path = int(kernel_path)      # 0 auto, 1 force the generic CUDA-core accumulate path
         c.tuning = int(tuning)                # SSVI_TUNE_* bits (include/ssvi_b200.h); never changes a result
+        # sample table of the sweep path as floats (SSVI_TF_d, full covariance): the contract's fp32 option, tolerance 1e-4
+        c.table_dtype = _lib.TABLE_F32 if table_dtype == torch.float32 else _lib.TABLE_F64
+        self.table_dtype = table_dtype
         c.eta, c.cov_eta, c.sigma_eta = float(cfg["eta"]), float(cfg["cov_eta"]), float(cfg["sigma_eta"])
         c.poisson_eta = float(cfg.get("poisson_eta", 0.1))
         c.min_eigenval = float(cfg.get("min_eigenval", 0.01))

@@ -42,7 +42,7 @@ def test_version_and_acc_len():
 def test_config_struct_matches_header_layout():
     from ssvi_tf_b200 import _lib
     # 12 int32 + 7 double + 8 int64
-    assert ctypes.sizeof(_lib.SsviConfig) == 12 * 4 + 7 * 8 + 8 * 8
+    assert ctypes.sizeof(_lib.SsviConfig) == 14 * 4 + 7 * 8 + 8 * 8
 
 
 def test_create_rejects_bad_config_without_gpu():

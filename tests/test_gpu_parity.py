@@ -224,6 +224,17 @@ def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W
                 assert len(plan.groups) == P
                 np.testing.assert_array_equal(np.sort(plan.entry_ids.cpu().numpy()), np.sort(perm[dim]))
             acc = eng.accumulate(plan).cpu().numpy().copy()
+            if sweep and model == "d":
+                # the SSVI_TUNE_* kernel variants (include/ssvi_b200.h) must give the same records: L2 prefetch, the
+                # linear-weight kernel of the normal likelihood, deeper register prefetch (rank 25..32, order 3)
+                for tuning in (1, 2, 3, 4, 8, 2 | 4, 2 | 8):
+                    eng.set_tuning(tuning)
+                    alt = eng.accumulate(plan).cpu().numpy()
+                    np.testing.assert_allclose(alt, acc, rtol=1e-9, atol=1e-12 * np.abs(acc).max(),
+                                               err_msg="tuning %d" % tuning)
+                    np.testing.assert_array_equal(alt[:, -1], acc[:, -1])
+                eng.set_tuning(0)
+                eng.check_flags()
             eng.row_update(plan, eng.accumulate(plan))
             eng.check_flags()
             accs.append(acc)
@@ -246,6 +257,62 @@ def test_sweep_table_path_matches_direct_paths_and_oracle(dims, D, k1, lik, P, W
         so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
         for got in states:
             assert_state_close(got, want, cfg, RTOL, what="dims=%s mode %d" % (dims, dim))
+
+
+@pytest.mark.parametrize("dims,D,lik,P,W", [
+    ([6, 5, 4], 20, "bernoulli", 4, 64),      # config 2's kernel instance (NT = 3, ones row)
+    ([5, 4, 4], 32, "normal", 5, 3),          # config 5's (NT = 4), segments of 3 entries
+    ([4, 3, 3, 3], 10, "normal", 3, 64),      # config 1's rank, three other modes
+    ([40, 3, 3], 12, "poisson", 1, 200),      # chunks longer than 128 entries
+    ([7, 9], 7, "bernoulli", 2, 4),           # one other mode, odd rank
+])
+def test_sweep_float_table_is_within_the_fp32_tolerance(dims, D, lik, P, W, capsys):
+    """SSVI_TABLE_F32 (the contract's fp32 option): the sample table of the sweep path stored as floats, arithmetic in
+    fp64.  Updated means / covariances / optimiser state must agree with the oracle within 1e-4 (BASELINE.json's fp32
+    bar); the accumulator records are compared with the double table's to show the actual deviation (~1e-7)."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(D * 77 + P)
+    N = len(dims)
+    cfg = so.make_config("d", lik, D, diag=False, k1=64, k2=4, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, lik, dims, int(0.8 * np.prod(dims)))
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    pool = so.make_tape(rng, cfg, N, P)
+    worst = 0.0
+    for dim in range(N):
+        n = dims[dim]
+        accs, states = [], []
+        for tdt in (torch.float64, torch.float32):
+            eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, sweep_chunk_entries=W,
+                         table_budget_bytes=1, table_dtype=tdt)
+            eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=False))
+            engine_load_state(eng, st0)
+            plan = eng.plan_sweep(dim)
+            if tdt == torch.float32:
+                assert plan.table_bytes * 2 == table_bytes64          # half the table
+            else:
+                table_bytes64 = plan.table_bytes
+            accs.append(eng.accumulate(plan).cpu().numpy().copy())
+            eng.row_update(plan, eng.accumulate(plan))
+            eng.check_flags()
+            states.append(engine_dump_state(eng, st0))
+            eng.close()
+        scale = np.abs(accs[0]).max()
+        dev = np.abs(accs[1] - accs[0]).max() / scale
+        worst = max(worst, dev)
+        assert dev < 2e-6, dev
+        np.testing.assert_array_equal(accs[1][:, -1], accs[0][:, -1])              # counts: bit-exact
+        entries, tapes = [], []
+        for row in range(n):
+            ids = perm[dim][rowptr[dim][row]:rowptr[dim][row + 1]]
+            sl = np.arange(len(ids)) % P
+            tapes.append(so.Tape(pool.z_other[sl], pool.z_own[sl], pool.r_w[sl], pool.z_f[sl]))
+            entries.append((coords[ids], vals[ids]))
+        want = so.copy_state(st0)
+        so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
+        assert_state_close(states[1], want, cfg, 1e-4, what="float table, dims=%s mode %d" % (dims, dim))
+    with capsys.disabled():
+        print("\n  float table vs double table, largest accumulator deviation / max |acc|: %.2e (dims %s, D %d)" % (worst, dims, D))
 
 
 @pytest.mark.parametrize("dims,D,lik,P,W,nb,offs,model", [

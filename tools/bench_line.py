@@ -4,7 +4,7 @@ import json
 import sys
 
 try:
-    d = json.load(open(sys.argv[1]))
+    d = json.loads([ln for ln in open(sys.argv[1]) if ln.startswith("{")][-1])      # NCCL prints its version first
 except Exception as e:                                      # noqa: BLE001
     print("  no JSON line:", e)
     sys.exit(0)
