@@ -326,6 +326,24 @@ int64_t ssvi_loop_workspace_bytes(const SsviHandle* h, int32_t batch_size);
 int ssvi_factorize_iterations(SsviHandle* h, SsviLoop* loop /*HOST*/, int64_t first_iteration, int64_t n_iterations,
                               void* stream);
 
+/* Stages 1-3 + the in-order chunk reduction in ONE call that needs no workspace and allocates nothing.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  Equivalent to
+ *   ssvi_accumulate(h, dim, n_chunks, ..., partial, stream);  ssvi_reduce_chunks(h, n_rows, row_chunk_ptr, partial, acc_out, stream);
+ * with `partial` -- n_chunks records of ssvi_acc_len doubles -- held in a file-scope static device array of
+ * SSVI_STATIC_SCRATCH_BYTES (8 MiB; every GPU that loads the library holds it until the process exits) instead of a
+ * caller buffer.  Inputs and the output acc_out [n_rows][ssvi_acc_len] are the caller's, as for the two calls above.
+ * Fails with SSVI_E_INVALID and a message naming both sizes when n_chunks * ssvi_acc_len * 8 exceeds the maximum.
+ * Calls no cudaMalloc / cudaFree / allocating library routine.  All calls on a GPU share the one array, which keeps
+ * the previous call's contents (nothing in it needs clearing: every chunk record is written in full before it is
+ * read); calls that overlap on the GPU -- other streams, handles or host threads -- RACE on it: serialise them. */
+#define SSVI_STATIC_SCRATCH_BYTES (8u << 20)
+int64_t ssvi_static_scratch_bytes(void);
+int ssvi_accumulate_rows_static(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t* chunk_row,
+                                const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot0,
+                                const int64_t* entry_ids, const int64_t* rows, const double* w_state, int64_t n_rows,
+                                const int64_t* row_chunk_ptr, double* acc_out, void* stream);
+
 /* Reads and clears the device flag word (synchronises `stream`).  flags_out HOST. */
 int ssvi_check_flags(SsviHandle* h, int32_t* flags_out /*HOST*/, void* stream);
 

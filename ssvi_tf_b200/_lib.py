@@ -88,6 +88,8 @@ SIGNATURES = {
     "ssvi_fill_noise": (ctypes.c_int, [_P, _P, _P, _P, _P, _I32, ctypes.c_uint64, ctypes.c_uint64, _P]),
     "ssvi_loop_workspace_bytes": (_I64, [_P, _I32]),
     "ssvi_factorize_iterations": (ctypes.c_int, [_P, ctypes.POINTER(SsviLoop), _I64, _I64, _P]),
+    "ssvi_static_scratch_bytes": (_I64, []),
+    "ssvi_accumulate_rows_static": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),
     "ssvi_check_flags": (ctypes.c_int, [_P, ctypes.POINTER(_I32), _P]),
 }
 

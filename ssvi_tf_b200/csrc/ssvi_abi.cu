@@ -1070,3 +1070,53 @@ extern "C" int ssvi_factorize_iterations(SsviHandle* h, SsviLoop* lp, int64_t fi
   if (rc == SSVI_OK) CUDA_TRY(h, cudaGetLastError());
   return rc;
 }
+
+// ---- stages 1-3 + chunk reduction with NO caller workspace and NO allocation -------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  ssvi_accumulate needs a
+// scratch buffer of n_chunks chunk records (`partial_out`) that ssvi_reduce_chunks then folds into the row accumulators;
+// here that scratch is a file-scope device array of SSVI_STATIC_SCRATCH_BYTES (every GPU that loads the library holds
+// it until the process exits).  In HOST code the array's name is only a stand-in for the symbol, not a device address:
+// the address is taken with cudaGetSymbolAddress once per device, with that device current, and passed to the kernels.
+// Every call shares the array and it keeps the last call's contents; nothing in it has to start at zero, because
+// every accumulate kernel writes each chunk record in full before reduce_chunks_kernel reads it.  Two calls that
+// overlap on one GPU (different streams, or different handles / host threads) race on it.
+static __device__ __align__(256) double g_static_scratch[SSVI_STATIC_SCRATCH_BYTES / sizeof(double)];
+#define SSVI_MAX_DEVICES 64
+static double* g_static_scratch_ptr[SSVI_MAX_DEVICES];   // per device, filled on the first call made with it current
+
+extern "C" int64_t ssvi_static_scratch_bytes(void) { return (int64_t)SSVI_STATIC_SCRATCH_BYTES; }
+
+extern "C" int ssvi_accumulate_rows_static(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_t* chunk_row,
+                                           const int64_t* chunk_start, const int32_t* chunk_len,
+                                           const int32_t* chunk_slot0, const int64_t* entry_ids, const int64_t* rows,
+                                           const double* w_state, int64_t n_rows, const int64_t* row_chunk_ptr,
+                                           double* acc_out, void* stream) {
+  if (!h) return SSVI_E_INVALID;
+  if (n_rows < 0 || n_chunks < 0) return fail(h, SSVI_E_INVALID, "accumulate_rows_static: negative count%s");
+  if (n_rows == 0) return SSVI_OK;
+  if (!row_chunk_ptr || !acc_out) return fail(h, SSVI_E_INVALID, "accumulate_rows_static: null pointer%s");
+  const int64_t need = n_chunks * h->acc_len * (int64_t)sizeof(double);
+  if (need > (int64_t)SSVI_STATIC_SCRATCH_BYTES) {
+    char msg[160];
+    snprintf(msg, sizeof(msg), "%lld chunk records of %lld doubles need %lld bytes, the static scratch holds %lld",
+             (long long)n_chunks, (long long)h->acc_len, (long long)need, (long long)SSVI_STATIC_SCRATCH_BYTES);
+    return fail(h, SSVI_E_INVALID, "accumulate_rows_static: %s (use ssvi_accumulate with a caller workspace)", msg);
+  }
+  int dev = -1;
+  CUDA_TRY(h, cudaGetDevice(&dev));
+  if (dev < 0 || dev >= SSVI_MAX_DEVICES) return fail(h, SSVI_E_INVALID, "accumulate_rows_static: device ordinal out of range%s");
+  if (!g_static_scratch_ptr[dev]) {                     // set-up, once per device, with that device current
+    double* p = nullptr;
+    CUDA_TRY(h, cudaGetSymbolAddress((void**)&p, g_static_scratch));
+    if (!p) return fail(h, SSVI_E_CUDA, "accumulate_rows_static: cudaGetSymbolAddress returned a null address%s");
+    g_static_scratch_ptr[dev] = p;
+  }
+  double* scratch = g_static_scratch_ptr[dev];
+  if (n_chunks > 0) {
+    const int rc = ssvi_accumulate(h, dim, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot0, entry_ids, rows,
+                                   w_state, scratch, stream);
+    if (rc != SSVI_OK) return rc;
+  }
+  return ssvi_reduce_chunks(h, n_rows, row_chunk_ptr, scratch, acc_out, stream);
+}
