@@ -65,6 +65,10 @@ SIDE_RUNS = [
     ("c3", "c3", 0.25, {}),
     ("c3_quadrature", "c3", 0.25, {"quadrature": 30}),
     ("c4", "c4", 1.0, {}),
+    # ranks above 32 with a full covariance (the reference's real-data default is rank 50, real_test.py:27): C2's tensor at
+    # D = 50 through accumulate_wide.cuh, and the generic CUDA-core kernel it replaces there (on 5 % of the entries)
+    ("c2_rank50", "c2", 1.0, {"rank": 50}),
+    ("c2_rank50_generic_kernel", "c2", 0.05, {"rank": 50, "kernel_path": 1}),
     # the contract's fp32 option on the headline workload: sample table stored as floats (arithmetic stays fp64)
     ("c5_table_f32", "c5", 1.0, {"table_f32": True}),
 ]
@@ -279,10 +283,12 @@ def hbm_peak():
 # ------------------------------------------------------------------------------------------------
 class Workload(object):
     def __init__(self, args, cfg_id, c, device, rank, world, group, scale=1.0, batch_size=None, quadrature=None,
-                 sharded=False, table_f32=False):
+                 sharded=False, table_f32=False, factor_rank=None, kernel_path=0):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
+        if factor_rank:
+            c = dict(c, D=int(factor_rank), desc=c["desc"].replace("D=%d" % c["D"], "D=%d" % int(factor_rank)))
         self.args, self.cfg_id, self.c = args, cfg_id, c
         self.device, self.rank, self.world, self.group = device, rank, world, group
         self.B = batch_size
@@ -301,7 +307,8 @@ class Workload(object):
                                  dict(table_budget_bytes=int(args.table_mb * (1 << 20)),
                                       sweep_chunk_entries=args.sweep_chunk, sweep_streams=args.sweep_streams,
                                       sweep_tile_blocks=args.tile_blocks, tuning=args.tuning,
-                                      table_dtype=torch.float32 if table_f32 else torch.float64),
+                                      table_dtype=torch.float32 if table_f32 else torch.float64,
+                                      kernel_path=kernel_path),
                                  quadrature=quadrature)
         self.eng = self.model.engine
         self.N = self.model.order
@@ -406,6 +413,8 @@ class Workload(object):
         if c["diag"]:
             return "accumulate_diag_lin_kernel" if c["model"] == "simple" and c["lik"] == "normal" else \
                 ("accumulate_diag_d_kernel" if c["model"] == "d" else "accumulate_diag_kernel")
+        if c["D"] > 32:
+            return "accumulate_wide_kernel (+ sample_table_wide_kernel)"
         return "accumulate_memo_kernel (+ sample_table_kernel)" if c["model"] == "d" else \
             "memo_weights_kernel (+ memo_f / memo_c / sample_table kernels)"
 
@@ -745,7 +754,9 @@ def main():
             t0 = time.time()
             try:
                 w2 = Workload(args, cid, cc, device, 0, 1, None, scale=scale, batch_size=opt.get("batch_size"),
-                              quadrature=opt.get("quadrature"), table_f32=opt.get("table_f32", False))
+                              quadrature=opt.get("quadrature"), table_f32=opt.get("table_f32", False),
+                              factor_rank=opt.get("rank"), kernel_path=opt.get("kernel_path", 0))
+                cc = w2.c
                 r2 = w2.run_resident(2 * Nm, Nm)
                 side[key] = {"workload": cc["desc"] + (" at %.3g of its nnz" % scale if scale != 1.0 else ""),
                              "schedule": ("reference minibatches: every row takes <= %d entries drawn on the device each "

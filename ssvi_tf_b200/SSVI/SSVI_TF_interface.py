@@ -308,8 +308,8 @@ class SSVI_TF(TrueModelMixin):
             self._warned_direct_sweep = True
             import warnings
             warnings.warn("sweep(): this configuration is outside the slot-major sweep kernels (full covariance needs "
-                          "rank <= 32 and k1 == 64, diagonal covariance rank <= 64 and k1 a multiple of 16 up to 64, order "
-                          "<= 4); the direct / generic kernels run instead, several times slower (DESIGN.md 3)")
+                          "k1 == 64 and rank <= 32, or rank <= 64 for SSVI_TF_d; diagonal covariance rank <= 64 and k1 a "
+                          "multiple of 16 up to 64; order <= 4); the direct / generic kernels run instead, several times slower (DESIGN.md 3)")
         plan = eng.plan_sweep(dim, off) if eng.sweep_supported else eng.plan_full(dim, None, off)
         return plan, n_obs
 

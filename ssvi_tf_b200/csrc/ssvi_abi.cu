@@ -4,6 +4,7 @@
 #include <new>
 
 #include "accumulate_memo2.cuh"
+#include "accumulate_wide.cuh"
 #include "accumulate_diag.cuh"
 #include "estimate.cuh"
 #include "row_update.cuh"
@@ -297,12 +298,14 @@ static bool sweep_diag_ok(const SsviConfig& c, int max_smem) {
          diag_cta_smem(c.order, c.rank, c.k1) <= (size_t)max_smem;
 }
 static bool sweep_full_ok(const SsviConfig& c) {
-  return c.cov_kind == SSVI_COV_FULL && c.rank <= 32 && c.k1 == 8 * SSVI_MEMO_KT && c.order >= 2 &&
-         c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
+  // rank <= 32: one warp holds an entry's whole contraction (accumulate_memo*.cuh, every model); 32 < rank <= 64: the
+  // contraction split over the CTA's warps (accumulate_wide.cuh, SSVI_TF_d)
+  return c.cov_kind == SSVI_COV_FULL && (c.rank <= 32 || (c.rank <= 64 && c.model == SSVI_MODEL_D)) &&
+         c.k1 == 8 * SSVI_MEMO_KT && c.order >= 2 && c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
 }
 // the float table is built for the kernels of SSVI_TF_d (the three-pass path of simple / robust keeps doubles)
 static bool table_f32(const SsviConfig& c) {
-  return c.table_dtype == SSVI_TABLE_F32 && c.model == SSVI_MODEL_D && c.cov_kind == SSVI_COV_FULL;
+  return c.table_dtype == SSVI_TABLE_F32 && c.model == SSVI_MODEL_D && c.cov_kind == SSVI_COV_FULL && c.rank <= 32;
 }
 static bool sweep_ok(const SsviHandle* h) { return sweep_full_ok(h->cfg) || sweep_diag_ok(h->cfg, h->max_smem_optin); }
 
@@ -410,6 +413,47 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
   }
 #undef SSVI_MEMO_LAUNCH
 #undef SSVI_MEMO_LAUNCH_K
+  CUDA_TRY(h, cudaGetLastError());
+  return SSVI_OK;
+}
+
+template <typename ZT>
+static int launch_sweep_wide(SsviHandle* h, const DevView& v, const MemoView& mv, int nt, int64_t n_chunks,
+                             const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
+                             const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
+                             const int64_t* rows, double* partial_out, cudaStream_t st) {
+  {
+    const size_t smem = (size_t)sample_table_wide_smem(v.D, v.k1);
+    auto kern = sample_table_wide_kernel<ZT>;
+    CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)mv.blk_base[mv.n_oth], 128, smem, st>>>(v, mv, (const ZT*)h->z_other);
+    CUDA_TRY(h, cudaGetLastError());
+  }
+  if (n_chunks == 0) return SSVI_OK;
+  const int z_f32 = sizeof(ZT) == 4;
+  const size_t smem = (size_t)wide_cta_smem(nt, v.D);
+  if (smem > (size_t)h->max_smem_optin) return fail(h, SSVI_E_INVALID, "sweep_accumulate: shared memory%s");
+#define SSVI_WIDE_LAUNCH(NT_, NOTH_)                                                                               \
+  do {                                                                                                             \
+    auto kern = accumulate_wide_kernel<NT_, NOTH_>;                                                                \
+    CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));               \
+    kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot,    \
+                                                chunk_out, entry_ids, rows, h->z_own, z_f32, partial_out);         \
+  } while (0)
+#define SSVI_WIDE_NT(NT_)                                                                                          \
+  switch (mv.n_oth) {                                                                                              \
+    case 1: SSVI_WIDE_LAUNCH(NT_, 1); break;                                                                       \
+    case 2: SSVI_WIDE_LAUNCH(NT_, 2); break;                                                                       \
+    default: SSVI_WIDE_LAUNCH(NT_, 3); break;                                                                      \
+  }
+  switch (nt) {
+    case 5: SSVI_WIDE_NT(5) break;
+    case 6: SSVI_WIDE_NT(6) break;
+    case 7: SSVI_WIDE_NT(7) break;
+    default: SSVI_WIDE_NT(8) break;
+  }
+#undef SSVI_WIDE_NT
+#undef SSVI_WIDE_LAUNCH
   CUDA_TRY(h, cudaGetLastError());
   return SSVI_OK;
 }
@@ -536,6 +580,19 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
   cudaStream_t st = (cudaStream_t)stream;
 #define SSVI_SWEEP_ARGS h, v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, partial_out, w_state, wk, st
   const int nt = (v.D + 7) / 8;
+  if (nt > 4) {                                         // 32 < rank <= 64: accumulate_wide.cuh (4 table rows per CTA)
+    int64_t blocks = 0;
+    for (int a = 0; a < mv.n_oth; ++a) {
+      mv.blk_base[a] = blocks;
+      blocks += ((mv.n_rows[a] + 3) / 4) * (int64_t)n_slots;
+    }
+    mv.blk_base[mv.n_oth] = blocks;
+    if (h->cfg.noise_dtype == SSVI_NOISE_F32)
+      return launch_sweep_wide<float>(h, v, mv, nt, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
+                                      entry_ids, rows, partial_out, st);
+    return launch_sweep_wide<double>(h, v, mv, nt, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
+                                     entry_ids, rows, partial_out, st);
+  }
   if (h->cfg.noise_dtype == SSVI_NOISE_F32) {
     switch (nt) {
       case 1: return launch_sweep<1, float>(SSVI_SWEEP_ARGS);

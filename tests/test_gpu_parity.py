@@ -188,6 +188,12 @@ def test_mma_path_matches_oracle_and_generic(D, k1, model, lik):
     ([7, 9], 7, 64, "bernoulli", 2, 4, False, "d"),          # matrix: one other mode
     ([4, 3, 3, 3], 10, 64, "normal", 3, 64, False, "d"),     # 4-way: three other modes (config 1's NT=2)
     ([40, 3, 3], 20, 64, "normal", 1, 200, False, "d"),      # one slot, chunks longer than 128 entries
+    # 32 < D <= 64 (accumulate_wide.cuh: the contraction split over the CTA's warps); the reference's real-data rank is 50
+    ([6, 5, 4], 50, 64, "bernoulli", 3, 64, False, "d"),     # NT = 7 (odd: warp 0 owns one tile row, the others two)
+    ([5, 4, 4], 64, 64, "normal", 2, 3, True, "d"),          # NT = 8, every lane a live row, segments of 3, shifted slots
+    ([7, 9], 40, 64, "poisson", 2, 5, False, "d"),           # NT = 5, one other mode
+    ([4, 3, 3, 3], 33, 64, "normal", 2, 64, False, "d"),     # NT = 5 with 7 padding rows, three other modes
+    ([40, 3, 3], 48, 64, "normal", 1, 200, False, "d"),      # NT = 6, chunks longer than 32 entries (second index batch)
     ([5, 4, 4], 30, 64, "poisson", 4, 64, False, "robust"),  # BASELINE config 3's kernel instances (three-pass path)
     ([6, 5, 4], 20, 64, "bernoulli", 3, 3, True, "robust"),
     ([6, 5, 4], 12, 64, "normal", 2, 64, False, "simple"),

@@ -8,6 +8,7 @@
 #   "bench <name> <args>"      python bench.py <args>                      -> <tag>_bench_<name>.json
 #   "dist <n> <name> <args>"   torchrun --nproc-per-node n bench.py --gpus n <args>
 #   "launches <name> <skip> <count> <cmd...>"   ncu launch list of <cmd> (run plain first)  -> <tag>_launches_<name>.csv + summary
+#   "klaunches <name> <kernel regex> <skip> <count> <cmd...>"   the same, counting only kernels whose name matches
 #   "ncu <name> <kernel regex> <skip> <count> <cmd...>"   ncu --set full with source of the matching kernel, exported to
 #                              CSV pages on the box (tools/ncu_export.sh; gpurun_out/ is capped at 64 MiB)
 #   "factorize [env...]"       tools/factorize_timing.py
@@ -29,6 +30,11 @@ for step in "$@"; do
           timeout 900 "$@" > $OUT/${TAG}_plain_$name.log 2>&1 &&
           timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s $skip -c $count --csv \
             --log-file $OUT/${TAG}_launches_$name.csv "$@" > $OUT/${TAG}_ncu_$name.log 2>&1; echo "launches $name rc=$?"
+          python tools/launch_summary.py $OUT/${TAG}_launches_$name.csv | tee $OUT/${TAG}_launches_${name}_summary.txt | head -14;;
+    klaunches) name=$1; regex=$2; skip=$3; count=$4; shift 4       # launch list restricted to kernels matching <regex>
+          timeout 900 "$@" > $OUT/${TAG}_plain_$name.log 2>&1 &&
+          timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:$regex -s $skip -c $count --csv \
+            --log-file $OUT/${TAG}_launches_$name.csv "$@" > $OUT/${TAG}_ncu_$name.log 2>&1; echo "klaunches $name rc=$?"
           python tools/launch_summary.py $OUT/${TAG}_launches_$name.csv | tee $OUT/${TAG}_launches_${name}_summary.txt | head -14;;
     ncu) name=$1; regex=$2; skip=$3; count=$4; shift 4
           timeout 900 "$@" > $OUT/${TAG}_plain_$name.log 2>&1 &&
