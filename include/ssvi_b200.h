@@ -55,7 +55,12 @@ enum { SSVI_NOISE_F64 = 0, SSVI_NOISE_F32 = 1 };
  * direct kernels compute.  F32: they are rounded to float when they are written (relative 6e-8) and widened again when
  * read; every sum, product and likelihood term is still fp64.  Halves the bytes a sweep gathers.  The fp32 option of
  * the contract (tolerance 1e-4); measured deviation of the updated rows from the F64 table: see DESIGN.md 3.5. */
-enum { SSVI_TABLE_F64 = 0, SSVI_TABLE_F32 = 1 };
+enum { SSVI_TABLE_F64 = 0, SSVI_TABLE_F32 = 1, SSVI_TABLE_F32_TC = 2 };
+/* F32_TC: the fp32 ARITHMETIC option (tolerance 1e-4).  Float table in the tensor-core path's lane order; V, f and the row
+ * sums are formed in fp32, the contraction G = SUM_b w_b V_b V_b^T (SSVI_TF_d.py:47-56) runs on the tcgen05 tensor cores
+ * (V split into two fp16 pieces scaled by 2^tc_scale_log2, hi hi^T + hi lo^T + lo hi^T accumulated in fp32 in tensor
+ * memory: csrc/accumulate_tc.cuh); likelihood derivatives, chunk records and everything from stage 3 on stay fp64.
+ * SSVI_TF_d, full covariance, rank <= 32, k1 == 64; other configurations treat it as SSVI_TABLE_F32 / F64. */
 
 enum {
   SSVI_OK = 0,
@@ -70,7 +75,9 @@ enum {
   SSVI_FLAG_NONFINITE_COV = 2,   /* S_next not finite           (SSVI_TF_interface.py:202-204) */
   SSVI_FLAG_PHI_ZERO = 4,        /* phi == 0 or not finite      (SSVI_TF_robust.py:87-92, 106) */
   SSVI_FLAG_CHOL_FAIL = 8,       /* covariance not positive definite in the sampler refresh     */
-  SSVI_FLAG_EIG_NOCONV = 16      /* Jacobi eigen-iteration hit its sweep limit                  */
+  SSVI_FLAG_EIG_NOCONV = 16,     /* Jacobi eigen-iteration hit its sweep limit                  */
+  SSVI_FLAG_TC_RANGE = 32        /* SSVI_TABLE_F32_TC: an operand left the fp16 range (|2^tc_scale_log2 V| > 65504); lower
+                                    cfg.tc_scale_log2 or use the fp64 path */
 };
 
 /* Constructor kwargs + hidden constants of SSVI_TF.__init__ (SSVI_TF_interface.py:21-98). */
@@ -88,7 +95,7 @@ typedef struct SsviConfig {
   int32_t kernel_path;      /* 0 = auto; 1 = force the generic CUDA-core accumulate path (testing)  */
   int32_t tuning;           /* bit set of SSVI_TUNE_* kernel options (0 = defaults); results do not depend on it */
   int32_t table_dtype;      /* SSVI_TABLE_*: element type of the sweep path's sample table (SSVI_TF_d, full covariance) */
-  int32_t reserved2;
+  int32_t tc_scale_log2;    /* SSVI_TABLE_F32_TC: log2 of the operand scale of the fp16 split; 0 = default (6) */
   double eta;               /* (:85)  */
   double cov_eta;           /* (:86)  */
   double sigma_eta;         /* (:88)  */

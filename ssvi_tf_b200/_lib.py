@@ -17,11 +17,11 @@ MODEL_D, MODEL_SIMPLE, MODEL_ROBUST = 0, 1, 2
 LIK_NORMAL, LIK_BERNOULLI, LIK_POISSON = 0, 1, 2
 UPDATE_S, UPDATE_N = 0, 1
 NOISE_F64, NOISE_F32 = 0, 1
-TABLE_F64, TABLE_F32 = 0, 1
+TABLE_F64, TABLE_F32, TABLE_F32_TC = 0, 1, 2
 
 TUNE_L2_PREFETCH, TUNE_LIN, TUNE_PF2, TUNE_PF3 = 1, 2, 4, 8
 
-FLAG_NONFINITE_ACC, FLAG_NONFINITE_COV, FLAG_PHI_ZERO, FLAG_CHOL_FAIL, FLAG_EIG_NOCONV = 1, 2, 4, 8, 16
+FLAG_NONFINITE_ACC, FLAG_NONFINITE_COV, FLAG_PHI_ZERO, FLAG_CHOL_FAIL, FLAG_EIG_NOCONV, FLAG_TC_RANGE = 1, 2, 4, 8, 16, 32
 
 
 class SsviConfig(ctypes.Structure):
@@ -29,7 +29,7 @@ class SsviConfig(ctypes.Structure):
         ("order", ctypes.c_int32), ("rank", ctypes.c_int32), ("cov_kind", ctypes.c_int32),
         ("model", ctypes.c_int32), ("likelihood", ctypes.c_int32), ("k1", ctypes.c_int32),
         ("k2", ctypes.c_int32), ("mean_update", ctypes.c_int32), ("cov_update", ctypes.c_int32),
-        ("noise_dtype", ctypes.c_int32), ("kernel_path", ctypes.c_int32), ("tuning", ctypes.c_int32), ("table_dtype", ctypes.c_int32), ("reserved2", ctypes.c_int32),
+        ("noise_dtype", ctypes.c_int32), ("kernel_path", ctypes.c_int32), ("tuning", ctypes.c_int32), ("table_dtype", ctypes.c_int32), ("tc_scale_log2", ctypes.c_int32),
         ("eta", ctypes.c_double), ("cov_eta", ctypes.c_double), ("sigma_eta", ctypes.c_double),
         ("poisson_eta", ctypes.c_double), ("min_eigenval", ctypes.c_double), ("cov_floor", ctypes.c_double),
         ("likelihood_param", ctypes.c_double), ("dims", ctypes.c_int64 * MAX_ORDER),

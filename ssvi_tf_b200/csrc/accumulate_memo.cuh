@@ -18,6 +18,7 @@
 // double2 per lane, i.e. a table record is [NT][KT][32] double2 and a warp reads a tile as 512 contiguous bytes.
 #pragma once
 #include "accumulate_mma.cuh"
+#include "tc_ops.cuh"
 
 #define SSVI_MEMO_MAX_OTH 3
 
@@ -25,7 +26,9 @@ struct MemoView {
   int32_t n_oth;                          // N - 1
   int32_t rec_len;                        // doubles per table record = NT * KT * 64
   int32_t slot_lo, n_slots;               // slots [slot_lo, slot_lo + n_slots) are in the table
-  int32_t tab32;                          // records hold FLOATS: [NT][KT/2][32] float4 = (x, y of k-tile 2p | x, y of 2p+1)
+  int32_t tab32;                          // 1: records hold FLOATS: [NT][KT/2][32] float4 = (x, y of k-tile 2p | x, y of 2p+1)
+                                          // 2: floats in the tensor-core path's order (tc_rec_index, tc_ops.cuh)
+  float tc_alpha;                         // tab32 == 2: power-of-two operand scale of the fp16 hi / lo split
   int32_t od[SSVI_MEMO_MAX_OTH];          // other modes, ascending
   int64_t n_rows[SSVI_MEMO_MAX_OTH];      // rows of each other mode
   int64_t rec_base[SSVI_MEMO_MAX_OTH + 1];// first record of each other mode's block; [n_oth] = total records
@@ -87,6 +90,17 @@ __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView m
   // Padding rows (n >= D) come out as exact zeros (zero mean, zero factor rows); row n == D is set to ONE so that the
   // contraction V V^T of the accumulate kernel also delivers the row sums sum_k V[n][k] (its row D) for free.
   const int64_t rec = memo_rec(mv, jj, sl, j);
+  if (mv.tab32 == 2) {                                  // SSVI_TABLE_F32_TC: lane (g, q) holds x[8i + g][8t + 2q + {0,1}]
+    float* out = reinterpret_cast<float*>(mv.tab) + rec * (int64_t)(NT * 8 * 64);
+#pragma unroll
+    for (int i = 0; i < NT; ++i)
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (t < KT)
+          *reinterpret_cast<float2*>(out + tc_rec_index(8 * i + g, 8 * t + 2 * (lane & 3))) =
+              make_float2((float)vv[i][t][0], (float)vv[i][t][1]);
+    return;
+  }
   if (mv.tab32) {                                       // SSVI_TABLE_F32: half the bytes, two k-tiles per 16-byte load
     float4* out = reinterpret_cast<float4*>(mv.tab) + rec * (int64_t)(NT * (KT >> 1) * 32);
 #pragma unroll

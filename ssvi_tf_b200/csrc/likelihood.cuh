@@ -91,11 +91,11 @@ __device__ __forceinline__ double exp_nonpos(double x) {
   return __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
 }
 
-__constant__ double SSVI_EXPC[14] = {1.0, 1.0, 0.5, 1.0 / 6.0, 1.0 / 24.0, 1.0 / 120.0, 1.0 / 720.0, 1.0 / 5040.0,
+static __constant__ double SSVI_EXPC[14] = {1.0, 1.0, 0.5, 1.0 / 6.0, 1.0 / 24.0, 1.0 / 120.0, 1.0 / 720.0, 1.0 / 5040.0,
                                      1.0 / 40320.0, 1.0 / 362880.0, 1.0 / 3628800.0, 1.0 / 39916800.0,
                                      1.0 / 479001600.0, 1.0 / 6227020800.0};
 // [0..9]: 2/(2n+3), n = 0..9 (atanh series of log);  [10] = ln 2,  [11] = sqrt 2,  [12] = log2(e),  [13] = magic 1.5*2^52
-__constant__ double SSVI_LOGC[16] = {2.0 / 3.0,  2.0 / 5.0,  2.0 / 7.0,  2.0 / 9.0,  2.0 / 11.0, 2.0 / 13.0,
+static __constant__ double SSVI_LOGC[16] = {2.0 / 3.0,  2.0 / 5.0,  2.0 / 7.0,  2.0 / 9.0,  2.0 / 11.0, 2.0 / 13.0,
                                      2.0 / 15.0, 2.0 / 17.0, 2.0 / 19.0, 2.0 / 21.0, 6.93147180559945286227e-01,
                                      1.41421356237309514547e+00, 1.4426950408889634, 6755399441055744.0,
                                      -6.93147180369123816490e-01, -1.90821492927058770002e-10};

@@ -8,6 +8,7 @@
 #include "accumulate_diag.cuh"
 #include "estimate.cuh"
 #include "row_update.cuh"
+#include "tc_sweep.cuh"
 
 #define SSVI_VERSION_STR "ssvi_b200 0.1 sm_100a"
 
@@ -64,7 +65,9 @@ extern "C" int ssvi_create(const SsviConfig* cfg, SsviHandle** out) {
   if (cfg->mean_update != SSVI_UPDATE_S && cfg->mean_update != SSVI_UPDATE_N) return fail(nullptr, SSVI_E_INVALID, "Unidentified update formula for mean param%s");
   if (cfg->cov_update != SSVI_UPDATE_S && cfg->cov_update != SSVI_UPDATE_N) return fail(nullptr, SSVI_E_INVALID, "Unidentified update formula for covariance param%s");
   if (cfg->noise_dtype != SSVI_NOISE_F64 && cfg->noise_dtype != SSVI_NOISE_F32) return fail(nullptr, SSVI_E_INVALID, "bad noise_dtype%s");
-  if (cfg->table_dtype != SSVI_TABLE_F64 && cfg->table_dtype != SSVI_TABLE_F32) return fail(nullptr, SSVI_E_INVALID, "bad table_dtype%s");
+  if (cfg->table_dtype != SSVI_TABLE_F64 && cfg->table_dtype != SSVI_TABLE_F32 && cfg->table_dtype != SSVI_TABLE_F32_TC)
+    return fail(nullptr, SSVI_E_INVALID, "bad table_dtype%s");
+  if (cfg->tc_scale_log2 < -14 || cfg->tc_scale_log2 > 14) return fail(nullptr, SSVI_E_INVALID, "tc_scale_log2 outside [-14, 14]%s");
   for (int d = 0; d < cfg->order; ++d)
     if (cfg->dims[d] < 1) return fail(nullptr, SSVI_E_INVALID, "dims must be >= 1%s");
   int ndev = 0;
@@ -305,8 +308,11 @@ static bool sweep_full_ok(const SsviConfig& c) {
 }
 // the float table is built for the kernels of SSVI_TF_d (the three-pass path of simple / robust keeps doubles)
 static bool table_f32(const SsviConfig& c) {
-  return c.table_dtype == SSVI_TABLE_F32 && c.model == SSVI_MODEL_D && c.cov_kind == SSVI_COV_FULL && c.rank <= 32;
+  return (c.table_dtype == SSVI_TABLE_F32 || c.table_dtype == SSVI_TABLE_F32_TC) && c.model == SSVI_MODEL_D &&
+         c.cov_kind == SSVI_COV_FULL && c.rank <= 32;
 }
+// ... and in the tensor-core path's order, for accumulate_tc_kernel (fp32 arithmetic, tcgen05 contraction)
+static bool table_tc(const SsviConfig& c) { return table_f32(c) && c.table_dtype == SSVI_TABLE_F32_TC; }
 static bool sweep_ok(const SsviHandle* h) { return sweep_full_ok(h->cfg) || sweep_diag_ok(h->cfg, h->max_smem_optin); }
 
 extern "C" int ssvi_sweep_supported(const SsviHandle* h) { return (h && sweep_ok(h)) ? 1 : 0; }
@@ -382,6 +388,13 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
       CUDA_TRY(h, cudaGetLastError());
       return SSVI_OK;
     }
+  }
+  if (mv.tab32 == 2) {                                  // SSVI_TABLE_F32_TC: tc_sweep.cu
+    const cudaError_t e = (cudaError_t)ssvi_launch_accumulate_tc(v, mv, NT, n_chunks, chunk_row, chunk_start, chunk_len,
+                                                                 chunk_slot, chunk_out, entry_ids, rows, h->z_own, z_f32,
+                                                                 partial_out, st);
+    CUDA_TRY(h, e);
+    return SSVI_OK;
   }
   if (mv.tab32) {                                       // SSVI_TABLE_F32: the base kernel over a float table
     constexpr int MB = (NT <= 3 ? SSVI_MEMO_MINB : 3);
@@ -546,7 +559,8 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
   mv.slot_lo = slot_lo;
   mv.n_slots = n_slots;
   mv.tab = (double*)table_ws;
-  mv.tab32 = table_f32(h->cfg) ? 1 : 0;
+  mv.tab32 = table_tc(h->cfg) ? 2 : (table_f32(h->cfg) ? 1 : 0);
+  mv.tc_alpha = ldexpf(1.f, h->cfg.tc_scale_log2 ? h->cfg.tc_scale_log2 : 6);
   int jj = 0;
   int64_t base = 0, blocks = 0;
   for (int d = 0; d < h->cfg.order; ++d) {

@@ -1,0 +1,38 @@
+// Translation unit of the tcgen05 sweep kernel (SSVI_TABLE_F32_TC): kept apart from ssvi_abi.cu so that the two compile
+// in parallel.  No extern "C" entry point lives here: the kernel is reached through ssvi_sweep_accumulate.
+#include "tc_sweep.cuh"
+#include "accumulate_tc.cuh"
+
+template <int NT, int NOTH>
+static int launch_tc(const DevView& v, const MemoView& mv, int64_t n_chunks, const int32_t* chunk_row,
+                     const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
+                     const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own, int z_f32,
+                     double* partial_out, cudaStream_t st) {
+  auto kern = accumulate_tc_kernel<NT, NOTH>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SSVI_TC_SMEM);
+  if (e != cudaSuccess) return (int)e;
+  kern<<<(unsigned)n_chunks, 128, SSVI_TC_SMEM, st>>>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
+                                                      entry_ids, rows, z_own, z_f32, partial_out);
+  return (int)cudaGetLastError();
+}
+
+int ssvi_launch_accumulate_tc(const DevView& v, const MemoView& mv, int nt, int64_t n_chunks, const int32_t* chunk_row,
+                              const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
+                              const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own,
+                              int z_f32, double* partial_out, cudaStream_t st) {
+#define TC_ARGS v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, z_own, z_f32, partial_out, st
+#define TC_NT(NT_)                                   \
+  switch (mv.n_oth) {                                \
+    case 1: return launch_tc<NT_, 1>(TC_ARGS);       \
+    case 2: return launch_tc<NT_, 2>(TC_ARGS);       \
+    default: return launch_tc<NT_, 3>(TC_ARGS);      \
+  }
+  switch (nt) {
+    case 1: TC_NT(1)
+    case 2: TC_NT(2)
+    case 3: TC_NT(3)
+    default: TC_NT(4)
+  }
+#undef TC_NT
+#undef TC_ARGS
+}

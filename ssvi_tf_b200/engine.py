@@ -19,6 +19,7 @@ FLAG_TEXT = {
     _lib.FLAG_PHI_ZERO: "phi == 0 or not finite (reference asserts SSVI_TF_robust.py:87-92, 106)",
     _lib.FLAG_CHOL_FAIL: "covariance not positive definite",
     _lib.FLAG_EIG_NOCONV: "Jacobi eigen-iteration did not converge",
+    _lib.FLAG_TC_RANGE: "tensor-core sweep (table_dtype='f32_tc'): an operand left the fp16 range; lower tc_scale_log2",
 }
 
 
@@ -161,7 +162,7 @@ class Engine(object):
     def __init__(self, cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float32, chunk_entries=16,
                  kernel_path=0, table_budget_bytes=48 << 20, sweep_chunk_entries=64, sweep_streams=2,
                  sweep_tile_blocks=0, sweep_tile_min_entries=24.0, record_budget_bytes=256 << 20, tuning=0,
-                 table_dtype=torch.float64):
+                 table_dtype=torch.float64, tc_scale_log2=0):
         """cfg: dict with model, likelihood, D, diag, k1, k2, batch_size, mean_update, cov_update, eta,
         cov_eta, sigma_eta (+ hidden constants poisson_eta, min_eigenval, epsilon, likelihood_param)."""
         if not torch.cuda.is_available():
@@ -198,7 +199,10 @@ class Engine(object):
         c.kernel_path = int(kernel_path)      # 0 auto, 1 force the generic CUDA-core accumulate path
         c.tuning = int(tuning)                # SSVI_TUNE_* bits (include/ssvi_b200.h); never changes a result
         # sample table of the sweep path as floats (SSVI_TF_d, full covariance): the contract's fp32 option, tolerance 1e-4
-        c.table_dtype = _lib.TABLE_F32 if table_dtype == torch.float32 else _lib.TABLE_F64
+        # table_dtype="f32_tc": the fp32 ARITHMETIC option, contraction on the tcgen05 tensor cores (accumulate_tc.cuh)
+        c.table_dtype = (_lib.TABLE_F32_TC if table_dtype == "f32_tc"
+                         else _lib.TABLE_F32 if table_dtype == torch.float32 else _lib.TABLE_F64)
+        c.tc_scale_log2 = int(tc_scale_log2)
         self.table_dtype = table_dtype
         c.eta, c.cov_eta, c.sigma_eta = float(cfg["eta"]), float(cfg["cov_eta"]), float(cfg["sigma_eta"])
         c.poisson_eta = float(cfg.get("poisson_eta", 0.1))

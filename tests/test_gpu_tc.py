@@ -1,0 +1,104 @@
+"""GPU: the fp32 ARITHMETIC option of the sweep path (SSVI_TABLE_F32_TC, csrc/accumulate_tc.cuh): V, f and the row sums in
+fp32, the contraction on the tcgen05 tensor cores (fp16 hi / lo split, fp32 accumulation in tensor memory).  Bar:
+BASELINE.json's fp32 tolerance, 1e-4 relative on the updated means / covariances / optimiser state against the oracle;
+counts bit-exact.  The accumulator records are also compared with the all-fp64 sweep to show the actual deviation."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ssvi_oracle as so
+from tests.helpers import (assert_state_close, engine_dump_state, engine_load_state, random_problem, random_state)
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(cfg, dims, coords, vals, st0, pool, dim, W, table_dtype, blocks=0, **kw):
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, sweep_chunk_entries=W,
+                 table_budget_bytes=1, table_dtype=table_dtype, sweep_tile_blocks=blocks, sweep_tile_min_entries=0.0, **kw)
+    eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=False))
+    engine_load_state(eng, st0)
+    plan = eng.plan_sweep(dim)
+    acc = eng.accumulate(plan).cpu().numpy().copy()
+    eng.row_update(plan, eng.accumulate(plan))
+    eng.check_flags()
+    state = engine_dump_state(eng, st0)
+    eng.close()
+    return acc, state, plan
+
+
+@pytest.mark.parametrize("dims,D,lik,P,W", [
+    ([6, 5, 4], 20, "bernoulli", 4, 64),      # config 2's kernel instance (NT = 3)
+    ([5, 4, 4], 32, "normal", 5, 3),          # config 5's (NT = 4), segments of 3 entries (ragged quads)
+    ([4, 3, 3, 3], 10, "normal", 3, 64),      # config 1's rank, three other modes
+    ([40, 3, 3], 12, "poisson", 1, 200),      # chunks longer than 128 entries: the 32-quad batches roll over
+    ([7, 9], 7, "bernoulli", 2, 4),           # one other mode, one row group
+    ([3, 30, 30], 32, "bernoulli", 2, 1000),  # rows of ~360 entries in one chunk: many quads through both buffers
+])
+def test_tensor_core_sweep_is_within_the_fp32_tolerance(dims, D, lik, P, W, capsys):
+    rng = np.random.default_rng(D * 131 + P)
+    N = len(dims)
+    cfg = so.make_config("d", lik, D, diag=False, k1=64, k2=4, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, lik, dims, int(0.8 * np.prod(dims)))
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    pool = so.make_tape(rng, cfg, N, P)
+    worst = 0.0
+    for dim in range(N):
+        n = dims[dim]
+        acc64, _, plan64 = _run(cfg, dims, coords, vals, st0, pool, dim, W, torch.float64)
+        acc_tc, state_tc, plan_tc = _run(cfg, dims, coords, vals, st0, pool, dim, W, "f32_tc")
+        assert plan_tc.table_bytes * 2 == plan64.table_bytes                      # a float table
+        dev = np.abs(acc_tc - acc64).max() / np.abs(acc64).max()
+        worst = max(worst, dev)
+        assert dev < 2e-5, dev
+        np.testing.assert_array_equal(acc_tc[:, -1], acc64[:, -1])                # counts: bit-exact
+        entries, tapes = [], []
+        for row in range(n):
+            ids = perm[dim][rowptr[dim][row]:rowptr[dim][row + 1]]
+            sl = np.arange(len(ids)) % P
+            tapes.append(so.Tape(pool.z_other[sl], pool.z_own[sl], pool.r_w[sl], pool.z_f[sl]))
+            entries.append((coords[ids], vals[ids]))
+        want = so.copy_state(st0)
+        so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
+        assert_state_close(state_tc, want, cfg, 1e-4, what="tensor-core sweep, dims=%s mode %d" % (dims, dim))
+    with capsys.disabled():
+        print("\n  tcgen05 sweep vs fp64 sweep, largest accumulator deviation / max |acc|: %.2e (dims %s, D %d)" % (worst, dims, D))
+
+
+def test_tensor_core_sweep_under_l2_tiling_and_on_an_f32_pool():
+    """The launch-order variants the bench uses at config 5 (L2 tiles, float noise pool) change nothing for this kernel:
+    same entry set, accumulators equal to the untiled run up to summation order."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(7)
+    dims, D, P = [7, 9, 8], 32, 3
+    cfg = so.make_config("d", "normal", D, diag=False, k1=64, k2=4, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, "normal", dims, int(0.7 * np.prod(dims)))
+    st0 = random_state(rng, cfg, dims)
+    pool = so.make_tape(rng, cfg, 3, P)
+    for dim in range(3):
+        a1, _, _ = _run(cfg, dims, coords, vals, st0, pool, dim, 64, "f32_tc")
+        a2, _, _ = _run(cfg, dims, coords, vals, st0, pool, dim, 64, "f32_tc", blocks=2)
+        np.testing.assert_allclose(a2, a1, rtol=0, atol=2e-6 * np.abs(a1).max())
+        np.testing.assert_array_equal(a2[:, -1], a1[:, -1])
+
+
+def test_tensor_core_sweep_flags_an_fp16_overflow():
+    """An operand outside the fp16 window must not pass silently: the chunk record goes non-finite and check_flags raises."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(11)
+    dims, D, P = [5, 4, 4], 16, 2
+    cfg = so.make_config("d", "normal", D, diag=False, k1=64, k2=4, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, "normal", dims, 60)
+    st0 = random_state(rng, cfg, dims)
+    pool = so.make_tape(rng, cfg, 3, P)
+    eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, table_dtype="f32_tc", tc_scale_log2=14)
+    eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=False))
+    engine_load_state(eng, st0)
+    for d in range(3):                                   # samples of magnitude ~30: 2^14 * 30 * 30 is far beyond 65504
+        eng.params[d][:, 0, :] *= 30.0
+    eng.refresh_sampler()
+    eng.accumulate(eng.plan_sweep(0))
+    with pytest.raises(AssertionError, match="fp16 range"):
+        eng.check_flags()
+    eng.close()
