@@ -71,6 +71,9 @@ SIDE_RUNS = [
     ("c2_rank50_generic_kernel", "c2", 0.05, {"rank": 50, "kernel_path": 1}),
     # the contract's fp32 option on the headline workload: sample table stored as floats (arithmetic stays fp64)
     ("c5_table_f32", "c5", 1.0, {"table_f32": True}),
+    # the fp32 ARITHMETIC option (SSVI_TABLE_F32_TC, tolerance 1e-4): V, f in fp32, contraction on the tcgen05 tensor cores
+    ("c5_f32_tensor_core", "c5", 1.0, {"table_tc": True}),
+    ("c2_f32_tensor_core", "c2", 1.0, {"table_tc": True}),
 ]
 
 
@@ -283,7 +286,7 @@ def hbm_peak():
 # ------------------------------------------------------------------------------------------------
 class Workload(object):
     def __init__(self, args, cfg_id, c, device, rank, world, group, scale=1.0, batch_size=None, quadrature=None,
-                 sharded=False, table_f32=False, factor_rank=None, kernel_path=0):
+                 sharded=False, table_f32=False, factor_rank=None, kernel_path=0, table_tc=False):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -307,10 +310,11 @@ class Workload(object):
                                  dict(table_budget_bytes=int(args.table_mb * (1 << 20)),
                                       sweep_chunk_entries=args.sweep_chunk, sweep_streams=args.sweep_streams,
                                       sweep_tile_blocks=args.tile_blocks, tuning=args.tuning,
-                                      table_dtype=torch.float32 if table_f32 else torch.float64,
+                                      table_dtype="f32_tc" if table_tc else (torch.float32 if table_f32 else torch.float64),
                                       kernel_path=kernel_path),
                                  quadrature=quadrature)
         self.eng = self.model.engine
+        self.table_tc = bool(table_tc) and self.eng.sweep_supported and not c["diag"] and c["D"] <= 32 and c["model"] == "d"
         self.N = self.model.order
         n = torch.tensor([self.eng.nnz], device=device, dtype=torch.int64)
         if sharded and world > 1:
@@ -395,8 +399,10 @@ class Workload(object):
                     "launch": "one call of Engine.accumulate = stages 1-3 of one mode sweep on this rank (CUDA events "
                               "around it; a sweep issues one sample-table + one accumulate launch per slot group on "
                               "side streams, profiles/*_launches_*)",
-                    "fp64_pipe": fp64_pipe_stats(c, sum(acc_units) / (sum(acc_ms) * 1e-3)) if self.B is None else None,
-                    "note": "fp64 contract: the FP64 pipe (37 TFLOP/s measured), not HBM, bounds this kernel; DESIGN.md 3.1"}
+                    "fp64_pipe": fp64_pipe_stats(c, sum(acc_units) / (sum(acc_ms) * 1e-3)) if self.B is None and not self.table_tc else None,
+                    "note": ("fp32 arithmetic option (1e-4): contraction on the tcgen05 tensor cores, the table gathers "
+                             "(L2 -> SM) pace the kernel; DESIGN.md 3.8") if self.table_tc else
+                            "fp64 contract: the FP64 pipe (37 TFLOP/s measured), not HBM, bounds this kernel; DESIGN.md 3.1"}
         tr_path = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr_path):          # DRAM bytes per unit from the committed ncu capture of this kernel
             tr = json.load(open(tr_path)).get(self.cfg_id if self.B is None else self.cfg_id + "_b128")
@@ -415,6 +421,8 @@ class Workload(object):
                 ("accumulate_diag_d_kernel" if c["model"] == "d" else "accumulate_diag_kernel")
         if c["D"] > 32:
             return "accumulate_wide_kernel (+ sample_table_wide_kernel)"
+        if self.table_tc:
+            return "accumulate_tc_kernel (tcgen05 contraction; + sample_table_kernel)"
         return "accumulate_memo_kernel (+ sample_table_kernel)" if c["model"] == "d" else \
             "memo_weights_kernel (+ memo_f / memo_c / sample_table kernels)"
 
@@ -689,6 +697,8 @@ def main():
     ap.add_argument("--ab-tunings", default="", help="comma-separated SSVI_TUNE_* values timed after the headline, same "
                                                      "process and plans (details.ab_tunings); diagnostic")
     ap.add_argument("--table-f32", action="store_true", help="headline with the sample table stored as floats (fp32 option)")
+    ap.add_argument("--table-tc", action="store_true", help="headline with the fp32 arithmetic option: tcgen05 contraction (SSVI_TABLE_F32_TC)")
+    ap.add_argument("--tc-scale-log2", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="diagnostic runs only")
     ap.add_argument("--no-configs", action="store_true", help="skip the side measurements of the other configs (N = 1)")
@@ -717,7 +727,7 @@ def main():
         parity = sdist.selfcheck(group, device)
 
     wl = Workload(args, args.config, c, device, rank, world, group, scale=args.scale,
-                  batch_size=args.batch_size or None, sharded=True, table_f32=args.table_f32)
+                  batch_size=args.batch_size or None, sharded=True, table_f32=args.table_f32, table_tc=args.table_tc)
     res = wl.run_resident(args.steps, args.warmup, sample_clocks=True)
     ab = {}
     for t in [int(x) for x in args.ab_tunings.split(",") if x]:
@@ -754,7 +764,7 @@ def main():
             t0 = time.time()
             try:
                 w2 = Workload(args, cid, cc, device, 0, 1, None, scale=scale, batch_size=opt.get("batch_size"),
-                              quadrature=opt.get("quadrature"), table_f32=opt.get("table_f32", False),
+                              quadrature=opt.get("quadrature"), table_f32=opt.get("table_f32", False), table_tc=opt.get("table_tc", False),
                               factor_rank=opt.get("rank"), kernel_path=opt.get("kernel_path", 0))
                 cc = w2.c
                 r2 = w2.run_resident(2 * Nm, Nm)
@@ -763,7 +773,11 @@ def main():
                                           "sweep, scale = len/B" % opt["batch_size"]) if opt.get("batch_size") else
                              "full-row Jacobi sweeps (scale = 1)" + (", 30-node Gauss-Hermite second layer "
                                                                     "(SSVI_TF_robust quadrature=True)" if opt.get("quadrature") else "")
-                             + (", sample table stored as float32 (SSVI_TABLE_F32), arithmetic fp64" if opt.get("table_f32") else ""),
+                             + (", sample table stored as float32 (SSVI_TABLE_F32), arithmetic fp64" if opt.get("table_f32") else "")
+                             + (", fp32 arithmetic option (SSVI_TABLE_F32_TC): float table, V / f in fp32, contraction on the "
+                                "tcgen05 tensor cores (fp16 hi/lo split, fp32 accumulation in tensor memory), likelihood and "
+                                "stages 3-4 fp64" if opt.get("table_tc") else ""),
+                             "dtype": "f32 (tcgen05 contraction)" if opt.get("table_tc") else "f64",
                              "nnz_train": w2.eng.nnz, "steps": 2 * Nm, "warmup": Nm, "value": r2["value"], "unit": UNIT,
                              "ms_per_step": r2["ms_per_step"], "roofline_frac": r2["roofline"]["frac"],
                              "algorithmic_bytes_per_unit": r2["roofline"]["algorithmic_bytes_per_unit"],
@@ -784,7 +798,7 @@ def main():
         print(json.dumps({
             "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": res["ms_per_step"], "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64" if not args.table_f32 else "f64 (f32 sample table)",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (tcgen05 contraction; likelihood and stage 4 fp64)" if args.table_tc else ("f64" if not args.table_f32 else "f64 (f32 sample table)"),
             "data": "synthetic",
             "config": workload_config(args, c, world), "details": details, "multi_gpu_parity": parity,
             "roofline": res["roofline"], "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": res["launches"],

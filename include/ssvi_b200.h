@@ -128,7 +128,10 @@ enum {
   SSVI_TUNE_LIN = 2,             /* SSVI_TF_d + normal likelihood sweeps: the linear-weight kernel (contraction accumulated
                                     across the chunk) instead of the general one */
   SSVI_TUNE_PF2 = 4,             /* rank 25..32, order 3 sweeps: two k-tiles of table records in flight, 2 CTAs per SM */
-  SSVI_TUNE_PF3 = 8              /* ... three k-tiles in flight */
+  SSVI_TUNE_PF3 = 8,             /* ... three k-tiles in flight */
+  SSVI_TUNE_TC_RING = 16         /* SSVI_TABLE_F32_TC sweeps: table records through a per-warp cp.async.bulk ring in shared
+                                    memory (2 CTAs per SM) instead of the register prefetch (3 CTAs per SM); measured 1.6x
+                                    SLOWER on config 5: 1 KB bulk copies are served too slowly */
 };
 
 /* The library itself allocates only the device flag word of a handle. */

@@ -92,13 +92,14 @@ __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView m
   const int64_t rec = memo_rec(mv, jj, sl, j);
   if (mv.tab32 == 2) {                                  // SSVI_TABLE_F32_TC: lane (g, q) holds x[8i + g][8t + 2q + {0,1}]
     float* out = reinterpret_cast<float*>(mv.tab) + rec * (int64_t)(NT * 8 * 64);
+    const double a = jj == 0 ? (double)mv.tc_alpha : 1.0;     // the first other mode's records carry the operand scale
 #pragma unroll
     for (int i = 0; i < NT; ++i)
 #pragma unroll
       for (int t = 0; t < 8; ++t)
         if (t < KT)
           *reinterpret_cast<float2*>(out + tc_rec_index(8 * i + g, 8 * t + 2 * (lane & 3))) =
-              make_float2((float)vv[i][t][0], (float)vv[i][t][1]);
+              make_float2((float)(a * vv[i][t][0]), (float)(a * vv[i][t][1]));
     return;
   }
   if (mv.tab32) {                                       // SSVI_TABLE_F32: half the bytes, two k-tiles per 16-byte load

@@ -16,17 +16,34 @@
 // time: profiles/r3a_tc_probe.txt).  While the next quad is being formed, each warp reads ITS block of the previous
 // accumulator (tcgen05.ld: lane n gets row n) and folds it into registers with the entry's weight:
 //     G += dw_b V_b V_b^T                                                           (SSVI_TF_d.py:47-56)
-// Tiles and accumulators are double-buffered; two mbarriers per buffer (tile written by 4 warps / MMAs complete).
+// A warp folds quad q - 1 after it has formed quad q's tile and before it arrives for quad q, so ONE accumulator (128
+// tensor-memory columns per CTA) suffices; the operand tiles are double-buffered (MMA q reads one while the warps write
+// q + 1).  mbarriers: full[buffer] (4 warp arrivals), done (tcgen05.commit, one phase per quad).  U sits in shared memory
+// as floats pre-divided by a; the table records of the first other mode are pre-multiplied by a (sample_table_kernel), so
+// x = a V needs no multiply.  72 KB of shared memory and <= 168 registers: three CTAs per SM.
 // fp16 range: a |V| > 65504 overflows to inf, which lands in the chunk record and raises SSVI_FLAG_NONFINITE_ACC |
 // SSVI_FLAG_TC_RANGE; a (MemoView::tc_alpha, a power of two) moves the window.
 #pragma once
 #include "accumulate_memo.cuh"
 #include "tc_ops.cuh"
 
-#define SSVI_TC_SMEM (4 * TC_TILE_BYTES + 64)
+// RING (SSVI_TUNE_TC_RING; a measured alternative, not the default): the records reach the warp through a per-warp ring
+// of stages in shared memory, one stage = one item (1 KB of each of the N - 1 records), filled by cp.async.bulk (one lane
+// issues, an mbarrier per stage counts the bytes): four items in flight per warp at no register cost, 104 KB of shared
+// memory, two CTAs per SM.  It LOSES: config 5 at full size 2.11e8 against 3.37e8 entry-updates/s on the same plans
+// (profiles/r3g_bench_c5tc_ring.json): 1 KB bulk copies are served far more slowly than the 32 LDG.128 of the default path
+// move the same bytes.  An L2 prefetch of the next entry's records (prefetch.global.L2, an entry ahead) was measured too:
+// 3.19e8 against 3.32e8 (profiles/r3h).  Default: register prefetch one item ahead, 72 KB, <= 168 registers, three CTAs
+// per SM.
+#define SSVI_TC_U_BYTES(NT) ((NT) * 2048)
+__host__ __device__ constexpr int tc_ring_stages(int NOTH, bool RING) { return RING ? (NOTH == 3 ? 2 : 4) : 0; }
+__host__ __device__ constexpr int tc_ring_bytes(int NOTH, bool RING) { return 4 * tc_ring_stages(NOTH, RING) * NOTH * 1024; }
+__host__ __device__ constexpr int tc_cta_smem(int NOTH, bool RING) {
+  return 4 * TC_TILE_BYTES + SSVI_TC_U_BYTES(4) + tc_ring_bytes(NOTH, RING) + 256;
+}
 
-template <int NT, int NOTH>
-__global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
+template <int NT, int NOTH, bool RING>
+__global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
     DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
     const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
     const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
@@ -48,9 +65,13 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
   const int nq = (len + 3) >> 2;
 
   unsigned char* tiles = smem;                                     // [buffer][hi | lo][16 KB]
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + 4 * TC_TILE_BYTES);
+  float4* Uf = reinterpret_cast<float4*>(smem + 4 * TC_TILE_BYTES);        // [item][p][lane]: U / a in the lanes' order
+  constexpr int RS = tc_ring_stages(NOTH, RING), STAGE_BYTES = NOTH * 1024;
+  unsigned char* wring = smem + 4 * TC_TILE_BYTES + SSVI_TC_U_BYTES(4) + warp * (RS * STAGE_BYTES);   // this warp's ring
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + 4 * TC_TILE_BYTES + SSVI_TC_U_BYTES(4) + tc_ring_bytes(NOTH, RING));
   uint64_t* done = full + 2;
-  uint32_t* holder = reinterpret_cast<uint32_t*>(done + 2);
+  uint64_t* rbar = done + 1 + warp * 4;                 // this warp's stage barriers (RS <= 4)
+  uint32_t* holder = reinterpret_cast<uint32_t*>(done + 1 + 16);
   // the prologue's staging (sampler row + noise block as doubles) and U overlay the tiles, which are idle until the loop
   double* S = reinterpret_cast<double*>(smem);
   double* zs = S + v.srow_len;
@@ -59,11 +80,52 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
   if (tid == 0) {
     tc_mbar_init(&full[0], 4);
     tc_mbar_init(&full[1], 4);
-    tc_mbar_init(&done[0], 1);
-    tc_mbar_init(&done[1], 1);
+    tc_mbar_init(done, 1);
+    for (int i = 0; i < 16; ++i) tc_mbar_init(done + 1 + i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
-  if (warp == 0) tc_tmem_alloc(holder, 256);
+  if (warp == 0) tc_tmem_alloc(holder, 128);
+
+  // ---- this warp's entries (w, w + 4, ...): lane l holds value and table records of entry q0 + l of the current batch of
+  //      32; fetched before the prologue so that the index -> coordinate chain overlaps the own-row sampling --------------
+  const int my_cnt = (len - warp + 3) >> 2;             // may be 0 for high warps of a short chunk
+  const unsigned char* tabb = reinterpret_cast<const unsigned char*>(mv.tab);
+  constexpr int REC_BYTES = NT * 2048;
+  double my_y = 0.0;
+  int32_t my_rec[NOTH];
+  auto load_batch = [&](int q0) {
+    my_y = 0.0;
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = 0;
+    const int b = 4 * (q0 + lane) + warp;
+    if (b < len) {
+      const int64_t eid = __ldcs(entry_ids + start + b);         // touched once: keep the L2 for the table
+      my_y = __ldcs(v.vals + eid);
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, __ldcs(v.coords + eid * N + mv.od[jj]));
+    }
+  };
+  load_batch(0);
+  // ring producer: items [issued, min(limit, consumed + S)) -> stages (item % S); every lane calls, lane 0 issues
+  int issued = 0;
+  auto top_up = [&](int consumed, int limit) {
+    if constexpr (RING) {
+      while (issued < limit && issued < consumed + RS) {
+        const int e2 = issued / NI, it2 = issued - e2 * NI;
+        int32_t r[NOTH];
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj) r[jj] = __shfl_sync(0xffffffffu, my_rec[jj], e2 & 31);
+        if (lane == 0) {
+          const int st = issued % RS;
+          mbar_expect_tx(&rbar[st], STAGE_BYTES);
+#pragma unroll
+          for (int jj = 0; jj < NOTH; ++jj)
+            bulk_g2s(wring + st * STAGE_BYTES + jj * 1024, tabb + (int64_t)r[jj] * REC_BYTES + it2 * 1024, 1024, &rbar[st]);
+        }
+        ++issued;
+      }
+    }
+  };
 
   // ---- prologue: U(row, slot) = m + L z_own, once per CTA (ui samples, SSVI_TF_interface.py:251-254) --------------------
   {
@@ -78,7 +140,8 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
       for (int i = tid; i < v.zblk; i += 128) zs[i] = zsrc[i];
     }
   }
-  __syncthreads();
+  __syncthreads();                                      // (also: the mbarriers are initialised)
+  top_up(0, min(my_cnt, 32) * NI);                      // the first S items travel while U is sampled
 #pragma unroll
   for (int i = 0; i < NT; ++i)
 #pragma unroll
@@ -88,20 +151,23 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
       Us[(i * KT + warp + 4 * h) * 32 + lane] = make_double2(c0, c1);
     }
   __syncthreads();
-  float u[NI][8];                                       // this lane's share of U: rows 8 rg + r8, samples 8 (kq + 4 h) + j
+  const float alpha = mv.tc_alpha;
+  const double inv_alpha = 1.0 / (double)alpha;
+  if (warp == 0) {                                      // lane (r8, kq): rows 8 rg + r8, samples 8 (kq + 4 h) + j of U / a
 #pragma unroll
-  for (int it = 0; it < NI; ++it) {
-    const int rg = it >> 1, h = it & 1;
-#pragma unroll
-    for (int jp = 0; jp < 4; ++jp) {
-      const double2 x = Us[(rg * KT + kq + 4 * h) * 32 + r8 * 4 + jp];
-      u[it][2 * jp] = (float)x.x;
-      u[it][2 * jp + 1] = (float)x.y;
+    for (int it = 0; it < NI; ++it) {
+      const int rg = it >> 1, h = it & 1;
+      const double2* up = Us + (rg * KT + kq + 4 * h) * 32 + r8 * 4;
+      const double2 x0 = up[0], x1 = up[1], x2 = up[2], x3 = up[3];
+      Uf[(it * 2) * 32 + lane] = make_float4((float)(x0.x * inv_alpha), (float)(x0.y * inv_alpha), (float)(x1.x * inv_alpha),
+                                             (float)(x1.y * inv_alpha));
+      Uf[(it * 2 + 1) * 32 + lane] = make_float4((float)(x2.x * inv_alpha), (float)(x2.y * inv_alpha),
+                                                 (float)(x3.x * inv_alpha), (float)(x3.y * inv_alpha));
     }
   }
-  __syncthreads();                                      // staging and U are dead: the region becomes the operand tiles
-  for (int i = tid; i < 4 * TC_TILE_BYTES / 16; i += 128) reinterpret_cast<uint4*>(tiles)[i] = make_uint4(0, 0, 0, 0);
-  tc_fence_async_smem();
+  // Staging and U are dead: the region becomes the operand tiles.  They are NOT cleared: row n of an accumulator block
+  // depends on row n of the operands only, and rows / blocks that no entry wrote (n >= 8 NT, warps without an entry in
+  // the last quad) are never folded into an output.
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -109,7 +175,6 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
 
   // ---- main loop -----------------------------------------------------------------------------------------------------
   const float4* tab4 = reinterpret_cast<const float4*>(mv.tab);
-  const float alpha = mv.tc_alpha;
   const double inv_k1 = 1.0 / (double)(8 * KT);
   const uint32_t idesc = tc_idesc_f16(128, 128);
   float gacc[32], dacc[NT];
@@ -117,38 +182,42 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
   for (int cc = 0; cc < 32; ++cc) gacc[cc] = 0.f;
 #pragma unroll
   for (int i = 0; i < NT; ++i) dacc[i] = 0.f;
-  double my_y = 0.0;                                    // lane l: entry (q0 + l) of this warp, q0 = the quad batch's first
-  int32_t my_rec[NOTH];
-#pragma unroll
-  for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = 0;
   float4 cur[NOTH][2];                                  // item 0 of the entry about to be processed
   bool have_cur = false;
   float w_prev = 0.f;
   bool prev_valid = false;
 
-  for (int q = 0; q <= nq; ++q) {
+  // this warp's block of the accumulator (quad p's V V^T, row n in lane n) folded into registers with the entry's weight
+  auto fold = [&](int p) {
+    tc_mbar_wait(done, p & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      float d[16];
+      tc_tmem_ld16(tmem + ((uint32_t)(32 * warp) << 16) + 32 * warp + 16 * half, d);
+      if (prev_valid) {
+#pragma unroll
+        for (int cc = 0; cc < 16; ++cc) gacc[16 * half + cc] = fmaf(w_prev, d[cc], gacc[16 * half + cc]);
+      }
+    }
+    tc_fence_before();
+  };
+
+  for (int q = 0; q < nq; ++q) {
     const int buf = q & 1;
     float w_b = 0.f;
     bool valid = false;
-    if (q < nq) {
+    {
       valid = 4 * q + warp < len;                       // warp-uniform
       unsigned char* thi = tiles + (buf * 2) * TC_TILE_BYTES;
       unsigned char* tlo = thi + TC_TILE_BYTES;
       if (valid) {
         const int el = q & 31;
-        if (el == 0) {                                  // next 32 entries of this warp: ids, values, table records
-          my_y = 0.0;
-#pragma unroll
-          for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = 0;
-          const int b = 4 * (q + lane) + warp;
-          if (b < len) {
-            const int64_t eid = entry_ids[start + b];
-            my_y = v.vals[eid];
-#pragma unroll
-            for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, v.coords[eid * N + mv.od[jj]]);
-          }
+        if (el == 0 && q > 0) {                         // next 32 entries of this warp (the ring is drained here)
+          load_batch(q);
           have_cur = false;
         }
+        const int lim = min(my_cnt, q - el + 32) * NI;  // the producer stops at the batch's end
         const double y = __shfl_sync(0xffffffffu, my_y, el);
         const bool next_valid = (el + 1 < 32) && (4 * (q + 1) + warp < len);
         const float4* pc[NOTH];
@@ -158,7 +227,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
           pc[jj] = tab4 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], el) * REC4 + lane;
           pn[jj] = tab4 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], next_valid ? el + 1 : el) * REC4 + lane;
         }
-        if (!have_cur) {
+        if (!RING && !have_cur) {
 #pragma unroll
           for (int jj = 0; jj < NOTH; ++jj) {
             cur[jj][0] = __ldcg(pc[jj]);
@@ -172,11 +241,23 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
         for (int it = 0; it < NI; ++it) {
           const int rg = it >> 1, h = it & 1;
           float4 nxt[NOTH][2];                          // one item ahead (the next entry's first item at the end)
+          if constexpr (RING) {
+            const int gi = q * NI + it, st = gi % RS;
+            top_up(gi, lim);
+            tc_mbar_wait(&rbar[st], (gi / RS) & 1);
+            const float4* rp = reinterpret_cast<const float4*>(wring + st * STAGE_BYTES) + lane;
 #pragma unroll
-          for (int jj = 0; jj < NOTH; ++jj) {
-            const float4* p = (it + 1 < NI) ? pc[jj] + ((it + 1) * 2) * 32 : pn[jj];
-            nxt[jj][0] = __ldcg(p);
-            nxt[jj][1] = __ldcg(p + 32);
+            for (int jj = 0; jj < NOTH; ++jj) {
+              cur[jj][0] = rp[jj * 64];
+              cur[jj][1] = rp[jj * 64 + 32];
+            }
+          } else {
+#pragma unroll
+            for (int jj = 0; jj < NOTH; ++jj) {
+              const float4* p = (it + 1 < NI) ? pc[jj] + ((it + 1) * 2) * 32 : pn[jj];
+              nxt[jj][0] = __ldcg(p);
+              nxt[jj][1] = __ldcg(p + 32);
+            }
           }
           float x[8] = {cur[0][0].x, cur[0][0].y, cur[0][0].z, cur[0][0].w, cur[0][1].x, cur[0][1].y, cur[0][1].z, cur[0][1].w};
 #pragma unroll
@@ -184,18 +265,26 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
             x[0] *= cur[jj][0].x; x[1] *= cur[jj][0].y; x[2] *= cur[jj][0].z; x[3] *= cur[jj][0].w;
             x[4] *= cur[jj][1].x; x[5] *= cur[jj][1].y; x[6] *= cur[jj][1].z; x[7] *= cur[jj][1].w;
           }
+          if constexpr (RING) {                         // every lane's reads of the stage have returned: refill it
+            __syncwarp();
+            top_up(q * NI + it + 1, lim);
+          }
+          const float4 u0 = Uf[(it * 2) * 32 + lane], u1 = Uf[(it * 2 + 1) * 32 + lane];
+          const float uu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
           float s = 0.f;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            fp[h][j] = fmaf(u[it][j], x[j], fp[h][j]);
+            fp[h][j] = fmaf(uu[j], x[j], fp[h][j]);
             s += x[j];
           }
           if (h == 0) rs[rg] = s; else rs[rg] += s;
-          tc_store_split8(thi, tlo, 32 * warp + 8 * rg + r8, kq + 4 * h, x, alpha);
+          tc_store_split8(thi, tlo, 32 * warp + 8 * rg + r8, kq + 4 * h, x);
+          if constexpr (!RING) {
 #pragma unroll
-          for (int jj = 0; jj < NOTH; ++jj) {
-            cur[jj][0] = nxt[jj][0];
-            cur[jj][1] = nxt[jj][1];
+            for (int jj = 0; jj < NOTH; ++jj) {
+              cur[jj][0] = nxt[jj][0];
+              cur[jj][1] = nxt[jj][1];
+            }
           }
         }
         have_cur = next_valid;
@@ -214,7 +303,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
         log_pdf_derivs_pair(v.lik, y, (double)f[0], (double)f[1], v.lik_param, a0, b0, a1, b1);
         double sum_a = a0 + a1, sum_d = b0 + b1;
         warp_sum2(sum_a, sum_d, lane);
-        const float aw = (float)(sum_a * inv_k1 * inv_k1);
+        const float aw = (float)(sum_a * inv_k1 * inv_k1 * inv_alpha);   // the row sums below are of x = a V
         w_b = (float)(0.5 * sum_d * inv_k1 * inv_k1);
 #pragma unroll
         for (int i = 0; i < NT; ++i) {                  // row sums: over this lane's 16 samples (done), then over kq
@@ -224,15 +313,16 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
           dacc[i] = fmaf(aw, s, dacc[i]);
         }
       }
+      if (q > 0) fold(q - 1);                           // before this warp licenses the MMAs that overwrite the accumulator
       tc_fence_async_smem();                            // tile stores -> visible to the tensor core
-      tc_fence_before();                                // and this warp's reads of the accumulator it is about to release
+      tc_fence_before();
       __syncwarp();
       if (lane == 0) tc_mbar_arrive(&full[buf]);
       if (warp == 0) {
         tc_mbar_wait(&full[buf], (q >> 1) & 1);
         tc_fence_after();
         if (lane == 0) {
-          const uint32_t ahi = tc_smem_u32(thi), alo = tc_smem_u32(tlo), dst = tmem + buf * 128;
+          const uint32_t ahi = tc_smem_u32(thi), alo = tc_smem_u32(tlo), dst = tmem;
 #pragma unroll
           for (int s = 0; s < 4; ++s) {
             const uint64_t dh = tc_smem_desc(ahi + 256 * s, TC_LBO, TC_SBO), dl = tc_smem_desc(alo + 256 * s, TC_LBO, TC_SBO);
@@ -240,26 +330,15 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
             tc_mma_f16(dst, dh, dl, idesc, 1);
             tc_mma_f16(dst, dl, dh, idesc, 1);
           }
-          tc_commit(&done[buf]);
+          tc_commit(done);
         }
         __syncwarp();
       }
     }
-    if (q > 0) {                                        // the previous quad's V V^T: this warp's block, row n in lane n
-      const int pb = buf ^ 1;
-      tc_mbar_wait(&done[pb], ((q - 1) >> 1) & 1);
-      tc_fence_after();
-      float d[32];
-      tc_tmem_ld32(tmem + ((uint32_t)(32 * warp) << 16) + pb * 128 + 32 * warp, d);
-      if (prev_valid) {
-#pragma unroll
-        for (int cc = 0; cc < 32; ++cc) gacc[cc] = fmaf(w_prev, d[cc], gacc[cc]);
-      }
-      tc_fence_before();
-    }
     w_prev = w_b;
     prev_valid = valid;
   }
+  if (nq > 0) fold(nq - 1);
 
   // ---- CTA reduction (fixed warp order => deterministic) and the chunk record [di | Di | si_sum | count] ------------
   __syncthreads();                                      // every MMA has completed and been read: the tiles are dead
@@ -277,7 +356,7 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
   bool bad = false;
   for (int n = tid; n < D; n += 128) {
     const float x = ((dred[n] + dred[32 + n]) + dred[64 + n]) + dred[96 + n];
-    out[n] = (double)x;
+    __stcs(out + n, (double)x);
     bad |= !isfinite(x);
   }
   for (int i = tid; i < 32 * 32; i += 128) {
@@ -285,8 +364,8 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
     if (n1 < D && n2 <= n1) {                           // lower triangle incl. diagonal, mirrored: exactly symmetric
       const float x = ((red[n1 * 33 + n2] + red[(32 + n1) * 33 + n2]) + red[(64 + n1) * 33 + n2]) + red[(96 + n1) * 33 + n2];
       const double xd = ia2 * (double)x;
-      out[D + n1 * D + n2] = xd;
-      out[D + n2 * D + n1] = xd;
+      __stcs(out + D + n1 * D + n2, xd);
+      __stcs(out + D + n2 * D + n1, xd);
       bad |= !isfinite(x);
     }
   }
@@ -297,5 +376,5 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_kernel(
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tc_tmem_dealloc(tmem, 256);
+  if (warp == 0) tc_tmem_dealloc(tmem, 128);
 }

@@ -80,6 +80,20 @@ __device__ __forceinline__ void tc_tmem_ld32(uint32_t taddr, float (&d)[32]) {
   for (int i = 0; i < 32; ++i) d[i] = __uint_as_float(r[i]);
 }
 
+__device__ __forceinline__ void tc_tmem_ld16(uint32_t taddr, float (&d)[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) d[i] = __uint_as_float(r[i]);
+}
+
 // ---- descriptors -------------------------------------------------------------------------------------------------------
 // shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start >> 4 [0,14) | LBO >> 4 [16,30) | SBO >> 4 [32,46) |
 // version 1 [46,48) | base offset 0 [49,52) | layout type [61,64) = 0 (no swizzle)
@@ -109,14 +123,14 @@ __device__ __forceinline__ void tc_commit(uint64_t* bar) {
 }
 
 // ---- operand tile ------------------------------------------------------------------------------------------------------
-// 8 consecutive-k values of row r (k = 8 * k8 .. 8 * k8 + 7), scaled by alpha, split into fp16 hi / lo and stored as one
-// 16-byte vector each.  The 8 lanes of a quarter-warp write 8 consecutive rows of one core matrix: 128 contiguous bytes.
+// 8 consecutive-k values of row r (k = 8 * k8 .. 8 * k8 + 7), split into fp16 hi / lo and stored as one 16-byte vector
+// each (the caller has scaled them into the fp16 window).  The 8 lanes of a quarter-warp write 8 consecutive rows of one core matrix: 128 contiguous bytes.
 __device__ __forceinline__ void tc_store_split8(unsigned char* tile_hi, unsigned char* tile_lo, int r, int k8,
-                                                const float (&x)[8], float alpha) {
+                                                const float (&x)[8]) {
   uint32_t hi[4], lo[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const float a = x[2 * i] * alpha, b = x[2 * i + 1] * alpha;
+    const float a = x[2 * i], b = x[2 * i + 1];
     const __half2 h = __floats2half2_rn(a, b);
     const float2 hf = __half22float2(h);
     const __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);

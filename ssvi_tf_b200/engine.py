@@ -697,7 +697,12 @@ class Engine(object):
         others = [d for d in range(self.N) if d != dim]
         touched = sum(self.row_window[d][1] - self.row_window[d][0] + 1 for d in others)
         per_slot = per_slot * touched // max(sum(self.dims[d] for d in others), 1)   # the records this shard gathers
-        nb = -(-per_slot // max(self.table_budget_bytes, 1))
+        budget = max(self.table_budget_bytes, 1)
+        if self.table_dtype == "f32_tc":
+            # the tensor-core kernel waits on its gathers, not on a math pipe: it wants the tile well inside the L2
+            # (config 5 at full size, 2 / 3 / 4 / 5 blocks: 0.83 / 0.86 / 0.89 / 0.82 of the roofline, profiles/r3e, r3f)
+            budget = max(budget // 2, 1)
+        nb = -(-per_slot // budget)
         rp = self.rowptr_h[dim]
         rows_here = self.row_window[dim][1] - self.row_window[dim][0] + 1
         per_pair = float(rp[-1]) / max(rows_here * int(self.noise.slots), 1)          # entries per (row, slot)

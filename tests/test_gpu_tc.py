@@ -83,6 +83,23 @@ def test_tensor_core_sweep_under_l2_tiling_and_on_an_f32_pool():
         np.testing.assert_array_equal(a2[:, -1], a1[:, -1])
 
 
+def test_tensor_core_sweep_tuning_variants_give_the_same_records():
+    """SSVI_TUNE_TC_RING (records through a cp.async.bulk ring in shared memory) changes how the table records travel, not
+    what is computed: bitwise the same accumulators."""
+    rng = np.random.default_rng(5)
+    for dims, D, lik, P, W in (([5, 4, 4], 32, "normal", 5, 3), ([40, 3, 3], 12, "poisson", 1, 200),
+                               ([4, 3, 3, 3], 10, "normal", 3, 64), ([7, 9], 20, "bernoulli", 2, 64)):
+        cfg = so.make_config("d", lik, D, diag=False, k1=64, k2=4, batch_size=10 ** 9)
+        coords, vals = random_problem(rng, lik, dims, int(0.8 * np.prod(dims)))
+        st0 = random_state(rng, cfg, dims)
+        pool = so.make_tape(rng, cfg, len(dims), P)
+        for dim in range(len(dims)):
+            a0, _, _ = _run(cfg, dims, coords, vals, st0, pool, dim, W, "f32_tc")
+            for tuning in (16,):
+                a1, _, _ = _run(cfg, dims, coords, vals, st0, pool, dim, W, "f32_tc", tuning=tuning)
+                np.testing.assert_array_equal(a1, a0, err_msg="tuning %d, dims %s mode %d" % (tuning, dims, dim))
+
+
 def test_tensor_core_sweep_flags_an_fp16_overflow():
     """An operand outside the fp16 window must not pass silently: the chunk record goes non-finite and check_flags raises."""
     from ssvi_tf_b200.engine import Engine, NoisePool

@@ -122,7 +122,11 @@ __global__ void __launch_bounds__(128, 2) tc_probe_kernel(ProbeArgs a) {
             s += v[j];
           }
           if (h == 0) rs[rg] = s; else rs[rg] += s;
-          if (!a.no_tiles) tc_store_split8(thi, tlo, 32 * warp + 8 * rg + r8, kq + 4 * h, v, a.alpha);
+          if (!a.no_tiles) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] *= a.alpha;
+            tc_store_split8(thi, tlo, 32 * warp + 8 * rg + r8, kq + 4 * h, v);
+          }
           c0 = n0; c1 = n1; e0 = m0; e1 = m1;
         }
         // f_k = SUM_d u v: in-lane over the row groups (done), then over the 8 lanes r8 by a transposing reduction
