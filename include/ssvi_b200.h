@@ -129,9 +129,11 @@ enum {
                                     across the chunk) instead of the general one */
   SSVI_TUNE_PF2 = 4,             /* rank 25..32, order 3 sweeps: two k-tiles of table records in flight, 2 CTAs per SM */
   SSVI_TUNE_PF3 = 8,             /* ... three k-tiles in flight */
-  SSVI_TUNE_TC_RING = 16         /* SSVI_TABLE_F32_TC sweeps: table records through a per-warp cp.async.bulk ring in shared
+  SSVI_TUNE_TC_RING = 16,        /* SSVI_TABLE_F32_TC sweeps: table records through a per-warp cp.async.bulk ring in shared
                                     memory (2 CTAs per SM) instead of the register prefetch (3 CTAs per SM); measured 1.6x
                                     SLOWER on config 5: 1 KB bulk copies are served too slowly */
+  SSVI_TUNE_TC_PF = 32           /* SSVI_TABLE_F32_TC sweeps: 2-3 KB of each table record in flight per warp (a ring of
+                                    register buffers, ~200 registers, 2 CTAs per SM) instead of 1 KB (3 CTAs per SM) */
 };
 
 /* The library itself allocates only the device flag word of a handle. */

@@ -18,7 +18,7 @@
 // double2 per lane, i.e. a table record is [NT][KT][32] double2 and a warp reads a tile as 512 contiguous bytes.
 #pragma once
 #include "accumulate_mma.cuh"
-#include "tc_ops.cuh"
+#include "tc_layout.cuh"
 
 #define SSVI_MEMO_MAX_OTH 3
 

@@ -10,7 +10,7 @@
 //   * writes rows 32 w .. 32 w + 31 of the quad's operand tile: a V split into fp16 hi + lo (22 significand bits), K-major,
 //     no swizzle, straight from registers;
 //   * evaluates the k1-averaged log-likelihood derivatives in fp64 (two samples per lane; quirk Q3) -> weights aw, dw.
-// When the four warps have arrived, one thread issues 12 tcgen05.mma (kind::f16, M = N = 128, K = 16): per K-step
+// The last of the four warps to arrive (a shared-memory counter) issues, from one thread, 12 tcgen05.mma (kind::f16, M = N = 128, K = 16): per K-step
 // hi hi^T + hi lo^T + lo hi^T into a 128 x 128 fp32 accumulator in tensor memory whose diagonal 32 x 32 blocks are the
 // entries' V V^T (the off-diagonal blocks are the price of the 128-row minimum of the instruction; the tensor pipe has the
 // time: profiles/r3a_tc_probe.txt).  While the next quad is being formed, each warp reads ITS block of the previous
@@ -18,7 +18,7 @@
 //     G += dw_b V_b V_b^T                                                           (SSVI_TF_d.py:47-56)
 // A warp folds quad q - 1 after it has formed quad q's tile and before it arrives for quad q, so ONE accumulator (128
 // tensor-memory columns per CTA) suffices; the operand tiles are double-buffered (MMA q reads one while the warps write
-// q + 1).  mbarriers: full[buffer] (4 warp arrivals), done (tcgen05.commit, one phase per quad).  U sits in shared memory
+// q + 1).  One mbarrier, done (tcgen05.commit, one phase per quad), tells the warps a quad is ready.  U sits in shared memory
 // as floats pre-divided by a; the table records of the first other mode are pre-multiplied by a (sample_table_kernel), so
 // x = a V needs no multiply.  72 KB of shared memory and <= 168 registers: three CTAs per SM.
 // fp16 range: a |V| > 65504 overflows to inf, which lands in the chunk record and raises SSVI_FLAG_NONFINITE_ACC |
@@ -42,8 +42,13 @@ __host__ __device__ constexpr int tc_cta_smem(int NOTH, bool RING) {
   return 4 * TC_TILE_BYTES + SSVI_TC_U_BYTES(4) + tc_ring_bytes(NOTH, RING) + 256;
 }
 
-template <int NT, int NOTH, bool RING>
-__global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
+// PF: items (1 KB of each record) a warp keeps in flight ahead of the one it works on, in a static ring of PF + 1 register
+// buffers (2 NT must be a multiple of PF + 1 so that every entry starts at buffer 0).  PF == 1: 168 registers, three CTAs
+// per SM.  PF > 1: ~200 registers, two CTAs per SM, each warp with PF KB per record in flight.
+__host__ __device__ constexpr int tc_deep_pf(int NT) { return NT == 3 ? 2 : (NT == 1 ? 1 : 3); }
+
+template <int NT, int NOTH, bool RING, int PF = 1>
+__global__ void __launch_bounds__(128, (RING || PF > 1) ? 2 : 3) accumulate_tc_kernel(
     DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
     const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
     const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
@@ -72,14 +77,14 @@ __global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
   uint64_t* done = full + 2;
   uint64_t* rbar = done + 1 + warp * 4;                 // this warp's stage barriers (RS <= 4)
   uint32_t* holder = reinterpret_cast<uint32_t*>(done + 1 + 16);
+  uint32_t* cnt = holder + 1;                           // [2] arrival counters of the operand-tile buffers
   // the prologue's staging (sampler row + noise block as doubles) and U overlay the tiles, which are idle until the loop
   double* S = reinterpret_cast<double*>(smem);
   double* zs = S + v.srow_len;
   double2* Us = reinterpret_cast<double2*>(smem + 2 * TC_TILE_BYTES);
 
   if (tid == 0) {
-    tc_mbar_init(&full[0], 4);
-    tc_mbar_init(&full[1], 4);
+    cnt[0] = cnt[1] = 0;
     tc_mbar_init(done, 1);
     for (int i = 0; i < 16; ++i) tc_mbar_init(done + 1 + i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
@@ -182,8 +187,10 @@ __global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
   for (int cc = 0; cc < 32; ++cc) gacc[cc] = 0.f;
 #pragma unroll
   for (int i = 0; i < NT; ++i) dacc[i] = 0.f;
-  float4 cur[NOTH][2];                                  // item 0 of the entry about to be processed
-  bool have_cur = false;
+  constexpr int R = RING ? 1 : PF + 1;                  // register buffers: item it of ANY entry lives in rb[it % R]
+  static_assert(RING || NI % R == 0, "2 NT must be a multiple of PF + 1");
+  float4 rb[R][NOTH][2];
+  bool have_cur = false;                                // items 0 .. PF-1 of the entry about to be processed are in flight
   float w_prev = 0.f;
   bool prev_valid = false;
 
@@ -229,10 +236,12 @@ __global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
         }
         if (!RING && !have_cur) {
 #pragma unroll
-          for (int jj = 0; jj < NOTH; ++jj) {
-            cur[jj][0] = __ldcg(pc[jj]);
-            cur[jj][1] = __ldcg(pc[jj] + 32);
-          }
+          for (int d = 0; d < PF; ++d)
+#pragma unroll
+            for (int jj = 0; jj < NOTH; ++jj) {
+              rb[d % R][jj][0] = __ldcg(pc[jj] + (d * 2) * 32);
+              rb[d % R][jj][1] = __ldcg(pc[jj] + (d * 2 + 1) * 32);
+            }
         }
         float fp[2][8], rs[NT];
 #pragma unroll
@@ -240,7 +249,7 @@ __global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
 #pragma unroll
         for (int it = 0; it < NI; ++it) {
           const int rg = it >> 1, h = it & 1;
-          float4 nxt[NOTH][2];                          // one item ahead (the next entry's first item at the end)
+          float4 (&cur)[NOTH][2] = rb[RING ? 0 : it % R];
           if constexpr (RING) {
             const int gi = q * NI + it, st = gi % RS;
             top_up(gi, lim);
@@ -251,12 +260,13 @@ __global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
               cur[jj][0] = rp[jj * 64];
               cur[jj][1] = rp[jj * 64 + 32];
             }
-          } else {
+          } else {                                      // item it + PF (of the next entry at the end) -> its buffer
+            const int nit = it + PF;
 #pragma unroll
             for (int jj = 0; jj < NOTH; ++jj) {
-              const float4* p = (it + 1 < NI) ? pc[jj] + ((it + 1) * 2) * 32 : pn[jj];
-              nxt[jj][0] = __ldcg(p);
-              nxt[jj][1] = __ldcg(p + 32);
+              const float4* p = (nit < NI) ? pc[jj] + (nit * 2) * 32 : pn[jj] + ((nit - NI) * 2) * 32;
+              rb[nit % R][jj][0] = __ldcg(p);
+              rb[nit % R][jj][1] = __ldcg(p + 32);
             }
           }
           float x[8] = {cur[0][0].x, cur[0][0].y, cur[0][0].z, cur[0][0].w, cur[0][1].x, cur[0][1].y, cur[0][1].z, cur[0][1].w};
@@ -279,13 +289,6 @@ __global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
           }
           if (h == 0) rs[rg] = s; else rs[rg] += s;
           tc_store_split8(thi, tlo, 32 * warp + 8 * rg + r8, kq + 4 * h, x);
-          if constexpr (!RING) {
-#pragma unroll
-            for (int jj = 0; jj < NOTH; ++jj) {
-              cur[jj][0] = nxt[jj][0];
-              cur[jj][1] = nxt[jj][1];
-            }
-          }
         }
         have_cur = next_valid;
         // f_k = SUM_n u v: summed in-lane over the row groups, then over the 8 lanes r8 by a transposing reduction that
@@ -317,9 +320,13 @@ __global__ void __launch_bounds__(128, RING ? 2 : 3) accumulate_tc_kernel(
       tc_fence_async_smem();                            // tile stores -> visible to the tensor core
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) tc_mbar_arrive(&full[buf]);
-      if (warp == 0) {
-        tc_mbar_wait(&full[buf], (q >> 1) & 1);
+      // the LAST warp to arrive issues the quad's MMAs (no warp waits for the others here): arrivals for quad q go to
+      // counter q & 1, which has received all four of quad q - 2 before any of quad q (a warp folds q - 1 first, and
+      // MMA q - 1 needed everybody's arrival for q - 1, which follows the arrival for q - 2 in program order)
+      uint32_t last = 0;
+      if (lane == 0) last = (tc_arrive_count(&cnt[buf]) & 3u) == 3u;
+      last = __shfl_sync(0xffffffffu, last, 0);
+      if (last) {
         tc_fence_after();
         if (lane == 0) {
           const uint32_t ahi = tc_smem_u32(thi), alo = tc_smem_u32(tlo), dst = tmem;

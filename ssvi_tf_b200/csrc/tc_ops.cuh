@@ -13,6 +13,7 @@
 #pragma once
 #include <cuda_fp16.h>
 #include <stdint.h>
+#include "tc_layout.cuh"
 
 #define TC_LBO 128
 #define TC_SBO 1024
@@ -46,6 +47,13 @@ __device__ __forceinline__ void tc_mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!tc_mbar_try(bar, parity))
     if (++spins > (1u << 22)) __trap();
+}
+// Counting arrival with release + acquire semantics in the CTA scope: returns the count before this arrival.  The warp
+// that finds itself the last of a group both sees the others' writes and may act for the group.
+__device__ __forceinline__ uint32_t tc_arrive_count(uint32_t* cnt) {
+  uint32_t old;
+  asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;\n" : "=r"(old) : "r"(tc_smem_u32(cnt)) : "memory");
+  return old;
 }
 // generic-proxy writes (st.shared of the operand tiles) -> visible to the async proxy (the tensor core's reads)
 __device__ __forceinline__ void tc_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
@@ -140,13 +148,4 @@ __device__ __forceinline__ void tc_store_split8(unsigned char* tile_hi, unsigned
   const int off = (r >> 3) * TC_SBO + k8 * TC_LBO + (r & 7) * 16;
   *reinterpret_cast<uint4*>(tile_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
   *reinterpret_cast<uint4*>(tile_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-}
-
-// Table record of the fp32 tensor-core path: NT row groups x 64 samples as float4 vectors
-//     [rg][h][p][lane] float4,   lane = (d & 7) + 8 * ((k >> 3) & 3),  h = k >> 5,  p = (k >> 2) & 1,  element k & 3
-// so lane (r8 = lane & 7, kq = lane >> 3) reads, for row group rg and half h, the 8 samples k = 8 (kq + 4 h) .. + 7 of row
-// 8 rg + r8 with two fully coalesced 16-byte loads (p = 0, 1).
-__host__ __device__ inline int tc_rec_index(int d, int k) {
-  const int rg = d >> 3, r8 = d & 7, k8 = k >> 3, h = k8 >> 2, kq = k8 & 3, p = (k >> 2) & 1, e = k & 3;
-  return ((((rg * 2 + h) * 2 + p) * 32 + (r8 + 8 * kq)) << 2) + e;
 }

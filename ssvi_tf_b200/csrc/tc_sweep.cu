@@ -3,12 +3,12 @@
 #include "tc_sweep.cuh"
 #include "accumulate_tc.cuh"
 
-template <int NT, int NOTH, bool RING>
+template <int NT, int NOTH, bool RING, int PF>
 static int launch_tc1(const DevView& v, const MemoView& mv, int64_t n_chunks, const int32_t* chunk_row,
                      const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
                      const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own, int z_f32,
                      double* partial_out, cudaStream_t st) {
-  auto kern = accumulate_tc_kernel<NT, NOTH, RING>;
+  auto kern = accumulate_tc_kernel<NT, NOTH, RING, PF>;
   constexpr int smem = tc_cta_smem(NOTH, RING);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return (int)e;
@@ -22,11 +22,13 @@ static int launch_tc(const DevView& v, const MemoView& mv, int64_t n_chunks, con
                      const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
                      const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own, int z_f32,
                      double* partial_out, cudaStream_t st) {
-  if (v.tuning & SSVI_TUNE_TC_RING)
-    return launch_tc1<NT, NOTH, true>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids,
-                                      rows, z_own, z_f32, partial_out, st);
-  return launch_tc1<NT, NOTH, false>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows,
-                                     z_own, z_f32, partial_out, st);
+#define TC_L(RING_, PF_)                                                                                                 \
+  launch_tc1<NT, NOTH, RING_, PF_>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, \
+                                   z_own, z_f32, partial_out, st)
+  if (v.tuning & SSVI_TUNE_TC_RING) return TC_L(true, 1);
+  if (v.tuning & SSVI_TUNE_TC_PF) return TC_L(false, tc_deep_pf(NT));
+  return TC_L(false, 1);
+#undef TC_L
 }
 
 int ssvi_launch_accumulate_tc(const DevView& v, const MemoView& mv, int nt, int64_t n_chunks, const int32_t* chunk_row,

@@ -95,7 +95,7 @@ def test_tensor_core_sweep_tuning_variants_give_the_same_records():
         pool = so.make_tape(rng, cfg, len(dims), P)
         for dim in range(len(dims)):
             a0, _, _ = _run(cfg, dims, coords, vals, st0, pool, dim, W, "f32_tc")
-            for tuning in (16,):
+            for tuning in (16, 32):
                 a1, _, _ = _run(cfg, dims, coords, vals, st0, pool, dim, W, "f32_tc", tuning=tuning)
                 np.testing.assert_array_equal(a1, a0, err_msg="tuning %d, dims %s mode %d" % (tuning, dims, dim))
 
