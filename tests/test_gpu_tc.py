@@ -43,7 +43,7 @@ def test_tensor_core_sweep_is_within_the_fp32_tolerance(dims, D, lik, P, W, caps
     st0 = random_state(rng, cfg, dims)
     rowptr, perm = so.build_index(coords, dims)
     pool = so.make_tape(rng, cfg, N, P)
-    worst = 0.0
+    worst, fp64_bar = 0.0, True
     for dim in range(N):
         n = dims[dim]
         acc64, _, plan64 = _run(cfg, dims, coords, vals, st0, pool, dim, W, torch.float64)
@@ -62,8 +62,13 @@ def test_tensor_core_sweep_is_within_the_fp32_tolerance(dims, D, lik, P, W, caps
         want = so.copy_state(st0)
         so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
         assert_state_close(state_tc, want, cfg, 1e-4, what="tensor-core sweep, dims=%s mode %d" % (dims, dim))
+        try:                                             # informational: does the update also meet the fp64 bar?
+            assert_state_close(state_tc, want, cfg, 1e-5)
+        except AssertionError:
+            fp64_bar = False
     with capsys.disabled():
-        print("\n  tcgen05 sweep vs fp64 sweep, largest accumulator deviation / max |acc|: %.2e (dims %s, D %d)" % (worst, dims, D))
+        print("\n  tcgen05 sweep vs fp64 sweep, largest accumulator deviation / max |acc|: %.2e (dims %s, D %d); updated "
+              "rows within 1e-5 of the oracle as well: %s" % (worst, dims, D, fp64_bar))
 
 
 def test_tensor_core_sweep_under_l2_tiling_and_on_an_f32_pool():
