@@ -124,3 +124,41 @@ def test_tensor_core_sweep_flags_an_fp16_overflow():
     with pytest.raises(AssertionError, match="fp16 range"):
         eng.check_flags()
     eng.close()
+
+
+def test_nation_full_sweeps_with_the_tensor_core_option(tmp_path):
+    """End to end on the reference's own dataset (Baseline/Data/nation.txt, the run of real_test.py:58-84 at rank 20,
+    k1 = 64): full-row sweeps of every mode through the sample-table path, once all-fp64 and once with the fp32 / tcgen05
+    option, same split and same variates per seed.  The option must land on the fp64 run's test metrics (1 % per seed:
+    only the arithmetic differs) and must not be worse than the UNMODIFIED reference's (1 % + three standard errors)."""
+    import gzip
+    import os
+    import shutil
+    import ssvi_tf_b200 as pkg
+    e2e = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden_e2e")
+    z = np.load(os.path.join(e2e, "nation_d_full_metrics.npz"))
+    path = str(tmp_path / "nation.txt")
+    with gzip.open(os.path.join(e2e, "nation.txt.gz"), "rb") as f, open(path, "wb") as g:
+        shutil.copyfileobj(f, g)
+    seeds = [int(s) for s in z["seeds"]][:6]
+    sweeps = 12                                          # ~ the reference's 300 one-row-per-mode iterations / mean(dims)
+    res = {}
+    for table in (torch.float64, "f32_tc"):
+        out = []
+        for seed in seeds:
+            np.random.seed(seed)
+            t = pkg.binary_tensor()
+            t.read_from_file(path, 0.8, 0, 0.2)
+            m = pkg.SSVI_TF_d(tensor=t, rank=int(z["rank"]), mean_update="S", cov_update="N", eta=1.0, cov_eta=1.0,
+                              k1=int(z["k1"]), k2=int(z["k2"]), diag=False, noise_dtype=torch.float32, noise_seed=seed,
+                              noise_slots=128, engine_kwargs={"table_dtype": table})
+            assert m.engine.sweep_supported and m.engine.table_dtype == table
+            m.factorize(report=10 ** 9, max_iteration=sweeps - 1, detailed_report=False, rows_per_iteration="all")
+            out.append(m.evaluate_test_error())
+        res[table] = np.array(out)
+    r64, rtc = res[torch.float64], res["f32_tc"]
+    np.testing.assert_allclose(rtc[:, 0], r64[:, 0], rtol=1e-2)                   # test RMSE, seed by seed
+    assert np.abs(rtc[:, 1] - r64[:, 1]).max() <= 0.01                            # test error rate: 1 % absolute
+    ref = z["ref_test_rsme"][:len(seeds)]
+    d = rtc[:, 0] - ref
+    assert d.mean() <= 0.01 * ref.mean() + 3.0 * d.std(ddof=1) / np.sqrt(len(d)), (rtc[:, 0].tolist(), ref.tolist())
