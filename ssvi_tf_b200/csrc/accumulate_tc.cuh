@@ -42,13 +42,14 @@ __host__ __device__ constexpr int tc_cta_smem(int NOTH, bool RING) {
   return 4 * TC_TILE_BYTES + SSVI_TC_U_BYTES(4) + tc_ring_bytes(NOTH, RING) + 256;
 }
 
-// PF: items (1 KB of each record) a warp keeps in flight ahead of the one it works on, in a static ring of PF + 1 register
-// buffers (2 NT must be a multiple of PF + 1 so that every entry starts at buffer 0).  PF == 1: 168 registers, three CTAs
-// per SM.  PF > 1: ~200 registers, two CTAs per SM, each warp with PF KB per record in flight.
-__host__ __device__ constexpr int tc_deep_pf(int NT) { return NT == 3 ? 2 : (NT == 1 ? 1 : 3); }
+// PF: register buffers for table items (1 KB of each record) = items a warp has in flight: item it of ANY entry lives in
+// buffer it % PF (2 NT is a multiple of PF), and as soon as the Hadamard product has consumed an item its buffer is
+// refilled with item it + PF (of the next entry at the end).  PF == 2: 168 registers, three CTAs per SM.  PF > 2
+// (SSVI_TUNE_TC_PF): ~200 registers, two CTAs per SM.
+__host__ __device__ constexpr int tc_deep_pf(int NT) { return NT == 3 ? 3 : (NT == 1 ? 2 : 4); }
 
-template <int NT, int NOTH, bool RING, int PF = 1>
-__global__ void __launch_bounds__(128, (RING || PF > 1) ? 2 : 3) accumulate_tc_kernel(
+template <int NT, int NOTH, bool RING, int PF = 2>
+__global__ void __launch_bounds__(128, (RING || PF > 2) ? 2 : 3) accumulate_tc_kernel(
     DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
     const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
     const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
@@ -187,8 +188,8 @@ __global__ void __launch_bounds__(128, (RING || PF > 1) ? 2 : 3) accumulate_tc_k
   for (int cc = 0; cc < 32; ++cc) gacc[cc] = 0.f;
 #pragma unroll
   for (int i = 0; i < NT; ++i) dacc[i] = 0.f;
-  constexpr int R = RING ? 1 : PF + 1;                  // register buffers: item it of ANY entry lives in rb[it % R]
-  static_assert(RING || NI % R == 0, "2 NT must be a multiple of PF + 1");
+  constexpr int R = RING ? 1 : PF;                      // register buffers: item it of ANY entry lives in rb[it % R]
+  static_assert(RING || NI % R == 0, "2 NT must be a multiple of PF");
   float4 rb[R][NOTH][2];
   bool have_cur = false;                                // items 0 .. PF-1 of the entry about to be processed are in flight
   float w_prev = 0.f;
@@ -236,11 +237,11 @@ __global__ void __launch_bounds__(128, (RING || PF > 1) ? 2 : 3) accumulate_tc_k
         }
         if (!RING && !have_cur) {
 #pragma unroll
-          for (int d = 0; d < PF; ++d)
+          for (int d = 0; d < R; ++d)
 #pragma unroll
             for (int jj = 0; jj < NOTH; ++jj) {
-              rb[d % R][jj][0] = __ldcg(pc[jj] + (d * 2) * 32);
-              rb[d % R][jj][1] = __ldcg(pc[jj] + (d * 2 + 1) * 32);
+              rb[d][jj][0] = __ldcg(pc[jj] + (d * 2) * 32);
+              rb[d][jj][1] = __ldcg(pc[jj] + (d * 2 + 1) * 32);
             }
         }
         float fp[2][8], rs[NT];
@@ -260,14 +261,6 @@ __global__ void __launch_bounds__(128, (RING || PF > 1) ? 2 : 3) accumulate_tc_k
               cur[jj][0] = rp[jj * 64];
               cur[jj][1] = rp[jj * 64 + 32];
             }
-          } else {                                      // item it + PF (of the next entry at the end) -> its buffer
-            const int nit = it + PF;
-#pragma unroll
-            for (int jj = 0; jj < NOTH; ++jj) {
-              const float4* p = (nit < NI) ? pc[jj] + (nit * 2) * 32 : pn[jj] + ((nit - NI) * 2) * 32;
-              rb[nit % R][jj][0] = __ldcg(p);
-              rb[nit % R][jj][1] = __ldcg(p + 32);
-            }
           }
           float x[8] = {cur[0][0].x, cur[0][0].y, cur[0][0].z, cur[0][0].w, cur[0][1].x, cur[0][1].y, cur[0][1].z, cur[0][1].w};
 #pragma unroll
@@ -278,6 +271,14 @@ __global__ void __launch_bounds__(128, (RING || PF > 1) ? 2 : 3) accumulate_tc_k
           if constexpr (RING) {                         // every lane's reads of the stage have returned: refill it
             __syncwarp();
             top_up(q * NI + it + 1, lim);
+          } else {                                      // the buffer is free: item it + PF (of the next entry at the end)
+            const int nit = it + PF;
+#pragma unroll
+            for (int jj = 0; jj < NOTH; ++jj) {
+              const float4* p = (nit < NI) ? pc[jj] + (nit * 2) * 32 : pn[jj] + ((nit - NI) * 2) * 32;
+              cur[jj][0] = __ldcg(p);
+              cur[jj][1] = __ldcg(p + 32);
+            }
           }
           const float4 u0 = Uf[(it * 2) * 32 + lane], u1 = Uf[(it * 2 + 1) * 32 + lane];
           const float uu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};

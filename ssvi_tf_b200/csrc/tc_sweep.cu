@@ -25,9 +25,9 @@ static int launch_tc(const DevView& v, const MemoView& mv, int64_t n_chunks, con
 #define TC_L(RING_, PF_)                                                                                                 \
   launch_tc1<NT, NOTH, RING_, PF_>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, \
                                    z_own, z_f32, partial_out, st)
-  if (v.tuning & SSVI_TUNE_TC_RING) return TC_L(true, 1);
+  if (v.tuning & SSVI_TUNE_TC_RING) return TC_L(true, 2);
   if (v.tuning & SSVI_TUNE_TC_PF) return TC_L(false, tc_deep_pf(NT));
-  return TC_L(false, 1);
+  return TC_L(false, 2);
 #undef TC_L
 }
 
