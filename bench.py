@@ -74,6 +74,7 @@ SIDE_RUNS = [
     # the fp32 ARITHMETIC option (SSVI_TABLE_F32_TC, tolerance 1e-4): V, f in fp32, contraction on the tcgen05 tensor cores
     ("c5_f32_tensor_core", "c5", 1.0, {"table_tc": True}),
     ("c2_f32_tensor_core", "c2", 1.0, {"table_tc": True}),
+    ("c2_rank50_f32_tensor_core", "c2", 1.0, {"rank": 50, "table_tc": True}),
 ]
 
 
@@ -323,7 +324,7 @@ class Workload(object):
                                       kernel_path=kernel_path),
                                  quadrature=quadrature)
         self.eng = self.model.engine
-        self.table_tc = bool(table_tc) and self.eng.sweep_supported and not c["diag"] and c["D"] <= 32 and c["model"] == "d"
+        self.table_tc = bool(table_tc) and self.eng.sweep_supported and not c["diag"] and c["D"] <= 64 and c["model"] == "d"
         self.N = self.model.order
         n = torch.tensor([self.eng.nnz], device=device, dtype=torch.int64)
         if sharded and world > 1:
@@ -428,10 +429,11 @@ class Workload(object):
         if c["diag"]:
             return "accumulate_diag_lin_kernel" if c["model"] == "simple" and c["lik"] == "normal" else \
                 ("accumulate_diag_d_kernel" if c["model"] == "d" else "accumulate_diag_kernel")
+        if self.table_tc:
+            return "accumulate_tc_kernel (tcgen05 contraction; + sample_table_kernel)" if c["D"] <= 32 else \
+                "accumulate_tc_wide_kernel (tcgen05 contraction, two warps per entry; + sample_table_wide_kernel)"
         if c["D"] > 32:
             return "accumulate_wide_kernel (+ sample_table_wide_kernel)"
-        if self.table_tc:
-            return "accumulate_tc_kernel (tcgen05 contraction; + sample_table_kernel)"
         return "accumulate_memo_kernel (+ sample_table_kernel)" if c["model"] == "d" else \
             "memo_weights_kernel (+ memo_f / memo_c / sample_table kernels)"
 

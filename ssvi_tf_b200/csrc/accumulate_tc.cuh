@@ -386,3 +386,302 @@ __global__ void __launch_bounds__(128, (RING || PF > 2) ? 2 : 3) accumulate_tc_k
   __syncthreads();
   if (warp == 0) tc_tmem_dealloc(tmem, 128);
 }
+
+// =====================================================================================================================
+// Ranks 33..64 (NT = 5..8 row tiles; the reference's real-data default is rank 50, real_test.py:27): the same pipeline
+// with TWO warps per entry.  An entry's V is 64 rows x 64 samples, so a 128-row operand tile holds two entries ("pair"
+// p = entries 2p, 2p + 1) and the M = N = 128 accumulator carries their V V^T in its two diagonal 64 x 64 blocks.  Warp
+// w = 2e + h works on entry slot e and on the entry's rows 32h .. 32h + 31 (row groups 4h .. min(4h + 4, NT) - 1): it
+// gathers only those rows of the records, writes tile rows 32w .. 32w + 31 exactly as the narrow kernel does, and sums
+// f over ITS rows; the two partial f vectors meet in shared memory across a 64-thread named barrier, after which both
+// warps evaluate the (identical) weights.  Each warp folds its 32 x 64 block of the accumulator (64 registers).
+// 82 KB of shared memory, <= 255 registers: two CTAs per SM.
+// =====================================================================================================================
+__host__ __device__ constexpr int tc_wide_smem() { return 4 * TC_TILE_BYTES + 16384 + 2 * 4 * 64 * 4 + 256; }
+
+template <int NT, int NOTH>
+__global__ void __launch_bounds__(128, 2) accumulate_tc_wide_kernel(
+    DevView v, MemoView mv, int64_t n_chunks, const int32_t* __restrict__ chunk_row,
+    const int64_t* __restrict__ chunk_start, const int32_t* __restrict__ chunk_len,
+    const int32_t* __restrict__ chunk_slot, const int64_t* __restrict__ chunk_out,
+    const int64_t* __restrict__ entry_ids, const int64_t* __restrict__ rows, const void* __restrict__ z_own,
+    int z_f32, double* __restrict__ partial_out) {
+  static_assert(NT >= 5 && NT <= 8, "two warps per entry: 33 <= D <= 64");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  unsigned char* smem = smem_raw;
+  constexpr int KT = SSVI_MEMO_KT, REC4 = NT * 2 * 2 * 32;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2;
+  const int r8 = lane & 7, kq = lane >> 3;
+  const int e = warp >> 1, h = warp & 1;                // entry slot of the pair, half of the entry's rows
+  const int ngw = h ? NT - 4 : 4;                       // row groups of this warp, 2 items (k halves) each
+  const int nil = 2 * ngw;
+  const int64_t c = blockIdx.x;
+  if (c >= n_chunks) return;
+  const int N = v.N, D = v.D, NS = smp_ns(D);
+  const int64_t row = rows[chunk_row[c]];
+  const int64_t start = chunk_start[c];
+  const int len = chunk_len[c], slot = chunk_slot[c];
+  const int sl = slot - mv.slot_lo;
+  const int np = (len + 1) >> 1;
+
+  unsigned char* tiles = smem;                                     // [buffer][hi | lo][16 KB]
+  float* Uf = reinterpret_cast<float*>(smem + 4 * TC_TILE_BYTES);  // U / a, NT row groups in the table's record order
+  float* fx = reinterpret_cast<float*>(smem + 4 * TC_TILE_BYTES + 16384);   // [2][4 warps][64] partial f of the pair's halves
+  uint64_t* done = reinterpret_cast<uint64_t*>(smem + 4 * TC_TILE_BYTES + 16384 + 2048);
+  uint32_t* holder = reinterpret_cast<uint32_t*>(done + 1);
+  uint32_t* cnt = holder + 1;
+  double* S = reinterpret_cast<double*>(smem);          // prologue staging (<= 51 KB at D = 64), aliased on the tiles
+  double* zs = S + v.srow_len;
+
+  if (tid == 0) {
+    cnt[0] = cnt[1] = 0;
+    tc_mbar_init(done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (warp == 0) tc_tmem_alloc(holder, 128);
+
+  const int my_cnt = (len - e + 1) >> 1;                // entries of this warp's slot: e, e + 2, ...
+  double my_y = 0.0;
+  int32_t my_rec[NOTH];
+  auto load_batch = [&](int p0) {
+    my_y = 0.0;
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = 0;
+    const int b = 2 * (p0 + lane) + e;
+    if (b < len) {
+      const int64_t eid = __ldcs(entry_ids + start + b);
+      my_y = __ldcs(v.vals + eid);
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) my_rec[jj] = (int32_t)memo_rec(mv, jj, sl, __ldcs(v.coords + eid * N + mv.od[jj]));
+    }
+  };
+  load_batch(0);
+
+  // ---- prologue: U(row, slot) = m + L z_own, once per CTA, written straight into the record order as floats / a ------------
+  {
+    const double2* src = reinterpret_cast<const double2*>(v.sampler[v.dim] + row * (int64_t)v.srow_len);
+    double2* dst = reinterpret_cast<double2*>(S);
+    for (int i = tid; i < (v.srow_len >> 1); i += 128) dst[i] = src[i];
+    if (z_f32) {
+      const float* zsrc = reinterpret_cast<const float*>(z_own) + (int64_t)slot * v.zblk;
+      for (int i = tid; i < v.zblk; i += 128) zs[i] = (double)zsrc[i];
+    } else {
+      const double* zsrc = reinterpret_cast<const double*>(z_own) + (int64_t)slot * v.zblk;
+      for (int i = tid; i < v.zblk; i += 128) zs[i] = zsrc[i];
+    }
+  }
+  __syncthreads();
+  const float alpha = mv.tc_alpha;
+  const double inv_alpha = 1.0 / (double)alpha;
+  for (int i = 0; i < NT; ++i)
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      double c0, c1;
+      const int t = warp + 4 * hh;
+      mma_sample_tile(S, zs, NT, NS, lane, g, i, t, c0, c1);          // x[8i + g][8t + 2q + {0,1}], q = lane & 3
+      *reinterpret_cast<float2*>(Uf + tc_rec_index(8 * i + g, 8 * t + 2 * (lane & 3))) =
+          make_float2((float)(c0 * inv_alpha), (float)(c1 * inv_alpha));
+    }
+  tc_fence_before();
+  __syncthreads();                                      // U complete; staging dead: the region becomes the operand tiles
+  tc_fence_after();
+  const uint32_t tmem = *holder;
+
+  // ---- main loop -----------------------------------------------------------------------------------------------------
+  const float4* tab4 = reinterpret_cast<const float4*>(mv.tab);
+  const float4* Uf4 = reinterpret_cast<const float4*>(Uf);
+  const double inv_k1 = 1.0 / (double)(8 * KT);
+  const uint32_t idesc = tc_idesc_f16(128, 128);
+  float gacc[64], dacc[4];
+#pragma unroll
+  for (int cc = 0; cc < 64; ++cc) gacc[cc] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) dacc[i] = 0.f;
+  float4 rb[2][NOTH][2];                                // item it of ANY entry lives in rb[it & 1] (nil is even)
+  bool have_cur = false;
+  float w_prev = 0.f;
+  bool prev_valid = false;
+
+  auto fold = [&](int p) {
+    tc_mbar_wait(done, p & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int part = 0; part < 4; ++part) {
+      float d[16];
+      tc_tmem_ld16(tmem + ((uint32_t)(32 * warp) << 16) + 64 * e + 16 * part, d);
+      if (prev_valid) {
+#pragma unroll
+        for (int cc = 0; cc < 16; ++cc) gacc[16 * part + cc] = fmaf(w_prev, d[cc], gacc[16 * part + cc]);
+      }
+    }
+    tc_fence_before();
+  };
+
+  for (int p = 0; p < np; ++p) {
+    const int buf = p & 1;
+    float w_b = 0.f;
+    const bool valid = 2 * p + e < len;                 // uniform over the pair of warps
+    unsigned char* thi = tiles + (buf * 2) * TC_TILE_BYTES;
+    unsigned char* tlo = thi + TC_TILE_BYTES;
+    if (valid) {
+      const int el = p & 31;
+      if (el == 0 && p > 0) {
+        load_batch(p);
+        have_cur = false;
+      }
+      const double y = __shfl_sync(0xffffffffu, my_y, el);
+      const bool next_valid = (el + 1 < 32) && (2 * (p + 1) + e < len);
+      const float4* pc[NOTH];
+      const float4* pn[NOTH];
+#pragma unroll
+      for (int jj = 0; jj < NOTH; ++jj) {               // this warp's rows start at row group 4h: item 8h of the record
+        pc[jj] = tab4 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], el) * REC4 + (8 * h) * 64 + lane;
+        pn[jj] = tab4 + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], next_valid ? el + 1 : el) * REC4 + (8 * h) * 64 + lane;
+      }
+      if (!have_cur) {
+#pragma unroll
+        for (int d = 0; d < 2; ++d)
+#pragma unroll
+          for (int jj = 0; jj < NOTH; ++jj) {
+            rb[d][jj][0] = __ldcg(pc[jj] + (d * 2) * 32);
+            rb[d][jj][1] = __ldcg(pc[jj] + (d * 2 + 1) * 32);
+          }
+      }
+      float fp[2][8], rs[4];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) fp[0][j] = fp[1][j] = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) rs[i] = 0.f;
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        if (it < nil) {                                 // warp-uniform
+          const int rgl = it >> 1, hh = it & 1;
+          float4 (&cur)[NOTH][2] = rb[it & 1];
+          float x[8] = {cur[0][0].x, cur[0][0].y, cur[0][0].z, cur[0][0].w, cur[0][1].x, cur[0][1].y, cur[0][1].z, cur[0][1].w};
+#pragma unroll
+          for (int jj = 1; jj < NOTH; ++jj) {
+            x[0] *= cur[jj][0].x; x[1] *= cur[jj][0].y; x[2] *= cur[jj][0].z; x[3] *= cur[jj][0].w;
+            x[4] *= cur[jj][1].x; x[5] *= cur[jj][1].y; x[6] *= cur[jj][1].z; x[7] *= cur[jj][1].w;
+          }
+          {                                             // the buffer is free: item it + 2 (of the next entry at the end)
+            const int nit = it + 2;
+#pragma unroll
+            for (int jj = 0; jj < NOTH; ++jj) {
+              const float4* q4 = (nit < nil) ? pc[jj] + (nit * 2) * 32 : pn[jj] + ((nit - nil) * 2) * 32;
+              cur[jj][0] = __ldcg(q4);
+              cur[jj][1] = __ldcg(q4 + 32);
+            }
+          }
+          const float4 u0 = Uf4[((8 * h + it) * 2) * 32 + lane], u1 = Uf4[((8 * h + it) * 2 + 1) * 32 + lane];
+          const float uu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+          float s = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            fp[hh][j] = fmaf(uu[j], x[j], fp[hh][j]);
+            s += x[j];
+          }
+          rs[rgl] += s;
+          tc_store_split8(thi, tlo, 32 * warp + 8 * rgl + r8, kq + 4 * hh, x);
+        }
+      }
+      have_cur = next_valid;
+      // partial f over this warp's rows -> lane (hb, jb, jc | kq) holds samples k = 8 (kq + 4 hb) + 4 jb + 2 jc + {0, 1}
+      const bool hb = (lane >> 2) & 1, jb = (lane >> 1) & 1, jc = lane & 1;
+      float s8[8], s4[4], f[2];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s8[j] = (hb ? fp[1][j] : fp[0][j]) + __shfl_xor_sync(0xffffffffu, hb ? fp[0][j] : fp[1][j], 4);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) s4[j] = (jb ? s8[4 + j] : s8[j]) + __shfl_xor_sync(0xffffffffu, jb ? s8[j] : s8[4 + j], 2);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) f[j] = (jc ? s4[2 + j] : s4[j]) + __shfl_xor_sync(0xffffffffu, jc ? s4[j] : s4[2 + j], 1);
+      // the other half of the entry's rows: the partner warp's partial, through shared memory (double-buffered by pair)
+      float2* mine = reinterpret_cast<float2*>(fx + ((p & 1) * 4 + warp) * 64) + lane;
+      const float2* theirs = reinterpret_cast<const float2*>(fx + ((p & 1) * 4 + (warp ^ 1)) * 64) + lane;
+      *mine = make_float2(f[0], f[1]);
+      if (e == 0) asm volatile("bar.sync 1, 64;\n" ::: "memory");      // the pair's own named barrier (ids fixed at compile
+      else asm volatile("bar.sync 2, 64;\n" ::: "memory");             // time: a register id would reserve all sixteen)
+      const float2 o = *theirs;
+      const float f0 = h ? o.x + f[0] : f[0] + o.x, f1 = h ? o.y + f[1] : f[1] + o.y;   // same order in both warps
+      // ---- SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1 (both warps of the pair evaluate the same numbers) ---
+      double a0, b0, a1, b1;
+      log_pdf_derivs_pair(v.lik, y, (double)f0, (double)f1, v.lik_param, a0, b0, a1, b1);
+      double sum_a = a0 + a1, sum_d = b0 + b1;
+      warp_sum2(sum_a, sum_d, lane);
+      const float aw = (float)(sum_a * inv_k1 * inv_k1 * inv_alpha);
+      w_b = (float)(0.5 * sum_d * inv_k1 * inv_k1);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float s = rs[i];
+        s += __shfl_xor_sync(0xffffffffu, s, 8);
+        s += __shfl_xor_sync(0xffffffffu, s, 16);
+        dacc[i] = fmaf(aw, s, dacc[i]);
+      }
+    }
+    if (p > 0) fold(p - 1);
+    tc_fence_async_smem();
+    tc_fence_before();
+    __syncwarp();
+    uint32_t last = 0;
+    if (lane == 0) last = (tc_arrive_count(&cnt[buf]) & 3u) == 3u;
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (last) {
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t ahi = tc_smem_u32(thi), alo = tc_smem_u32(tlo);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          const uint64_t dh = tc_smem_desc(ahi + 256 * s, TC_LBO, TC_SBO), dl = tc_smem_desc(alo + 256 * s, TC_LBO, TC_SBO);
+          tc_mma_f16(tmem, dh, dh, idesc, s > 0);
+          tc_mma_f16(tmem, dh, dl, idesc, 1);
+          tc_mma_f16(tmem, dl, dh, idesc, 1);
+        }
+        tc_commit(done);
+      }
+      __syncwarp();
+    }
+    w_prev = w_b;
+    prev_valid = valid;
+  }
+  if (np > 0) fold(np - 1);
+
+  // ---- CTA reduction and the chunk record [di | Di | si_sum | count] -------------------------------------------------
+  __syncthreads();
+  float* red = reinterpret_cast<float*>(tiles);         // [4 warps][32 lanes][65]
+  float* dred = red + 4 * 32 * 65;                      // [4 warps][32]
+#pragma unroll
+  for (int cc = 0; cc < 64; ++cc) red[(warp * 32 + lane) * 65 + cc] = gacc[cc];
+  if (kq == 0) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dred[warp * 32 + 8 * i + r8] = dacc[i];
+  }
+  __syncthreads();
+  double* out = partial_out + chunk_out[c] * (int64_t)v.acc_len;
+  const double ia2 = 1.0 / ((double)alpha * (double)alpha);
+  bool bad = false;
+  for (int n = tid; n < D; n += 128) {                  // row n: half n >> 5, lane n & 31 of the warps 0 + half and 2 + half
+    const int hh = n >> 5, l = n & 31;
+    const float x = dred[hh * 32 + l] + dred[(2 + hh) * 32 + l];
+    __stcs(out + n, (double)x);
+    bad |= !isfinite(x);
+  }
+  for (int i = tid; i < 64 * 64; i += 128) {
+    const int n1 = i >> 6, n2 = i & 63;
+    if (n1 < D && n2 <= n1) {                           // lower triangle incl. diagonal, mirrored: exactly symmetric
+      const int hh = n1 >> 5, l = n1 & 31;
+      const float x = red[(hh * 32 + l) * 65 + n2] + red[((2 + hh) * 32 + l) * 65 + n2];
+      const double xd = ia2 * (double)x;
+      __stcs(out + D + n1 * D + n2, xd);
+      __stcs(out + D + n2 * D + n1, xd);
+      bad |= !isfinite(x);
+    }
+  }
+  if (bad) atomicOr(v.flags, SSVI_FLAG_NONFINITE_ACC | SSVI_FLAG_TC_RANGE);
+  if (tid == 0) {
+    out[D + D * D] = 0.0;
+    out[D + D * D + 1] = (double)len;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc_tmem_dealloc(tmem, 128);
+}

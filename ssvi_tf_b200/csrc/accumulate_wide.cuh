@@ -73,6 +73,16 @@ __global__ void __launch_bounds__(128) sample_table_wide_kernel(DevView v, MemoV
       for (int t = 0; t < 8; ++t)
         if (t < KT) dmma_m8n8k4(c[t][0], c[t][1], a, zs[(t * NS + jx) * 32 + lane]);
     }
+    if (mv.tab32 == 2) {                                // SSVI_TABLE_F32_TC: floats in the tensor-core path's order
+      float* outf = reinterpret_cast<float*>(mv.tab) + memo_rec(mv, jj, sl, j) * (int64_t)mv.rec_len;
+      const double a = jj == 0 ? (double)mv.tc_alpha : 1.0;
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+        if (t < KT)
+          *reinterpret_cast<float2*>(outf + tc_rec_index(8 * i + g, 8 * t + 2 * (lane & 3))) =
+              make_float2((float)(a * c[t][0]), (float)(a * c[t][1]));
+      continue;
+    }
 #pragma unroll
     for (int t = 0; t < 8; ++t)
       if (t < KT) out[(i * KT + t) * 32 + lane] = make_double2(c[t][0], c[t][1]);

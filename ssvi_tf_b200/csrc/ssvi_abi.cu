@@ -307,12 +307,14 @@ static bool sweep_full_ok(const SsviConfig& c) {
          c.k1 == 8 * SSVI_MEMO_KT && c.order >= 2 && c.order - 1 <= SSVI_MEMO_MAX_OTH && c.kernel_path != 1;
 }
 // the float table is built for the kernels of SSVI_TF_d (the three-pass path of simple / robust keeps doubles)
-static bool table_f32(const SsviConfig& c) {
-  return (c.table_dtype == SSVI_TABLE_F32 || c.table_dtype == SSVI_TABLE_F32_TC) && c.model == SSVI_MODEL_D &&
-         c.cov_kind == SSVI_COV_FULL && c.rank <= 32;
+// ... or in the tensor-core path's order, for accumulate_tc[_wide]_kernel (fp32 arithmetic, tcgen05 contraction; rank <= 64)
+static bool table_tc(const SsviConfig& c) {
+  return c.table_dtype == SSVI_TABLE_F32_TC && c.model == SSVI_MODEL_D && c.cov_kind == SSVI_COV_FULL && c.rank <= 64;
 }
-// ... and in the tensor-core path's order, for accumulate_tc_kernel (fp32 arithmetic, tcgen05 contraction)
-static bool table_tc(const SsviConfig& c) { return table_f32(c) && c.table_dtype == SSVI_TABLE_F32_TC; }
+static bool table_f32(const SsviConfig& c) {
+  return table_tc(c) || ((c.table_dtype == SSVI_TABLE_F32 || c.table_dtype == SSVI_TABLE_F32_TC) && c.model == SSVI_MODEL_D &&
+                         c.cov_kind == SSVI_COV_FULL && c.rank <= 32);
+}
 static bool sweep_ok(const SsviHandle* h) { return sweep_full_ok(h->cfg) || sweep_diag_ok(h->cfg, h->max_smem_optin); }
 
 extern "C" int ssvi_sweep_supported(const SsviHandle* h) { return (h && sweep_ok(h)) ? 1 : 0; }
@@ -444,6 +446,11 @@ static int launch_sweep_wide(SsviHandle* h, const DevView& v, const MemoView& mv
   }
   if (n_chunks == 0) return SSVI_OK;
   const int z_f32 = sizeof(ZT) == 4;
+  if (mv.tab32 == 2) {                                  // SSVI_TABLE_F32_TC: tc_sweep.cu (two warps per entry)
+    CUDA_TRY(h, (cudaError_t)ssvi_launch_accumulate_tc(v, mv, nt, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot,
+                                                       chunk_out, entry_ids, rows, h->z_own, z_f32, partial_out, st));
+    return SSVI_OK;
+  }
   const size_t smem = (size_t)wide_cta_smem(nt, v.D);
   if (smem > (size_t)h->max_smem_optin) return fail(h, SSVI_E_INVALID, "sweep_accumulate: shared memory%s");
 #define SSVI_WIDE_LAUNCH(NT_, NOTH_)                                                                               \

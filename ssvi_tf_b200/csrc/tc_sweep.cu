@@ -31,6 +31,20 @@ static int launch_tc(const DevView& v, const MemoView& mv, int64_t n_chunks, con
 #undef TC_L
 }
 
+template <int NT, int NOTH>
+static int launch_tc_wide(const DevView& v, const MemoView& mv, int64_t n_chunks, const int32_t* chunk_row,
+                          const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
+                          const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own,
+                          int z_f32, double* partial_out, cudaStream_t st) {
+  auto kern = accumulate_tc_wide_kernel<NT, NOTH>;
+  constexpr int smem = tc_wide_smem();
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return (int)e;
+  kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, mv, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
+                                              entry_ids, rows, z_own, z_f32, partial_out);
+  return (int)cudaGetLastError();
+}
+
 int ssvi_launch_accumulate_tc(const DevView& v, const MemoView& mv, int nt, int64_t n_chunks, const int32_t* chunk_row,
                               const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
                               const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own,
@@ -42,12 +56,23 @@ int ssvi_launch_accumulate_tc(const DevView& v, const MemoView& mv, int nt, int6
     case 2: return launch_tc<NT_, 2>(TC_ARGS);       \
     default: return launch_tc<NT_, 3>(TC_ARGS);      \
   }
+#define TC_WIDE(NT_)                                                                                            \
+  switch (mv.n_oth) {                                                                                           \
+    case 1: return launch_tc_wide<NT_, 1>(TC_ARGS);                                                             \
+    case 2: return launch_tc_wide<NT_, 2>(TC_ARGS);                                                             \
+    default: return launch_tc_wide<NT_, 3>(TC_ARGS);                                                            \
+  }
   switch (nt) {
     case 1: TC_NT(1)
     case 2: TC_NT(2)
     case 3: TC_NT(3)
-    default: TC_NT(4)
+    case 4: TC_NT(4)
+    case 5: TC_WIDE(5)
+    case 6: TC_WIDE(6)
+    case 7: TC_WIDE(7)
+    default: TC_WIDE(8)
   }
+#undef TC_WIDE
 #undef TC_NT
 #undef TC_ARGS
 }

@@ -2,7 +2,7 @@
 #pragma once
 #include "accumulate_memo.cuh"
 
-// Returns a cudaError_t as int.  nt = ceil(D / 8) in 1..4, mv.n_oth in 1..3, mv.tab32 == 2.
+// Returns a cudaError_t as int.  nt = ceil(D / 8) in 1..8 (5..8: two warps per entry), mv.n_oth in 1..3, mv.tab32 == 2.
 int ssvi_launch_accumulate_tc(const DevView& v, const MemoView& mv, int nt, int64_t n_chunks, const int32_t* chunk_row,
                               const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
                               const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own,

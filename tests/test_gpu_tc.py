@@ -34,6 +34,12 @@ def _run(cfg, dims, coords, vals, st0, pool, dim, W, table_dtype, blocks=0, **kw
     ([40, 3, 3], 12, "poisson", 1, 200),      # chunks longer than 128 entries: the 32-quad batches roll over
     ([7, 9], 7, "bernoulli", 2, 4),           # one other mode, one row group
     ([3, 30, 30], 32, "bernoulli", 2, 1000),  # rows of ~360 entries in one chunk: many quads through both buffers
+    # ranks 33..64: two warps per entry (accumulate_tc_wide_kernel)
+    ([6, 5, 4], 50, "bernoulli", 3, 64),      # the reference's real-data default rank (NT = 7: the upper warp has 3 groups)
+    ([5, 4, 4], 64, "normal", 2, 3),          # NT = 8, segments of 3 entries (odd pairs)
+    ([4, 3, 3, 3], 33, "normal", 3, 64),      # NT = 5 (one row group in the upper half), three other modes
+    ([40, 3, 3], 40, "poisson", 1, 200),      # NT = 5, chunks longer than 64 entries: the 32-pair batches roll over
+    ([7, 9], 48, "bernoulli", 2, 5),          # NT = 6, one other mode
 ])
 def test_tensor_core_sweep_is_within_the_fp32_tolerance(dims, D, lik, P, W, capsys):
     rng = np.random.default_rng(D * 131 + P)
@@ -61,7 +67,9 @@ def test_tensor_core_sweep_is_within_the_fp32_tolerance(dims, D, lik, P, W, caps
             entries.append((coords[ids], vals[ids]))
         want = so.copy_state(st0)
         so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
-        assert_state_close(state_tc, want, cfg, 1e-4, what="tensor-core sweep, dims=%s mode %d" % (dims, dim))
+        # fp32 bar: 1e-4 relative; elements below 1 % of an array's largest are held to 1e-6 of that scale (an fp32 product
+        # of three samples cannot do better on a near-zero covariance element)
+        assert_state_close(state_tc, want, cfg, 1e-4, what="tensor-core sweep, dims=%s mode %d" % (dims, dim), atol_frac=1e-2)
         try:                                             # informational: does the update also meet the fp64 bar?
             assert_state_close(state_tc, want, cfg, 1e-5)
         except AssertionError:
