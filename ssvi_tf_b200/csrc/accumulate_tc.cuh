@@ -441,7 +441,6 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_wide_kernel(
   }
   if (warp == 0) tc_tmem_alloc(holder, 128);
 
-  const int my_cnt = (len - e + 1) >> 1;                // entries of this warp's slot: e, e + 2, ...
   double my_y = 0.0;
   int32_t my_rec[NOTH];
   auto load_batch = [&](int p0) {
