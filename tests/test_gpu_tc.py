@@ -170,3 +170,38 @@ def test_nation_full_sweeps_with_the_tensor_core_option(tmp_path):
     ref = z["ref_test_rsme"][:len(seeds)]
     d = rtc[:, 0] - ref
     assert d.mean() <= 0.01 * ref.mean() + 3.0 * d.std(ddof=1) / np.sqrt(len(d)), (rtc[:, 0].tolist(), ref.tolist())
+
+
+@pytest.mark.parametrize("cfg_id,scale,kwargs", [
+    ("c2", 1.0, {}),                                      # config 2 at FULL size: 8e6 train entries, rank 20 (NT = 3)
+    ("c5", 0.01, dict(sweep_tile_blocks=2)),              # config 5's 10k^3 index space, rank 32, L2-tiled launch order
+    ("c2", 0.25, dict(rank=50)),                          # the reference's real-data default rank on config 2's tensor
+])
+def test_tensor_core_sweep_at_baseline_sizes_matches_the_fp64_direct_kernel(cfg_id, scale, kwargs):
+    """At BASELINE.json's sizes the oracle cannot follow; the tensor-core sweep is compared with the fp64 direct-evaluation
+    kernel (pinned to the oracle and the reference's fixtures at small sizes) on a sample of rows of every mode, with the
+    bench's float noise pool: within 2e-5 of the largest accumulator element, counts bit-exact over ALL rows."""
+    import bench
+    kwargs = dict(kwargs)
+    rank = kwargs.pop("rank", None)
+    c = bench.CONFIGS[cfg_id]
+    if rank:
+        c = dict(c, D=rank)
+    data = bench.DeviceTensorData(c, "cuda", 319 + int(cfg_id[1]), scale)
+    m = bench.build_model(c, data, "cuda", None, 16, 128, engine_kwargs=dict(kwargs, table_dtype="f32_tc"))
+    m.fresh_noise()
+    eng = m.engine
+    assert eng.sweep_supported and eng.table_dtype == "f32_tc"
+    rng = np.random.default_rng(36)
+    for dim in range(eng.N):
+        acc = eng.accumulate(eng.plan_sweep(dim)).clone()
+        eng.check_flags()
+        lens = np.diff(np.asarray(eng.rowptr_h[dim]))
+        np.testing.assert_array_equal(acc[:, -1].cpu().numpy(), lens.astype(np.float64))
+        rows = np.sort(rng.choice(eng.dims[dim], 6, replace=False))
+        direct = eng.accumulate(eng.plan_full(dim, rows)).clone().cpu().numpy()
+        eng.check_flags()
+        got = acc[torch.as_tensor(rows, device=acc.device)].cpu().numpy()
+        np.testing.assert_allclose(got, direct, rtol=0, atol=2e-5 * np.abs(direct).max(),
+                                   err_msg="%s mode %d: tensor-core sweep vs direct rows" % (cfg_id, dim))
+    eng.close()
