@@ -29,10 +29,13 @@ struct MemoView {
   int32_t tab32;                          // 1: records hold FLOATS: [NT][KT/2][32] float4 = (x, y of k-tile 2p | x, y of 2p+1)
                                           // 2: floats in the tensor-core path's order (tc_rec_index, tc_ops.cuh)
   float tc_alpha;                         // tab32 == 2: power-of-two operand scale of the fp16 hi / lo split
-  int32_t od[SSVI_MEMO_MAX_OTH];          // other modes, ascending
-  int64_t n_rows[SSVI_MEMO_MAX_OTH];      // rows of each other mode
-  int64_t rec_base[SSVI_MEMO_MAX_OTH + 1];// first record of each other mode's block; [n_oth] = total records
-  int64_t blk_base[SSVI_MEMO_MAX_OTH + 1];// sample_table_kernel: first CTA of each other mode (8 rows of one slot per CTA)
+  int32_t own;                            // 1 (tab32 == 2): the table also holds the SWEPT mode's samples U(row, slot) / a as
+                                          // "mode" n_oth (noise block z_own), so a chunk's prologue is one record copy
+  int32_t n_modes;                        // n_oth + own: modes the sample-table kernels fill
+  int32_t od[SSVI_MEMO_MAX_OTH + 1];      // other modes, ascending (+ the swept mode when own)
+  int64_t n_rows[SSVI_MEMO_MAX_OTH + 1];  // rows of each of them
+  int64_t rec_base[SSVI_MEMO_MAX_OTH + 2];// first record of each mode's block; [n_modes] = total records
+  int64_t blk_base[SSVI_MEMO_MAX_OTH + 2];// sample_table_kernel: first CTA of each mode (8 rows of one slot per CTA); [n_modes] = grid
   double* tab;
 };
 
@@ -55,15 +58,17 @@ __host__ __device__ inline int sample_table_smem(int D, int k1) {
 }
 
 template <int NT, typename ZT>
-__global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView mv, const ZT* __restrict__ z_other) {
+__global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView mv, const ZT* __restrict__ z_other,
+                                                           const ZT* __restrict__ z_own) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2;
   const int D = v.D, k1 = v.k1, KT = k1 >> 3, NS = smp_ns(D);
   int jj = 0;
 #pragma unroll
-  for (int a = 1; a < SSVI_MEMO_MAX_OTH; ++a)
-    if (a < mv.n_oth && (int64_t)blockIdx.x >= mv.blk_base[a]) jj = a;
+  for (int a = 1; a <= SSVI_MEMO_MAX_OTH; ++a)
+    if (a < mv.n_modes && (int64_t)blockIdx.x >= mv.blk_base[a]) jj = a;
+  const bool own = jj == mv.n_oth;                                      // the swept mode's own samples (mv.own)
   const int64_t nblk = (mv.n_rows[jj] + 7) >> 3;                        // CTAs per slot of this mode
   const int64_t local = (int64_t)blockIdx.x - mv.blk_base[jj];
   const int sl = (int)(local / nblk);
@@ -73,7 +78,7 @@ __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView m
   double* zs = reinterpret_cast<double*>(smem_raw);
   double* S = zs + v.zblk + (size_t)warp * v.srow_len;
   {
-    const ZT* zsrc = z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
+    const ZT* zsrc = own ? z_own + (int64_t)slot * v.zblk : z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
     for (int i = tid; i < v.zblk; i += 256) zs[i] = (double)zsrc[i];
   }
   const bool live = j < mv.n_rows[jj];
@@ -92,7 +97,8 @@ __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView m
   const int64_t rec = memo_rec(mv, jj, sl, j);
   if (mv.tab32 == 2) {                                  // SSVI_TABLE_F32_TC: lane (g, q) holds x[8i + g][8t + 2q + {0,1}]
     float* out = reinterpret_cast<float*>(mv.tab) + rec * (int64_t)(NT * 8 * 64);
-    const double a = jj == 0 ? (double)mv.tc_alpha : 1.0;     // the first other mode's records carry the operand scale
+    // the first other mode's records carry the operand scale a, the swept mode's own samples 1 / a
+    const double a = own ? 1.0 / (double)mv.tc_alpha : (jj == 0 ? (double)mv.tc_alpha : 1.0);
 #pragma unroll
     for (int i = 0; i < NT; ++i)
 #pragma unroll

@@ -5,8 +5,9 @@
 // arithmetic.  The table holds float samples X(j, s) in the lane order of tc_rec_index (tc_ops.cuh).  One CTA (4 warps)
 // per chunk; warp w takes entries w, w + 4, ...  ("quad" q = the four entries 4q .. 4q + 3).  Per entry a warp
 //   * gathers the N - 1 records (two coalesced 16-byte loads per lane and item, one item ahead), forms V = Hadamard
-//     product in fp32 registers, f_k = u_k . v_k against the own-row sample U(row, slot) held in registers (evaluated once
-//     per CTA with the DMMA sequence of every other kernel), and the row sums SUM_k V[n][k]      (SSVI_TF_d.py:31-46);
+//     product in fp32 registers, f_k = u_k . v_k against the own-row sample U(row, slot) (a record of the table like the
+//     others: sample_table_kernel samples the swept mode too, so a chunk's prologue is one 8 KB copy into shared memory),
+//     and the row sums SUM_k V[n][k]                                                             (SSVI_TF_d.py:31-46);
 //   * writes rows 32 w .. 32 w + 31 of the quad's operand tile: a V split into fp16 hi + lo (22 significand bits), K-major,
 //     no swizzle, straight from registers;
 //   * evaluates the k1-averaged log-likelihood derivatives in fp64 (two samples per lane; quirk Q3) -> weights aw, dw.
@@ -59,11 +60,10 @@ __global__ void __launch_bounds__(128, (RING || PF > 2) ? 2 : 3) accumulate_tc_k
   unsigned char* smem = smem_raw;
   constexpr int KT = SSVI_MEMO_KT, NI = 2 * NT, REC4 = NT * 2 * 2 * 32;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = lane >> 2;
   const int r8 = lane & 7, kq = lane >> 3;
   const int64_t c = blockIdx.x;
   if (c >= n_chunks) return;
-  const int N = v.N, D = v.D, NS = smp_ns(D);
+  const int N = v.N, D = v.D;
   const int64_t row = rows[chunk_row[c]];
   const int64_t start = chunk_start[c];
   const int len = chunk_len[c], slot = chunk_slot[c];
@@ -79,10 +79,6 @@ __global__ void __launch_bounds__(128, (RING || PF > 2) ? 2 : 3) accumulate_tc_k
   uint64_t* rbar = done + 1 + warp * 4;                 // this warp's stage barriers (RS <= 4)
   uint32_t* holder = reinterpret_cast<uint32_t*>(done + 1 + 16);
   uint32_t* cnt = holder + 1;                           // [2] arrival counters of the operand-tile buffers
-  // the prologue's staging (sampler row + noise block as doubles) and U overlay the tiles, which are idle until the loop
-  double* S = reinterpret_cast<double*>(smem);
-  double* zs = S + v.srow_len;
-  double2* Us = reinterpret_cast<double2*>(smem + 2 * TC_TILE_BYTES);
 
   if (tid == 0) {
     cnt[0] = cnt[1] = 0;
@@ -133,45 +129,18 @@ __global__ void __launch_bounds__(128, (RING || PF > 2) ? 2 : 3) accumulate_tc_k
     }
   };
 
-  // ---- prologue: U(row, slot) = m + L z_own, once per CTA (ui samples, SSVI_TF_interface.py:251-254) --------------------
-  {
-    const double2* src = reinterpret_cast<const double2*>(v.sampler[v.dim] + row * (int64_t)v.srow_len);
-    double2* dst = reinterpret_cast<double2*>(S);
-    for (int i = tid; i < (v.srow_len >> 1); i += 128) dst[i] = src[i];
-    if (z_f32) {
-      const float* zsrc = reinterpret_cast<const float*>(z_own) + (int64_t)slot * v.zblk;
-      for (int i = tid; i < v.zblk; i += 128) zs[i] = (double)zsrc[i];
-    } else {
-      const double* zsrc = reinterpret_cast<const double*>(z_own) + (int64_t)slot * v.zblk;
-      for (int i = tid; i < v.zblk; i += 128) zs[i] = zsrc[i];
-    }
-  }
-  __syncthreads();                                      // (also: the mbarriers are initialised)
-  top_up(0, min(my_cnt, 32) * NI);                      // the first S items travel while U is sampled
-#pragma unroll
-  for (int i = 0; i < NT; ++i)
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      double c0, c1;
-      mma_sample_tile(S, zs, NT, NS, lane, g, i, warp + 4 * h, c0, c1);
-      Us[(i * KT + warp + 4 * h) * 32 + lane] = make_double2(c0, c1);
-    }
-  __syncthreads();
+  // ---- prologue: U(row, slot) / a (ui samples, SSVI_TF_interface.py:251-254) is a record of the table too (the swept mode
+  //      is sampled by sample_table_kernel as one more "mode", MemoView::own): one 2 NT KB copy per chunk instead of staging
+  //      the sampler row and the noise block and re-sampling U in every chunk of the (row, slot) pair ----------------------------
   const float alpha = mv.tc_alpha;
   const double inv_alpha = 1.0 / (double)alpha;
-  if (warp == 0) {                                      // lane (r8, kq): rows 8 rg + r8, samples 8 (kq + 4 h) + j of U / a
-#pragma unroll
-    for (int it = 0; it < NI; ++it) {
-      const int rg = it >> 1, h = it & 1;
-      const double2* up = Us + (rg * KT + kq + 4 * h) * 32 + r8 * 4;
-      const double2 x0 = up[0], x1 = up[1], x2 = up[2], x3 = up[3];
-      Uf[(it * 2) * 32 + lane] = make_float4((float)(x0.x * inv_alpha), (float)(x0.y * inv_alpha), (float)(x1.x * inv_alpha),
-                                             (float)(x1.y * inv_alpha));
-      Uf[(it * 2 + 1) * 32 + lane] = make_float4((float)(x2.x * inv_alpha), (float)(x2.y * inv_alpha),
-                                                 (float)(x3.x * inv_alpha), (float)(x3.y * inv_alpha));
-    }
+  {
+    const float4* usrc = reinterpret_cast<const float4*>(mv.tab) + memo_rec(mv, NOTH, sl, row) * (int64_t)REC4;
+    for (int i = tid; i < REC4; i += 128) Uf[i] = __ldcg(usrc + i);
   }
-  // Staging and U are dead: the region becomes the operand tiles.  They are NOT cleared: row n of an accumulator block
+  __syncthreads();                                      // (also: the mbarriers are initialised)
+  top_up(0, min(my_cnt, 32) * NI);
+  // The operand tiles are NOT cleared: row n of an accumulator block
   // depends on row n of the operands only, and rows / blocks that no entry wrote (n >= 8 NT, warps without an entry in
   // the last quad) are never folded into an output.
   tc_fence_before();
@@ -411,14 +380,13 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_wide_kernel(
   unsigned char* smem = smem_raw;
   constexpr int KT = SSVI_MEMO_KT, REC4 = NT * 2 * 2 * 32;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = lane >> 2;
   const int r8 = lane & 7, kq = lane >> 3;
   const int e = warp >> 1, h = warp & 1;                // entry slot of the pair, half of the entry's rows
   const int ngw = h ? NT - 4 : 4;                       // row groups of this warp, 2 items (k halves) each
   const int nil = 2 * ngw;
   const int64_t c = blockIdx.x;
   if (c >= n_chunks) return;
-  const int N = v.N, D = v.D, NS = smp_ns(D);
+  const int N = v.N, D = v.D;
   const int64_t row = rows[chunk_row[c]];
   const int64_t start = chunk_start[c];
   const int len = chunk_len[c], slot = chunk_slot[c];
@@ -431,8 +399,6 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_wide_kernel(
   uint64_t* done = reinterpret_cast<uint64_t*>(smem + 4 * TC_TILE_BYTES + 16384 + 2048);
   uint32_t* holder = reinterpret_cast<uint32_t*>(done + 1);
   uint32_t* cnt = holder + 1;
-  double* S = reinterpret_cast<double*>(smem);          // prologue staging (<= 51 KB at D = 64), aliased on the tiles
-  double* zs = S + v.srow_len;
 
   if (tid == 0) {
     cnt[0] = cnt[1] = 0;
@@ -457,33 +423,16 @@ __global__ void __launch_bounds__(128, 2) accumulate_tc_wide_kernel(
   };
   load_batch(0);
 
-  // ---- prologue: U(row, slot) = m + L z_own, once per CTA, written straight into the record order as floats / a ------------
-  {
-    const double2* src = reinterpret_cast<const double2*>(v.sampler[v.dim] + row * (int64_t)v.srow_len);
-    double2* dst = reinterpret_cast<double2*>(S);
-    for (int i = tid; i < (v.srow_len >> 1); i += 128) dst[i] = src[i];
-    if (z_f32) {
-      const float* zsrc = reinterpret_cast<const float*>(z_own) + (int64_t)slot * v.zblk;
-      for (int i = tid; i < v.zblk; i += 128) zs[i] = (double)zsrc[i];
-    } else {
-      const double* zsrc = reinterpret_cast<const double*>(z_own) + (int64_t)slot * v.zblk;
-      for (int i = tid; i < v.zblk; i += 128) zs[i] = zsrc[i];
-    }
-  }
-  __syncthreads();
+  // ---- prologue: U(row, slot) / a is a record of the table (MemoView::own): one copy per chunk --------------------------------
   const float alpha = mv.tc_alpha;
   const double inv_alpha = 1.0 / (double)alpha;
-  for (int i = 0; i < NT; ++i)
-#pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      double c0, c1;
-      const int t = warp + 4 * hh;
-      mma_sample_tile(S, zs, NT, NS, lane, g, i, t, c0, c1);          // x[8i + g][8t + 2q + {0,1}], q = lane & 3
-      *reinterpret_cast<float2*>(Uf + tc_rec_index(8 * i + g, 8 * t + 2 * (lane & 3))) =
-          make_float2((float)(c0 * inv_alpha), (float)(c1 * inv_alpha));
-    }
+  {
+    const float4* usrc = reinterpret_cast<const float4*>(mv.tab) + memo_rec(mv, NOTH, sl, row) * (int64_t)REC4;
+    float4* Uw = reinterpret_cast<float4*>(Uf);
+    for (int i = tid; i < REC4; i += 128) Uw[i] = __ldcg(usrc + i);
+  }
   tc_fence_before();
-  __syncthreads();                                      // U complete; staging dead: the region becomes the operand tiles
+  __syncthreads();                                      // U complete (and the mbarrier initialised)
   tc_fence_after();
   const uint32_t tmem = *holder;
 

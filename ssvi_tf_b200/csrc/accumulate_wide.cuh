@@ -31,15 +31,17 @@ __host__ __device__ inline int sample_table_wide_smem(int D, int k1) {
 }
 
 template <typename ZT>
-__global__ void __launch_bounds__(128) sample_table_wide_kernel(DevView v, MemoView mv, const ZT* __restrict__ z_other) {
+__global__ void __launch_bounds__(128) sample_table_wide_kernel(DevView v, MemoView mv, const ZT* __restrict__ z_other,
+                                                                const ZT* __restrict__ z_own) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2;
   const int D = v.D, KT = v.k1 >> 3, NS = smp_ns(D), NT = smp_nt(D);
   int jj = 0;
 #pragma unroll
-  for (int a = 1; a < SSVI_MEMO_MAX_OTH; ++a)
-    if (a < mv.n_oth && (int64_t)blockIdx.x >= mv.blk_base[a]) jj = a;
+  for (int a = 1; a <= SSVI_MEMO_MAX_OTH; ++a)
+    if (a < mv.n_modes && (int64_t)blockIdx.x >= mv.blk_base[a]) jj = a;
+  const bool own = jj == mv.n_oth;                                      // the swept mode's own samples (mv.own)
   const int64_t nblk = (mv.n_rows[jj] + 3) >> 2;                        // CTAs per slot of this mode (4 rows each)
   const int64_t local = (int64_t)blockIdx.x - mv.blk_base[jj];
   const int sl = (int)(local / nblk);
@@ -48,7 +50,7 @@ __global__ void __launch_bounds__(128) sample_table_wide_kernel(DevView v, MemoV
   double* zs = reinterpret_cast<double*>(smem_raw);
   double* S = zs + v.zblk + (size_t)warp * v.srow_len;
   {
-    const ZT* zsrc = z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
+    const ZT* zsrc = own ? z_own + (int64_t)slot * v.zblk : z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
     for (int i = tid; i < v.zblk; i += 128) zs[i] = (double)zsrc[i];
   }
   const bool live = j < mv.n_rows[jj];
@@ -75,7 +77,7 @@ __global__ void __launch_bounds__(128) sample_table_wide_kernel(DevView v, MemoV
     }
     if (mv.tab32 == 2) {                                // SSVI_TABLE_F32_TC: floats in the tensor-core path's order
       float* outf = reinterpret_cast<float*>(mv.tab) + memo_rec(mv, jj, sl, j) * (int64_t)mv.rec_len;
-      const double a = jj == 0 ? (double)mv.tc_alpha : 1.0;
+      const double a = own ? 1.0 / (double)mv.tc_alpha : (jj == 0 ? (double)mv.tc_alpha : 1.0);
 #pragma unroll
       for (int t = 0; t < 8; ++t)
         if (t < KT)

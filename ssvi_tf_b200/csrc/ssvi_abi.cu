@@ -323,7 +323,7 @@ extern "C" int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int3
   if (!h || !sweep_full_ok(h->cfg) || dim < 0 || dim >= h->cfg.order || n_slots < 1) return 0;   // diagonal: no table
   int64_t recs = 0;
   for (int d = 0; d < h->cfg.order; ++d)
-    if (d != dim) recs += h->cfg.dims[d] * (int64_t)n_slots;
+    if (d != dim || table_tc(h->cfg)) recs += h->cfg.dims[d] * (int64_t)n_slots;   // tensor-core path: + the swept mode's own samples
   return recs * memo_rec_len(h->cfg.rank, h->cfg.k1) * (int64_t)(table_f32(h->cfg) ? sizeof(float) : sizeof(double));
 }
 
@@ -341,7 +341,7 @@ static int launch_sweep(SsviHandle* h, const DevView& v, const MemoView& mv, int
     const size_t smem = (size_t)sample_table_smem(v.D, v.k1);
     auto kern = sample_table_kernel<NT, ZT>;
     CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)mv.blk_base[mv.n_oth], 256, smem, st>>>(v, mv, (const ZT*)h->z_other);
+    kern<<<(unsigned)mv.blk_base[mv.n_modes], 256, smem, st>>>(v, mv, (const ZT*)h->z_other, (const ZT*)h->z_own);
     CUDA_TRY(h, cudaGetLastError());
   }
   if (n_chunks == 0) return SSVI_OK;
@@ -441,7 +441,7 @@ static int launch_sweep_wide(SsviHandle* h, const DevView& v, const MemoView& mv
     const size_t smem = (size_t)sample_table_wide_smem(v.D, v.k1);
     auto kern = sample_table_wide_kernel<ZT>;
     CUDA_TRY(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)mv.blk_base[mv.n_oth], 128, smem, st>>>(v, mv, (const ZT*)h->z_other);
+    kern<<<(unsigned)mv.blk_base[mv.n_modes], 128, smem, st>>>(v, mv, (const ZT*)h->z_other, (const ZT*)h->z_own);
     CUDA_TRY(h, cudaGetLastError());
   }
   if (n_chunks == 0) return SSVI_OK;
@@ -580,6 +580,17 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
     blocks += ((h->cfg.dims[d] + 7) / 8) * (int64_t)n_slots;
     ++jj;
   }
+  mv.own = mv.tab32 == 2 ? 1 : 0;
+  mv.n_modes = mv.n_oth + mv.own;
+  if (mv.own) {                                         // the swept mode's own samples as one more "mode" of the table
+    mv.od[jj] = dim;
+    mv.n_rows[jj] = h->cfg.dims[dim];
+    mv.rec_base[jj] = base;
+    mv.blk_base[jj] = blocks;
+    base += h->cfg.dims[dim] * (int64_t)n_slots;
+    blocks += ((h->cfg.dims[dim] + 7) / 8) * (int64_t)n_slots;
+    ++jj;
+  }
   mv.rec_base[jj] = base;
   mv.blk_base[jj] = blocks;
   if (base >= ((int64_t)1 << 31)) return fail(h, SSVI_E_INVALID, "sweep_accumulate: too many table records; use fewer slots per call%s");
@@ -603,11 +614,11 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
   const int nt = (v.D + 7) / 8;
   if (nt > 4) {                                         // 32 < rank <= 64: accumulate_wide.cuh (4 table rows per CTA)
     int64_t blocks = 0;
-    for (int a = 0; a < mv.n_oth; ++a) {
+    for (int a = 0; a < mv.n_modes; ++a) {
       mv.blk_base[a] = blocks;
       blocks += ((mv.n_rows[a] + 3) / 4) * (int64_t)n_slots;
     }
-    mv.blk_base[mv.n_oth] = blocks;
+    mv.blk_base[mv.n_modes] = blocks;
     if (h->cfg.noise_dtype == SSVI_NOISE_F32)
       return launch_sweep_wide<float>(h, v, mv, nt, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out,
                                       entry_ids, rows, partial_out, st);

@@ -696,7 +696,9 @@ class Engine(object):
         per_slot = int(self.lib.ssvi_sweep_table_bytes(self.h, dim, 1))
         others = [d for d in range(self.N) if d != dim]
         touched = sum(self.row_window[d][1] - self.row_window[d][0] + 1 for d in others)
-        per_slot = per_slot * touched // max(sum(self.dims[d] for d in others), 1)   # the records this shard gathers
+        # the records this shard gathers (the tensor-core table also carries the swept mode's own samples: not gathered)
+        per_slot = per_slot * touched // max(sum(self.dims[d] for d in others) +
+                                             (self.dims[dim] if self.table_dtype == "f32_tc" else 0), 1)
         budget = max(self.table_budget_bytes, 1)
         if self.table_dtype == "f32_tc":
             # the tensor-core kernel waits on its gathers, not on a math pipe: it wants the tile well inside the L2

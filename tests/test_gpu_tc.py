@@ -54,7 +54,8 @@ def test_tensor_core_sweep_is_within_the_fp32_tolerance(dims, D, lik, P, W, caps
         n = dims[dim]
         acc64, _, plan64 = _run(cfg, dims, coords, vals, st0, pool, dim, W, torch.float64)
         acc_tc, state_tc, plan_tc = _run(cfg, dims, coords, vals, st0, pool, dim, W, "f32_tc")
-        assert plan_tc.table_bytes * 2 == plan64.table_bytes                      # a float table
+        # a float table, which also carries the swept mode's own samples U(row, slot)
+        assert plan_tc.table_bytes * 2 * (sum(dims) - n) == plan64.table_bytes * sum(dims)
         dev = np.abs(acc_tc - acc64).max() / np.abs(acc64).max()
         worst = max(worst, dev)
         assert dev < 2e-5, dev
