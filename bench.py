@@ -415,7 +415,8 @@ class Workload(object):
                             "fp64 contract: the FP64 pipe (37 TFLOP/s measured), not HBM, bounds this kernel; DESIGN.md 3.1"}
         tr_path = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr_path):          # DRAM bytes per unit from the committed ncu capture of this kernel
-            tr = json.load(open(tr_path)).get(self.cfg_id if self.B is None else self.cfg_id + "_b128")
+            tr = json.load(open(tr_path)).get((self.cfg_id + ("_tc" if self.table_tc else "")) if self.B is None
+                                              else self.cfg_id + "_b128")
             if tr:
                 roofline["traffic"] = tr["dram_bytes_per_unit"] * float(np.mean(acc_units))
                 roofline["traffic_source"] = tr["source"]
