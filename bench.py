@@ -75,6 +75,8 @@ SIDE_RUNS = [
     ("c5_f32_tensor_core", "c5", 1.0, {"table_tc": True}),
     ("c2_f32_tensor_core", "c2", 1.0, {"table_tc": True}),
     ("c2_rank50_f32_tensor_core", "c2", 1.0, {"rank": 50, "table_tc": True}),
+    # ... and on config 4 (diagonal covariance, closed-form weights): the fp32 instance of the entry-blocked kernel
+    ("c4_f32", "c4", 1.0, {"table_tc": True}),
 ]
 
 
@@ -324,6 +326,7 @@ class Workload(object):
                                       kernel_path=kernel_path),
                                  quadrature=quadrature)
         self.eng = self.model.engine
+        self.arith32 = bool(table_tc)                                  # the fp32 arithmetic option was asked for
         self.table_tc = bool(table_tc) and self.eng.sweep_supported and not c["diag"] and c["D"] <= 64 and c["model"] == "d"
         self.N = self.model.order
         n = torch.tensor([self.eng.nnz], device=device, dtype=torch.int64)
@@ -428,6 +431,8 @@ class Workload(object):
             return "accumulate_mma_kernel (direct evaluation, one warp per row-chunk)" if not c["diag"] and c["D"] <= 32 \
                 else "accumulate_generic_kernel"
         if c["diag"]:
+            if self.arith32 and c["model"] == "simple" and c["lik"] == "normal":
+                return "accumulate_diag_lin32_kernel (fp32 arithmetic option)"
             return "accumulate_diag_lin_kernel" if c["model"] == "simple" and c["lik"] == "normal" else \
                 ("accumulate_diag_d_kernel" if c["model"] == "d" else "accumulate_diag_kernel")
         if self.table_tc:
@@ -788,10 +793,12 @@ def main():
                              "full-row Jacobi sweeps (scale = 1)" + (", 30-node Gauss-Hermite second layer "
                                                                     "(SSVI_TF_robust quadrature=True)" if opt.get("quadrature") else "")
                              + (", sample table stored as float32 (SSVI_TABLE_F32), arithmetic fp64" if opt.get("table_f32") else "")
-                             + (", fp32 arithmetic option (SSVI_TABLE_F32_TC): float table, V / f in fp32, contraction on the "
+                             + (", fp32 arithmetic option (SSVI_TABLE_F32_TC): samples, f, weights and per-group sums in fp32 "
+                                "(accumulate_diag32.cuh), chunk accumulators and stages 3-4 fp64" if opt.get("table_tc") and cc["diag"] else
+                                ", fp32 arithmetic option (SSVI_TABLE_F32_TC): float table, V / f in fp32, contraction on the "
                                 "tcgen05 tensor cores (fp16 hi/lo split, fp32 accumulation in tensor memory), likelihood and "
                                 "stages 3-4 fp64" if opt.get("table_tc") else ""),
-                             "dtype": "f32 (tcgen05 contraction)" if opt.get("table_tc") else "f64",
+                             "dtype": ("f32 (tcgen05 contraction)" if not cc["diag"] else "f32") if opt.get("table_tc") else "f64",
                              "nnz_train": w2.eng.nnz, "steps": 2 * Nm, "warmup": Nm, "value": r2["value"], "unit": UNIT,
                              "ms_per_step": r2["ms_per_step"], "roofline_frac": r2["roofline"]["frac"],
                              "algorithmic_bytes_per_unit": r2["roofline"]["algorithmic_bytes_per_unit"],

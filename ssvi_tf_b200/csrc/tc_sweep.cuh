@@ -7,3 +7,11 @@ int ssvi_launch_accumulate_tc(const DevView& v, const MemoView& mv, int nt, int6
                               const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
                               const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own,
                               int z_f32, double* partial_out, cudaStream_t st);
+
+// The fp32 closed-form kernel of the diagonal-covariance sweep (accumulate_diag32.cuh: SSVI_TF_simple + normal likelihood
+// under SSVI_TABLE_F32_TC).  Returns a cudaError_t as int; cudaErrorInvalidValue when the shared memory does not fit.
+int ssvi_launch_accumulate_diag32(const DevView& v, int n_oth, int noise_f32, int max_smem, int64_t n_chunks,
+                                  const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
+                                  const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
+                                  const int64_t* rows, const double* w_state, const void* z_other, const void* z_own,
+                                  const void* r_w, const void* z_f, double* partial_out, cudaStream_t st);

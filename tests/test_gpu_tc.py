@@ -206,3 +206,54 @@ def test_tensor_core_sweep_at_baseline_sizes_matches_the_fp64_direct_kernel(cfg_
         np.testing.assert_allclose(got, direct, rtol=0, atol=2e-5 * np.abs(direct).max(),
                                    err_msg="%s mode %d: tensor-core sweep vs direct rows" % (cfg_id, dim))
     eng.close()
+
+
+@pytest.mark.parametrize("dims,D,P,W", [
+    ([6, 5, 4, 3], 50, 3, 64),                # config 4's shape: 4-way, rank 50
+    ([9, 7, 5], 13, 2, 5),                    # odd rank (a padded component), short segments, ragged groups of four
+    ([40, 3, 3], 64, 1, 200),                 # chunks longer than 128 entries
+    ([7, 9], 8, 4, 64),                       # one other mode
+])
+def test_fp32_option_diagonal_closed_form_kernel(dims, D, P, W, capsys):
+    """The fp32 arithmetic option on the diagonal-covariance sweep of SSVI_TF_simple + normal likelihood (BASELINE config
+    4's kernel instance; csrc/accumulate_diag32.cuh): chunk records against the fp64 kernel's, updated state (incl. the
+    w_sigma recurrence) against the oracle at the fp32 bar, counts bit-exact."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(D * 17 + P)
+    N = len(dims)
+    cfg = so.make_config("simple", "normal", D, diag=True, k1=64, k2=8, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, "normal", dims, int(0.8 * np.prod(dims)))
+    st0 = random_state(rng, cfg, dims)
+    rowptr, perm = so.build_index(coords, dims)
+    pool = so.make_tape(rng, cfg, N, P)
+    worst = 0.0
+    for dim in range(N):
+        n = dims[dim]
+        accs, states = [], []
+        for table in (torch.float64, "f32_tc"):
+            eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, sweep_chunk_entries=W,
+                         table_dtype=table)
+            eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=True))
+            engine_load_state(eng, st0)
+            plan = eng.plan_sweep(dim)
+            accs.append(eng.accumulate(plan).cpu().numpy().copy())
+            eng.step(plan)
+            eng.check_flags()
+            states.append(engine_dump_state(eng, st0))
+            eng.close()
+        dev = np.abs(accs[1] - accs[0]).max() / np.abs(accs[0]).max()
+        worst = max(worst, dev)
+        assert dev < 2e-5, dev
+        np.testing.assert_array_equal(accs[1][:, -1], accs[0][:, -1])
+        entries, tapes = [], []
+        for row in range(n):
+            ids = perm[dim][rowptr[dim][row]:rowptr[dim][row + 1]]
+            sl = np.arange(len(ids)) % P
+            tapes.append(so.Tape(pool.z_other[sl], pool.z_own[sl], pool.r_w[sl], pool.z_f[sl]))
+            entries.append((coords[ids], vals[ids]))
+        want = so.copy_state(st0)
+        so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
+        assert_state_close(states[1], want, cfg, 1e-4, what="fp32 diagonal kernel, dims=%s mode %d" % (dims, dim), atol_frac=1e-2)
+    with capsys.disabled():
+        print("\n  fp32 diagonal closed-form kernel vs fp64, largest record deviation / max |record|: %.2e (dims %s, D %d)"
+              % (worst, dims, D))
