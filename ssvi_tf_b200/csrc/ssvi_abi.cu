@@ -9,6 +9,7 @@
 #include "estimate.cuh"
 #include "row_update.cuh"
 #include "tc_sweep.cuh"
+#include <vector>
 
 #define SSVI_VERSION_STR "ssvi_b200 0.1 sm_100a"
 
@@ -96,6 +97,15 @@ extern "C" int ssvi_create(const SsviConfig* cfg, SsviHandle** out) {
 extern "C" void ssvi_destroy(SsviHandle* h) {
   if (!h) return;
   if (h->d_flags) cudaFree(h->d_flags);
+  if (h->loop_ready) {
+    cudaStreamDestroy(h->loop_stream);
+    for (int i = 0; i < 2; ++i) {
+      cudaEventDestroy(h->loop_ev_plan[i]);
+      cudaEventDestroy(h->loop_ev_free[i]);
+    }
+    cudaEventDestroy(h->loop_ev_acc);
+    cudaEventDestroy(h->loop_ev_noise);
+  }
   delete h;
 }
 
@@ -657,7 +667,15 @@ __global__ void reduce_chunks_kernel(int64_t n_rows, int acc_len, const int64_t*
   if (accumulate && c0 == c1) return;
   for (int i = threadIdx.x; i < acc_len; i += blockDim.x) {
     double s = 0.0;
-    for (int64_t c = c0; c < c1; ++c) s += partial[c * acc_len + i];
+    int64_t c = c0;
+    for (; c + 8 <= c1; c += 8) {                        // eight loads in flight, added in chunk order (same sum, bit for bit)
+      double x[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] = partial[(c + j) * acc_len + i];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += x[j];
+    }
+    for (; c < c1; ++c) s += partial[c * acc_len + i];
     acc_out[r * acc_len + i] = accumulate ? acc_out[r * acc_len + i] + s : s;
   }
 }
@@ -1070,10 +1088,13 @@ __global__ void stop_check_kernel(const double* __restrict__ hyper_out, int N, d
 
 static inline int64_t align16(int64_t x) { return (x + 15) & ~(int64_t)15; }
 
-struct LoopWs {
+struct LoopPlan {                                        // one row update's minibatch plan (plan_row_kernel writes it)
   int64_t* entry_ids;
   int32_t *chunk_row, *chunk_len, *chunk_slot0;
   int64_t *chunk_start, *rcp, *rows, *n_obs;
+};
+struct LoopWs {
+  LoopPlan plan[2];                                      // double-buffered: update u + 1 is planned while update u runs
   double *partial, *acc, *si;
   int64_t bytes;
 };
@@ -1083,14 +1104,17 @@ static LoopWs loop_ws_layout(const SsviHandle* h, int32_t B, unsigned char* base
   LoopWs w;
   int64_t o = 0;
   auto take = [&](int64_t bytes) { unsigned char* p = base + o; o += align16(bytes); return p; };
-  w.entry_ids = (int64_t*)take(8 * (int64_t)B);
-  w.chunk_row = (int32_t*)take(4 * nch);
-  w.chunk_len = (int32_t*)take(4 * nch);
-  w.chunk_slot0 = (int32_t*)take(4 * nch);
-  w.chunk_start = (int64_t*)take(8 * nch);
-  w.rcp = (int64_t*)take(16);
-  w.rows = (int64_t*)take(8);
-  w.n_obs = (int64_t*)take(8);
+  for (int b = 0; b < 2; ++b) {
+    LoopPlan& p = w.plan[b];
+    p.entry_ids = (int64_t*)take(8 * (int64_t)B);
+    p.chunk_row = (int32_t*)take(4 * nch);
+    p.chunk_len = (int32_t*)take(4 * nch);
+    p.chunk_slot0 = (int32_t*)take(4 * nch);
+    p.chunk_start = (int64_t*)take(8 * nch);
+    p.rcp = (int64_t*)take(16);
+    p.rows = (int64_t*)take(8);
+    p.n_obs = (int64_t*)take(8);
+  }
   w.partial = (double*)take(8 * nch * h->acc_len);
   w.acc = (double*)take(8 * h->acc_len);
   w.si = (double*)take(8);
@@ -1121,32 +1145,112 @@ extern "C" int ssvi_factorize_iterations(SsviHandle* h, SsviLoop* lp, int64_t fi
   const LoopWs w = loop_ws_layout(h, lp->batch_size, (unsigned char*)lp->workspace);
   cudaStream_t st = (cudaStream_t)stream;
   const int B = lp->batch_size;
+  if (!h->loop_ready) {                                 // side stream + events of the plan pipeline, once per handle
+    CUDA_TRY(h, cudaStreamCreateWithFlags(&h->loop_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      CUDA_TRY(h, cudaEventCreateWithFlags(&h->loop_ev_plan[i], cudaEventDisableTiming));
+      CUDA_TRY(h, cudaEventCreateWithFlags(&h->loop_ev_free[i], cudaEventDisableTiming));
+    }
+    CUDA_TRY(h, cudaEventCreateWithFlags(&h->loop_ev_acc, cudaEventDisableTiming));
+    CUDA_TRY(h, cudaEventCreateWithFlags(&h->loop_ev_noise, cudaEventDisableTiming));
+    h->loop_ready = true;
+  }
+  // The minibatch plan of a row update (the reference's np.random.choice, :170-174, + the chunk tables) depends on the
+  // index and the draw counter only, not on the state: it is drawn on a side stream one update AHEAD, into the other of two
+  // plan buffers, while the current update's kernels run (the sequential without-replacement draw was 18 % of a row
+  // update on the critical path).  ev_plan[b]: plan in buffer b written; ev_free[b]: the update that read buffer b done.
+  struct Upd { int d; int64_t row, len; int n, W, nch; uint64_t seed, noise_draw; };
+  auto next_upd = [&](int64_t it, int d, const int64_t* col, uint64_t draws) {
+    Upd u;
+    u.d = d;
+    u.row = col[d];
+    u.len = lp->rowptr_host[d][u.row + 1] - lp->rowptr_host[d][u.row];
+    u.n = (int)(u.len < B ? u.len : B);
+    // same chunking rule as the per-call path (engine.py:_chunk_tables): short plans are cut fine enough to spread
+    int per = (u.n + 8 * h->sm_count - 1) / (8 * h->sm_count);
+    if (per < 2) per = 2;
+    u.W = lp->chunk_entries < per ? lp->chunk_entries : per;
+    u.nch = u.n > 0 ? (u.n + u.W - 1) / u.W : 0;
+    u.seed = lp->minibatch_seed + draws;
+    (void)it;
+    return u;
+  };
+  // the schedule of this call, in order: (iteration, mode) -> row (update_column_pointer, :115, :128-133)
+  std::vector<Upd> sched;
+  sched.reserve((size_t)n_iterations * N);
+  {
+    int64_t col[SSVI_MAX_ORDER];
+    for (int d = 0; d < N; ++d) col[d] = lp->col[d];
+    uint64_t draws = lp->minibatch_draws;
+    for (int64_t it = first_iteration; it < first_iteration + n_iterations; ++it) {
+      for (int d = 0; d < N; ++d) {
+        sched.push_back(next_upd(it, d, col, ++draws));
+        sched.back().noise_draw = lp->noise_draws + (uint64_t)sched.size();   // every (iteration, mode) advances the counter
+      }
+      for (int d = 0; d < N; ++d)
+        if (++col[d] >= c.dims[d]) col[d] = 0;
+    }
+  }
+  int64_t planned = 0, n_planned_real = 0;              // schedule position planned so far; plans issued (buffer parity)
+  std::vector<int> buf_of(sched.size(), -1);
+  auto plan_ahead = [&](int64_t upto) -> int {          // issue the plans of schedule entries [planned, upto]
+    for (; planned <= upto && planned < (int64_t)sched.size(); ++planned) {
+      const Upd& u = sched[planned];
+      if (u.n <= 0) continue;
+      const int b = (int)(n_planned_real & 1);
+      if (n_planned_real >= 2) CUDA_TRY(h, cudaStreamWaitEvent(h->loop_stream, h->loop_ev_free[b], 0));
+      const LoopPlan& p = w.plan[b];
+      plan_row_kernel<<<1, 32, (size_t)2 * B * sizeof(int32_t), h->loop_stream>>>(
+          u.row, lp->rowptr[u.d], lp->perm[u.d], B, u.W, u.seed, p.entry_ids, p.chunk_row, p.chunk_start, p.chunk_len,
+          p.chunk_slot0, p.rcp, p.rows, p.n_obs);
+      CUDA_TRY(h, cudaEventRecord(h->loop_ev_plan[b], h->loop_stream));
+      buf_of[planned] = b;
+      ++n_planned_real;
+    }
+    return SSVI_OK;
+  };
+  // the plan buffers may still be read by the tail of the previous call on `st`: the side stream starts behind it
+  CUDA_TRY(h, cudaEventRecord(h->loop_ev_free[0], st));
+  CUDA_TRY(h, cudaStreamWaitEvent(h->loop_stream, h->loop_ev_free[0], 0));
   h->stop = lp->stop;
   rc = SSVI_OK;
+  int64_t pos = 0;
+  bool noise_ahead = false;                              // the next real update's variates are being drawn on the side stream
   for (int64_t it = first_iteration; it < first_iteration + n_iterations && rc == SSVI_OK; ++it) {
-    for (int d = 0; d < N && rc == SSVI_OK; ++d) {
-      const int64_t row = lp->col[d];
-      const int64_t len = lp->rowptr_host[d][row + 1] - lp->rowptr_host[d][row];
-      const int n = (int)(len < B ? len : B);
+    for (int d = 0; d < N && rc == SSVI_OK; ++d, ++pos) {
+      const Upd& u = sched[pos];
       ++lp->minibatch_draws;
       ++lp->noise_draws;                                 // every call of the reference draws, observed row or not
-      if (n > 0) {
-        // same chunking rule as the per-call path (engine.py:_chunk_tables): short plans are cut fine enough to spread
-        int per = (n + 8 * h->sm_count - 1) / (8 * h->sm_count);
-        if (per < 2) per = 2;
-        const int W = lp->chunk_entries < per ? lp->chunk_entries : per;
-        const int nch = (n + W - 1) / W;
-        plan_row_kernel<<<1, 32, (size_t)2 * B * sizeof(int32_t), st>>>(
-            row, lp->rowptr[d], lp->perm[d], B, W, lp->minibatch_seed + lp->minibatch_draws, w.entry_ids, w.chunk_row,
-            w.chunk_start, w.chunk_len, w.chunk_slot0, w.rcp, w.rows, w.n_obs);
-        rc = ssvi_fill_noise(h, lp->z_other, lp->z_own, lp->r_w, lp->z_f, lp->pool_slots, lp->noise_seed, lp->noise_draws, stream);
+      if (u.n > 0) {
+        // this update's plan and the next REAL update's (the side stream runs one plan ahead of the kernels below)
+        int64_t ahead = pos + 1;
+        while (ahead < (int64_t)sched.size() && sched[ahead].n <= 0) ++ahead;
+        rc = plan_ahead(ahead);
+        if (rc != SSVI_OK) break;
+        const int b = buf_of[pos];
+        const LoopPlan& p = w.plan[b];
+        CUDA_TRY(h, cudaStreamWaitEvent(st, h->loop_ev_plan[b], 0));
+        // this update's variates: drawn behind the previous update's accumulate on the side stream (below), except for the
+        // first real update of the call
+        if (!noise_ahead) rc = ssvi_fill_noise(h, lp->z_other, lp->z_own, lp->r_w, lp->z_f, lp->pool_slots, lp->noise_seed, u.noise_draw, stream);
+        else CUDA_TRY(h, cudaStreamWaitEvent(st, h->loop_ev_noise, 0));
         if (rc == SSVI_OK)
-          rc = ssvi_accumulate(h, d, nch, w.chunk_row, w.chunk_start, w.chunk_len, w.chunk_slot0, w.entry_ids, w.rows,
+          rc = ssvi_accumulate(h, d, u.nch, p.chunk_row, p.chunk_start, p.chunk_len, p.chunk_slot0, p.entry_ids, p.rows,
                                lp->w_state, w.partial, stream);
-        if (rc == SSVI_OK) rc = ssvi_reduce_chunks(h, 1, w.rcp, w.partial, w.acc, stream);
+        noise_ahead = false;
+        if (rc == SSVI_OK && ahead < (int64_t)sched.size()) {  // the pool is free once accumulate has read it: next draws now
+          CUDA_TRY(h, cudaEventRecord(h->loop_ev_acc, st));
+          CUDA_TRY(h, cudaStreamWaitEvent(h->loop_stream, h->loop_ev_acc, 0));
+          rc = ssvi_fill_noise(h, lp->z_other, lp->z_own, lp->r_w, lp->z_f, lp->pool_slots, lp->noise_seed,
+                               sched[ahead].noise_draw, (void*)h->loop_stream);
+          CUDA_TRY(h, cudaEventRecord(h->loop_ev_noise, h->loop_stream));
+          noise_ahead = true;
+        }
+        if (rc == SSVI_OK) rc = ssvi_reduce_chunks(h, 1, p.rcp, w.partial, w.acc, stream);
         if (rc == SSVI_OK)
-          rc = ssvi_row_update(h, d, 1, w.rows, w.acc, w.n_obs, lp->pSigma, lp->w_state, lp->time_step[d],
+          rc = ssvi_row_update(h, d, 1, p.rows, w.acc, p.n_obs, lp->pSigma, lp->w_state, lp->time_step[d],
                                lp->fixed_covariance, w.si, stream);
+        if (rc == SSVI_OK) CUDA_TRY(h, cudaEventRecord(h->loop_ev_free[b], st));
         if (rc == SSVI_OK && c.model != SSVI_MODEL_D) rc = ssvi_sigma_update(h, 1, w.si, w.acc, lp->w_state, stream);
         lp->launches += 5 + (c.model != SSVI_MODEL_D ? 1 : 0);
       }
