@@ -1213,6 +1213,10 @@ extern "C" int ssvi_factorize_iterations(SsviHandle* h, SsviLoop* lp, int64_t fi
   CUDA_TRY(h, cudaEventRecord(h->loop_ev_free[0], st));
   CUDA_TRY(h, cudaStreamWaitEvent(h->loop_stream, h->loop_ev_free[0], 0));
   h->stop = lp->stop;
+  struct StopGuard {                                     // the stop word is honoured only while this call enqueues work
+    SsviHandle* h;
+    ~StopGuard() { h->stop = nullptr; }
+  } stop_guard{h};
   rc = SSVI_OK;
   int64_t pos = 0;
   bool noise_ahead = false;                              // the next real update's variates are being drawn on the side stream
