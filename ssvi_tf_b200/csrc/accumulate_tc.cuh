@@ -138,6 +138,22 @@ __global__ void __launch_bounds__(128, (RING || PF > 2) ? 2 : 3) accumulate_tc_k
     const float4* usrc = reinterpret_cast<const float4*>(mv.tab) + memo_rec(mv, NOTH, sl, row) * (int64_t)REC4;
     for (int i = tid; i < REC4; i += 128) Uf[i] = __ldcg(usrc + i);
   }
+  constexpr int R = RING ? 1 : PF;                      // register buffers: item it of ANY entry lives in rb[it % R]
+  static_assert(RING || NI % R == 0, "2 NT must be a multiple of PF");
+  float4 rb[R][NOTH][2];
+  bool have_cur = false;                                // items 0 .. PF-1 of the entry about to be processed are in flight
+  if (!RING && my_cnt > 0) {                            // the first entry's items travel across the prologue's barrier
+#pragma unroll
+    for (int jj = 0; jj < NOTH; ++jj) {
+      const float4* p0 = reinterpret_cast<const float4*>(mv.tab) + (int64_t)__shfl_sync(0xffffffffu, my_rec[jj], 0) * REC4 + lane;
+#pragma unroll
+      for (int d = 0; d < R; ++d) {
+        rb[d][jj][0] = __ldcg(p0 + (d * 2) * 32);
+        rb[d][jj][1] = __ldcg(p0 + (d * 2 + 1) * 32);
+      }
+    }
+    have_cur = true;
+  }
   __syncthreads();                                      // (also: the mbarriers are initialised)
   top_up(0, min(my_cnt, 32) * NI);
   // The operand tiles are NOT cleared: row n of an accumulator block
@@ -157,10 +173,6 @@ __global__ void __launch_bounds__(128, (RING || PF > 2) ? 2 : 3) accumulate_tc_k
   for (int cc = 0; cc < 32; ++cc) gacc[cc] = 0.f;
 #pragma unroll
   for (int i = 0; i < NT; ++i) dacc[i] = 0.f;
-  constexpr int R = RING ? 1 : PF;                      // register buffers: item it of ANY entry lives in rb[it % R]
-  static_assert(RING || NI % R == 0, "2 NT must be a multiple of PF");
-  float4 rb[R][NOTH][2];
-  bool have_cur = false;                                // items 0 .. PF-1 of the entry about to be processed are in flight
   float w_prev = 0.f;
   bool prev_valid = false;
 
