@@ -60,8 +60,8 @@ enum { SSVI_TABLE_F64 = 0, SSVI_TABLE_F32 = 1, SSVI_TABLE_F32_TC = 2 };
  * sums are formed in fp32, the contraction G = SUM_b w_b V_b V_b^T (SSVI_TF_d.py:47-56) runs on the tcgen05 tensor cores
  * (V split into two fp16 pieces scaled by 2^tc_scale_log2, hi hi^T + hi lo^T + lo hi^T accumulated in fp32 in tensor
  * memory: csrc/accumulate_tc.cuh); likelihood derivatives, chunk records and everything from stage 3 on stay fp64.
- * SSVI_TF_d, full covariance, rank <= 64, k1 == 64.  With a DIAGONAL covariance the flag selects the fp32 instance of the
- * closed-form sweep kernel (SSVI_TF_simple + normal likelihood: csrc/accumulate_diag32.cuh).  Other configurations treat it
+ * SSVI_TF_d, full covariance, rank <= 64, k1 == 64.  With a DIAGONAL covariance the flag selects the fp32 instances of the
+ * sweep kernels of SSVI_TF_d and of SSVI_TF_simple + normal likelihood (csrc/accumulate_diag32.cuh).  Other configurations treat it
  * as SSVI_TABLE_F32 / F64. */
 
 enum {

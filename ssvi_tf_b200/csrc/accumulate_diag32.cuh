@@ -48,6 +48,35 @@ __device__ __forceinline__ void diag32_load_row(const DevView& v, int d, int32_t
   s[1] = (live && n1 < D) ? (float)src[D + n1] : 0.f;
 }
 
+// Stage the chunk's slot in shared memory as FLOATS: the N-1 noise blocks of the other modes, transposed from the pool's
+// [c][k] to [k][DP], then the own-row sample U[k][c] = m[c] + sqrt(S)[c] z_own[c][k] (ui samples,
+// SSVI_TF_interface.py:251-254), evaluated in double and rounded once.  The caller synchronises.
+template <typename ZT>
+__device__ __forceinline__ void diag32_stage_chunk(const DevView& v, float* __restrict__ zs, const ZT* __restrict__ z_other,
+                                                   const ZT* __restrict__ z_own, int slot, int64_t row, int D, int k1,
+                                                   int DP, int tid) {
+  const int N = v.N, blk_stride = k1 * DP;
+  for (int b = 0; b < N - 1; ++b) {
+    const ZT* src = z_other + ((int64_t)slot * (N - 1) + b) * v.zblk;
+    float* dst = zs + (size_t)b * blk_stride;
+    for (int idx = tid; idx < D * k1; idx += 128) {
+      const int cc = idx / k1, k = idx - cc * k1;
+      dst[k * DP + cc] = (float)src[idx];
+    }
+    if (DP != D)
+      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.f;
+  }
+  const ZT* src = z_own + (int64_t)slot * v.zblk;
+  const double* own = v.sampler[v.dim] + row * (int64_t)v.srow_len;
+  float* dst = zs + (size_t)(N - 1) * blk_stride;
+  for (int idx = tid; idx < D * k1; idx += 128) {
+    const int cc = idx / k1, k = idx - cc * k1;
+    dst[k * DP + cc] = (float)fma(own[D + cc], (double)src[idx], own[cc]);
+  }
+  if (DP != D)
+    for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.f;
+}
+
 template <int NOTH, typename ZT>
 __global__ void __launch_bounds__(128, 3) accumulate_diag_lin32_kernel(
     DevView v, int64_t n_chunks, const int32_t* __restrict__ chunk_row, const int64_t* __restrict__ chunk_start,
@@ -81,29 +110,7 @@ __global__ void __launch_bounds__(128, 3) accumulate_diag_lin32_kernel(
   int32_t my_col[NOTH];
   diag_fetch_entries<NOTH>(v, entry_ids, start, 0, my_cnt, lane, warp, od, my_y, my_col);
 
-  // ---- stage the slot: the N-1 other-mode noise blocks transposed from the pool's [c][k] to [k][DP], then the own-row
-  //      sample U[k][c] = m[c] + sqrt(S)[c] z_own[c][k] (ui samples, SSVI_TF_interface.py:251-254) ------------------------
-  for (int b = 0; b < N - 1; ++b) {
-    const ZT* src = z_other + ((int64_t)slot * (N - 1) + b) * v.zblk;
-    float* dst = zs + (size_t)b * blk_stride;
-    for (int idx = tid; idx < D * k1; idx += 128) {
-      const int cc = idx / k1, k = idx - cc * k1;
-      dst[k * DP + cc] = (float)src[idx];
-    }
-    if (DP != D)
-      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.f;
-  }
-  {
-    const ZT* src = z_own + (int64_t)slot * v.zblk;
-    const double* own = v.sampler[dim] + row * (int64_t)v.srow_len;
-    float* dst = zs + (size_t)(N - 1) * blk_stride;
-    for (int idx = tid; idx < D * k1; idx += 128) {
-      const int cc = idx / k1, k = idx - cc * k1;
-      dst[k * DP + cc] = (float)fma(own[D + cc], (double)src[idx], own[cc]);
-    }
-    if (DP != D)
-      for (int k = tid; k < k1; k += 128) dst[k * DP + D] = 0.f;
-  }
+  diag32_stage_chunk<ZT>(v, zs, z_other, z_own, slot, row, D, k1, DP, tid);
   // chunk constants (double arithmetic, once per chunk): ws_k = w_sigma^2 * rayleigh draw (SSVI_TF_interface.py:258-261),
   // ck_k = ws_k * mean_i z_f[i][k]
   for (int k = tid; k < k1; k += 128) {
@@ -201,4 +208,125 @@ __global__ void __launch_bounds__(128, 3) accumulate_diag_lin32_kernel(
     for (int k = 0; k < k1; ++k) wsum += (double)WSK[k];
   diag_write_record(v, red, partial_out + chunk_out[c] * (int64_t)v.acc_len, D, DP, len, tid, g0, g1, G0, G1,
                     -is2 * wsum * (double)max(my_cnt, 0));
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// SSVI_TF_d with a diagonal covariance under the fp32 option: accumulate_diag_d_kernel (accumulate_diag.cuh) with float
+// samples.  The weights are uniform in k (SSVI_TF_d.py:31-57, quirk Q3: the derivatives are averaged over k1, then
+// broadcast), so only sum_k v and sum_k v^2 of each entry are kept (packed f32x2, 64 terms each, folded into the chunk's
+// double accumulators with the entry's double weights); the log-likelihood derivative pair of each (entry, sample) is
+// evaluated in double on the float f, once per quarter-warp.
+// ---------------------------------------------------------------------------------------------------------------------
+__host__ __device__ inline size_t diag32_d_cta_smem(int N, int D, int k1) {
+  return (size_t)N * k1 * diag_dp(D) * 4 + 64 + (size_t)4 * (2 * diag_dp(D) + 2) * 8;
+}
+
+template <int NOTH, typename ZT>
+__global__ void __launch_bounds__(128, 3) accumulate_diag_d32_kernel(
+    DevView v, int64_t n_chunks, const int32_t* __restrict__ chunk_row, const int64_t* __restrict__ chunk_start,
+    const int32_t* __restrict__ chunk_len, const int32_t* __restrict__ chunk_slot,
+    const int64_t* __restrict__ chunk_out, const int64_t* __restrict__ entry_ids, const int64_t* __restrict__ rows,
+    const ZT* __restrict__ z_other, const ZT* __restrict__ z_own, double* __restrict__ partial_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int E = 4, T = 4;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t c = blockIdx.x;
+  if (c >= n_chunks) return;
+  const int N = v.N, D = v.D, k1 = v.k1, DP = diag_dp(D), dim = v.dim;
+  const int blk_stride = k1 * DP;
+  const int qperm = lane >> 3;
+  float* zs = reinterpret_cast<float*>(smem_raw);                        // [N][k1][DP]: other modes, then own sample
+  double* red = reinterpret_cast<double*>(smem_raw + (((size_t)N * blk_stride * 4 + 15) & ~(size_t)15));
+
+  const int64_t row = rows[chunk_row[c]];
+  const int64_t start = chunk_start[c];
+  const int len = chunk_len[c], slot = chunk_slot[c];
+
+  int od[NOTH];
+  diag_other_modes<NOTH>(N, dim, od);
+  const int my_cnt = (len - warp + 3) >> 2;             // this warp's entries: w, w+4, ...
+  double my_y;
+  int32_t my_col[NOTH];
+  diag_fetch_entries<NOTH>(v, entry_ids, start, 0, my_cnt, lane, warp, od, my_y, my_col);
+  diag32_stage_chunk<ZT>(v, zs, z_other, z_own, slot, row, D, k1, DP, tid);
+  const int n0 = 2 * lane, n1 = 2 * lane + 1;
+  const int zoff = n0 < DP ? n0 : 0;
+  __syncthreads();
+
+  double g0 = 0.0, g1 = 0.0, G0 = 0.0, G1 = 0.0;
+  const double inv_k1 = 1.0 / (double)k1;
+  const float* zo = zs + (size_t)(N - 1) * blk_stride;
+  const int e_mine = lane >> 3;
+
+  for (int b0 = 0; b0 < my_cnt; b0 += 32) {
+    const int nb = min(32, my_cnt - b0);
+    if (b0 > 0) diag_fetch_entries<NOTH>(v, entry_ids, start, b0, nb, lane, warp, od, my_y, my_col);
+    for (int el = 0; el < nb; el += E) {
+      const double y_mine = __shfl_sync(0xffffffffu, my_y, min(el + e_mine, nb - 1));
+      float2 m[E][NOTH], s[E][NOTH];
+#pragma unroll
+      for (int e = 0; e < E; ++e)
+#pragma unroll
+        for (int jj = 0; jj < NOTH; ++jj) {
+          float mm[2], ss[2];
+          diag32_load_row(v, od[jj], __shfl_sync(0xffffffffu, my_col[jj], min(el + (e ^ qperm), 31)),
+                          el + (e ^ qperm) < nb, n0, n1, D, mm, ss);
+          m[e][jj] = make_float2(mm[0], mm[1]);
+          s[e][jj] = make_float2(ss[0], ss[1]);
+        }
+      float2 sv[E], sq[E];
+#pragma unroll
+      for (int e = 0; e < E; ++e) sv[e] = sq[e] = make_float2(0.f, 0.f);
+      double sum_a = 0.0, sum_d = 0.0;
+      for (int tile2 = 0; tile2 < k1 / (2 * T); ++tile2) {
+        float fsel = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          float p[E * T];
+#pragma unroll
+          for (int kk = 0; kk < T; ++kk) {
+            const int k = (2 * tile2 + h) * T + kk;
+            float2 z[NOTH];
+#pragma unroll
+            for (int jj = 0; jj < NOTH; ++jj)
+              z[jj] = *reinterpret_cast<const float2*>(zs + (size_t)jj * blk_stride + k * DP + zoff);
+            const float2 u = *reinterpret_cast<const float2*>(zo + k * DP + zoff);
+#pragma unroll
+            for (int e = 0; e < E; ++e) {
+              float2 vv = __ffma2_rn(s[e][0], z[0], m[e][0]);
+#pragma unroll
+              for (int jj = 1; jj < NOTH; ++jj) vv = __fmul2_rn(vv, __ffma2_rn(s[e][jj], z[jj], m[e][jj]));
+              p[e * T + kk] = fmaf(u.y, vv.y, u.x * vv.x);
+              sv[e] = __fadd2_rn(sv[e], vv);
+              sq[e] = __ffma2_rn(vv, vv, sq[e]);
+            }
+          }
+          const float f = transpose_reduce16_perm_f(p, lane);
+          if ((lane & 1) == h) fsel = f;
+        }
+        double fa, fb;
+        log_pdf_derivs(v.lik, y_mine, (double)fsel, v.lik_param, fa, fb);
+        sum_a += fa;
+        sum_d += fb;
+      }
+      // SSVI_TF_d.py:31-57 (Q3): derivatives averaged over k1 (the 8 lanes of a quarter-warp hold one entry's samples)
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) {
+        sum_a += __shfl_xor_sync(0xffffffffu, sum_a, o);
+        sum_d += __shfl_xor_sync(0xffffffffu, sum_d, o);
+      }
+      const double aw_q = (sum_a * inv_k1) * inv_k1, dw_q = 0.5 * (sum_d * inv_k1) * inv_k1;
+#pragma unroll
+      for (int e = 0; e < E; ++e) {                       // slot e of this lane worked on entry e ^ qperm
+        const double aw = __shfl_sync(0xffffffffu, aw_q, (e ^ qperm) << 3);
+        const double dw = __shfl_sync(0xffffffffu, dw_q, (e ^ qperm) << 3);
+        g0 = fma(aw, (double)sv[e].x, g0);
+        g1 = fma(aw, (double)sv[e].y, g1);
+        G0 = fma(dw, (double)sq[e].x, G0);
+        G1 = fma(dw, (double)sq[e].y, G1);
+      }
+    }
+  }
+
+  diag_write_record(v, red, partial_out + chunk_out[c] * (int64_t)v.acc_len, D, DP, len, tid, g0, g1, G0, G1, 0.0);
 }

@@ -532,9 +532,11 @@ static int sweep_diag(SsviHandle* h, int32_t dim, int64_t n_chunks, const int32_
 #define SSVI_DIAG_ARGS h, v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, w_state, partial_out, st
   // closed-form weights: SSVI_TF_simple + normal likelihood (BASELINE config 4), see accumulate_diag.cuh
   const bool lin = h->cfg.model == SSVI_MODEL_SIMPLE && h->cfg.likelihood == SSVI_LIK_NORMAL;
-  if (lin && h->cfg.table_dtype == SSVI_TABLE_F32_TC && (h->cfg.k1 % 4) == 0) {     // the fp32 arithmetic option: tc_sweep.cu
+  // the fp32 arithmetic option (tc_sweep.cu): the closed-form kernel and SSVI_TF_d's; the general simple / robust kernel
+  // (k1 x k2 likelihood evaluations per entry) has no fp32 instance
+  if ((lin || !second) && h->cfg.table_dtype == SSVI_TABLE_F32_TC && (h->cfg.k1 % 8) == 0) {
     CUDA_TRY(h, (cudaError_t)ssvi_launch_accumulate_diag32(
-                    v, h->cfg.order - 1, h->cfg.noise_dtype == SSVI_NOISE_F32, h->max_smem_optin, n_chunks, chunk_row,
+                    v, lin ? 1 : 0, h->cfg.order - 1, h->cfg.noise_dtype == SSVI_NOISE_F32, h->max_smem_optin, n_chunks, chunk_row,
                     chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, w_state, h->z_other, h->z_own, h->r_w,
                     h->z_f, partial_out, st));
     return SSVI_OK;

@@ -95,12 +95,42 @@ static int launch_diag32(const DevView& v, int max_smem, int64_t n_chunks, const
   return (int)cudaGetLastError();
 }
 
-int ssvi_launch_accumulate_diag32(const DevView& v, int n_oth, int noise_f32, int max_smem, int64_t n_chunks,
+template <int NOTH, typename ZT>
+static int launch_diag_d32(const DevView& v, int max_smem, int64_t n_chunks, const int32_t* chunk_row,
+                           const int64_t* chunk_start, const int32_t* chunk_len, const int32_t* chunk_slot,
+                           const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const double*,
+                           const void* z_other, const void* z_own, const void*, const void*, double* partial_out,
+                           cudaStream_t st) {
+  const size_t smem = diag32_d_cta_smem(v.N, v.D, v.k1);
+  if (smem > (size_t)max_smem) return (int)cudaErrorInvalidValue;
+  auto kern = accumulate_diag_d32_kernel<NOTH, ZT>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  kern<<<(unsigned)n_chunks, 128, smem, st>>>(v, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids,
+                                              rows, (const ZT*)z_other, (const ZT*)z_own, partial_out);
+  return (int)cudaGetLastError();
+}
+
+int ssvi_launch_accumulate_diag32(const DevView& v, int lin, int n_oth, int noise_f32, int max_smem, int64_t n_chunks,
                                   const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
                                   const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
                                   const int64_t* rows, const double* w_state, const void* z_other, const void* z_own,
                                   const void* r_w, const void* z_f, double* partial_out, cudaStream_t st) {
 #define D32_ARGS v, max_smem, n_chunks, chunk_row, chunk_start, chunk_len, chunk_slot, chunk_out, entry_ids, rows, w_state, z_other, z_own, r_w, z_f, partial_out, st
+  if (!lin) {
+    if (noise_f32) {
+      switch (n_oth) {
+        case 1: return launch_diag_d32<1, float>(D32_ARGS);
+        case 2: return launch_diag_d32<2, float>(D32_ARGS);
+        default: return launch_diag_d32<3, float>(D32_ARGS);
+      }
+    }
+    switch (n_oth) {
+      case 1: return launch_diag_d32<1, double>(D32_ARGS);
+      case 2: return launch_diag_d32<2, double>(D32_ARGS);
+      default: return launch_diag_d32<3, double>(D32_ARGS);
+    }
+  }
   if (noise_f32) {
     switch (n_oth) {
       case 1: return launch_diag32<1, float>(D32_ARGS);

@@ -8,9 +8,9 @@ int ssvi_launch_accumulate_tc(const DevView& v, const MemoView& mv, int nt, int6
                               const int64_t* chunk_out, const int64_t* entry_ids, const int64_t* rows, const void* z_own,
                               int z_f32, double* partial_out, cudaStream_t st);
 
-// The fp32 closed-form kernel of the diagonal-covariance sweep (accumulate_diag32.cuh: SSVI_TF_simple + normal likelihood
-// under SSVI_TABLE_F32_TC).  Returns a cudaError_t as int; cudaErrorInvalidValue when the shared memory does not fit.
-int ssvi_launch_accumulate_diag32(const DevView& v, int n_oth, int noise_f32, int max_smem, int64_t n_chunks,
+// The fp32 kernels of the diagonal-covariance sweep (accumulate_diag32.cuh, under SSVI_TABLE_F32_TC).  Returns a cudaError_t as int; cudaErrorInvalidValue when the shared memory does not fit.
+// lin != 0: SSVI_TF_simple + normal likelihood (closed-form weights); lin == 0: SSVI_TF_d (w_state, r_w, z_f unused).
+int ssvi_launch_accumulate_diag32(const DevView& v, int lin, int n_oth, int noise_f32, int max_smem, int64_t n_chunks,
                                   const int32_t* chunk_row, const int64_t* chunk_start, const int32_t* chunk_len,
                                   const int32_t* chunk_slot, const int64_t* chunk_out, const int64_t* entry_ids,
                                   const int64_t* rows, const double* w_state, const void* z_other, const void* z_own,

@@ -208,21 +208,25 @@ def test_tensor_core_sweep_at_baseline_sizes_matches_the_fp64_direct_kernel(cfg_
     eng.close()
 
 
-@pytest.mark.parametrize("dims,D,P,W", [
-    ([6, 5, 4, 3], 50, 3, 64),                # config 4's shape: 4-way, rank 50
-    ([9, 7, 5], 13, 2, 5),                    # odd rank (a padded component), short segments, ragged groups of four
-    ([40, 3, 3], 64, 1, 200),                 # chunks longer than 128 entries
-    ([7, 9], 8, 4, 64),                       # one other mode
+@pytest.mark.parametrize("model,lik,dims,D,P,W", [
+    ("simple", "normal", [6, 5, 4, 3], 50, 3, 64),      # config 4's shape: 4-way, rank 50
+    ("simple", "normal", [9, 7, 5], 13, 2, 5),          # odd rank (a padded component), short segments, ragged groups of four
+    ("simple", "normal", [40, 3, 3], 64, 1, 200),       # chunks longer than 128 entries
+    ("simple", "normal", [7, 9], 8, 4, 64),             # one other mode
+    ("d", "bernoulli", [6, 5, 4, 3], 50, 3, 64),        # SSVI_TF_d: weights uniform in k (accumulate_diag_d32_kernel)
+    ("d", "poisson", [9, 7, 5], 13, 2, 5),
+    ("d", "normal", [40, 3, 3], 64, 1, 200),
 ])
-def test_fp32_option_diagonal_closed_form_kernel(dims, D, P, W, capsys):
-    """The fp32 arithmetic option on the diagonal-covariance sweep of SSVI_TF_simple + normal likelihood (BASELINE config
-    4's kernel instance; csrc/accumulate_diag32.cuh): chunk records against the fp64 kernel's, updated state (incl. the
-    w_sigma recurrence) against the oracle at the fp32 bar, counts bit-exact."""
+def test_fp32_option_diagonal_kernels(model, lik, dims, D, P, W, capsys):
+    """The fp32 arithmetic option on the diagonal-covariance sweep (csrc/accumulate_diag32.cuh): SSVI_TF_simple + normal
+    likelihood (BASELINE config 4's kernel instance, closed-form weights) and SSVI_TF_d with every likelihood.  Chunk
+    records against the fp64 kernels', updated state (incl. the w_sigma recurrence) against the oracle at the fp32 bar,
+    counts bit-exact."""
     from ssvi_tf_b200.engine import Engine, NoisePool
     rng = np.random.default_rng(D * 17 + P)
     N = len(dims)
-    cfg = so.make_config("simple", "normal", D, diag=True, k1=64, k2=8, batch_size=10 ** 9)
-    coords, vals = random_problem(rng, "normal", dims, int(0.8 * np.prod(dims)))
+    cfg = so.make_config(model, lik, D, diag=True, k1=64, k2=8, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, lik, dims, int(0.8 * np.prod(dims)))
     st0 = random_state(rng, cfg, dims)
     rowptr, perm = so.build_index(coords, dims)
     pool = so.make_tape(rng, cfg, N, P)
@@ -255,5 +259,5 @@ def test_fp32_option_diagonal_closed_form_kernel(dims, D, P, W, capsys):
         so.rows_step(want, cfg, dim, np.arange(n), entries, tapes)
         assert_state_close(states[1], want, cfg, 1e-4, what="fp32 diagonal kernel, dims=%s mode %d" % (dims, dim), atol_frac=1e-2)
     with capsys.disabled():
-        print("\n  fp32 diagonal closed-form kernel vs fp64, largest record deviation / max |record|: %.2e (dims %s, D %d)"
-              % (worst, dims, D))
+        print("\n  fp32 diagonal kernel (%s, %s) vs fp64, largest record deviation / max |record|: %.2e (dims %s, D %d)"
+              % (model, lik, worst, dims, D))
