@@ -330,7 +330,7 @@ class Workload(object):
         self.table_tc = bool(table_tc) and self.eng.sweep_supported and not c["diag"] and c["D"] <= 64 and c["model"] == "d"
         self.N = self.model.order
         n = torch.tensor([self.eng.nnz], device=device, dtype=torch.int64)
-        if sharded and world > 1:
+        if sharded and world > 1 and group is not None:                # (group None: --shard-of, one rank's shard alone)
             dist.all_reduce(n)
         self.nnz_global = int(n.item())
         if batch_size is None:
@@ -716,6 +716,8 @@ def main():
     ap.add_argument("--table-f32", action="store_true", help="headline with the sample table stored as floats (fp32 option)")
     ap.add_argument("--table-tc", action="store_true", help="headline with the fp32 arithmetic option: tcgen05 contraction (SSVI_TABLE_F32_TC)")
     ap.add_argument("--tc-scale-log2", type=int, default=0)
+    ap.add_argument("--shard-of", type=int, default=0, help="diagnostic on ONE GPU: time rank 0's shard of the global problem as "
+                    "it is cut for this many ranks (no collectives); for ncu captures of the per-rank kernel at N > 1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="diagnostic runs only")
     ap.add_argument("--no-configs", action="store_true", help="skip the side measurements of the other configs (N = 1)")
@@ -743,7 +745,11 @@ def main():
         from ssvi_tf_b200 import dist as sdist
         parity = sdist.selfcheck(group, device)
 
-    wl = Workload(args, args.config, c, device, rank, world, group, scale=args.scale,
+    shard_world = world
+    if args.shard_of > 1:                                              # diagnostic: rank 0's shard of an N-rank job, alone
+        assert world == 1, "--shard-of is a one-GPU diagnostic"
+        shard_world = args.shard_of
+    wl = Workload(args, args.config, c, device, rank, shard_world, group, scale=args.scale,
                   batch_size=args.batch_size or None, sharded=True, table_f32=args.table_f32, table_tc=args.table_tc)
     res = wl.run_resident(args.steps, args.warmup, sample_clocks=True)
     ab = {}
@@ -764,6 +770,8 @@ def main():
                "parallelism": "entries sharded x%d along index-space blocks %s; all-reduce of the row accumulators, stage 4 "
                               "on row blocks + all-gather" % (world, "x".join(map(str, wl.grid))) if world > 1 else "one GPU",
                "tuning": args.tuning, "ab_tunings": ab or None,
+               "shard_of": ("DIAGNOSTIC: rank 0's shard of the problem as cut for %d ranks, alone on one GPU (no collectives); "
+                            "value counts this shard's entries only" % args.shard_of) if args.shard_of > 1 else None,
                "setup_s": {"data": round(wl.t_data, 1), "model_and_plans": round(wl.t_plan, 1)}}
     wl.close()
     del wl

@@ -66,6 +66,7 @@ SIGNATURES = {
     "ssvi_create": (ctypes.c_int, [ctypes.POINTER(SsviConfig), ctypes.POINTER(_P)]),
     "ssvi_destroy": (None, [_P]),
     "ssvi_set_tuning": (ctypes.c_int, [_P, _I32]),
+    "ssvi_set_row_windows": (ctypes.c_int, [_P, _P, _P]),
     "ssvi_last_error": (ctypes.c_char_p, [_P]),
     "ssvi_bind_data": (ctypes.c_int, [_P, _P, _P, _I64]),
     "ssvi_bind_state": (ctypes.c_int, [_P] + [ctypes.POINTER(_P)] * 6),

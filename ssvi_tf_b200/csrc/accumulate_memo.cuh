@@ -33,7 +33,8 @@ struct MemoView {
                                           // "mode" n_oth (noise block z_own), so a chunk's prologue is one record copy
   int32_t n_modes;                        // n_oth + own: modes the sample-table kernels fill
   int32_t od[SSVI_MEMO_MAX_OTH + 1];      // other modes, ascending (+ the swept mode when own)
-  int64_t n_rows[SSVI_MEMO_MAX_OTH + 1];  // rows of each of them
+  int64_t n_rows[SSVI_MEMO_MAX_OTH + 1];  // rows of each of them the table holds: the window [row_lo, row_lo + n_rows)
+  int64_t row_lo[SSVI_MEMO_MAX_OTH + 1];  // (ssvi_set_row_windows: the index range this shard's entries touch; default: all)
   int64_t rec_base[SSVI_MEMO_MAX_OTH + 2];// first record of each mode's block; [n_modes] = total records
   int64_t blk_base[SSVI_MEMO_MAX_OTH + 2];// sample_table_kernel: first CTA of each mode (8 rows of one slot per CTA); [n_modes] = grid
   double* tab;
@@ -42,7 +43,7 @@ struct MemoView {
 __host__ __device__ inline int memo_rec_len(int D, int k1) { return smp_nt(D) * (k1 >> 3) * 64; }
 // record of (local slot sl, other-mode ordinal jj, row j)
 __device__ __forceinline__ int64_t memo_rec(const MemoView& mv, int jj, int sl, int64_t j) {
-  return mv.rec_base[jj] + (int64_t)sl * mv.n_rows[jj] + j;
+  return mv.rec_base[jj] + (int64_t)sl * mv.n_rows[jj] + (j - mv.row_lo[jj]);
 }
 
 __host__ __device__ inline int memo_stage_bytes(int D, int k1, int zsize) {
@@ -72,7 +73,8 @@ __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView m
   const int64_t nblk = (mv.n_rows[jj] + 7) >> 3;                        // CTAs per slot of this mode
   const int64_t local = (int64_t)blockIdx.x - mv.blk_base[jj];
   const int sl = (int)(local / nblk);
-  const int64_t j = (local - (int64_t)sl * nblk) * 8 + warp;
+  const int64_t jl = (local - (int64_t)sl * nblk) * 8 + warp;           // position inside the mode's row window
+  const int64_t j = mv.row_lo[jj] + jl;
   const int slot = mv.slot_lo + sl;
 
   double* zs = reinterpret_cast<double*>(smem_raw);
@@ -81,7 +83,7 @@ __global__ void __launch_bounds__(256) sample_table_kernel(DevView v, MemoView m
     const ZT* zsrc = own ? z_own + (int64_t)slot * v.zblk : z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
     for (int i = tid; i < v.zblk; i += 256) zs[i] = (double)zsrc[i];
   }
-  const bool live = j < mv.n_rows[jj];
+  const bool live = jl < mv.n_rows[jj];
   if (live) {
     const double2* src = reinterpret_cast<const double2*>(v.sampler[mv.od[jj]] + j * (int64_t)v.srow_len);
     double2* dst = reinterpret_cast<double2*>(S);

@@ -45,7 +45,8 @@ __global__ void __launch_bounds__(128) sample_table_wide_kernel(DevView v, MemoV
   const int64_t nblk = (mv.n_rows[jj] + 3) >> 2;                        // CTAs per slot of this mode (4 rows each)
   const int64_t local = (int64_t)blockIdx.x - mv.blk_base[jj];
   const int sl = (int)(local / nblk);
-  const int64_t j = (local - (int64_t)sl * nblk) * 4 + warp;
+  const int64_t jl = (local - (int64_t)sl * nblk) * 4 + warp;           // position inside the mode's row window
+  const int64_t j = mv.row_lo[jj] + jl;
   const int slot = mv.slot_lo + sl;
   double* zs = reinterpret_cast<double*>(smem_raw);
   double* S = zs + v.zblk + (size_t)warp * v.srow_len;
@@ -53,7 +54,7 @@ __global__ void __launch_bounds__(128) sample_table_wide_kernel(DevView v, MemoV
     const ZT* zsrc = own ? z_own + (int64_t)slot * v.zblk : z_other + ((int64_t)slot * mv.n_oth + jj) * v.zblk;
     for (int i = tid; i < v.zblk; i += 128) zs[i] = (double)zsrc[i];
   }
-  const bool live = j < mv.n_rows[jj];
+  const bool live = jl < mv.n_rows[jj];
   if (live) {
     const double2* src = reinterpret_cast<const double2*>(v.sampler[mv.od[jj]] + j * (int64_t)v.srow_len);
     double2* dst = reinterpret_cast<double2*>(S);

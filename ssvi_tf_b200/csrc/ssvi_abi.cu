@@ -79,6 +79,7 @@ extern "C" int ssvi_create(const SsviConfig* cfg, SsviHandle** out) {
   memset(h, 0, sizeof(*h));
   h->cfg = *cfg;
   h->acc_len = ssvi_acc_len(cfg);
+  for (int d = 0; d < cfg->order; ++d) h->win_n[d] = cfg->dims[d];      // sample-table row windows: every row
   int dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, dev);
@@ -107,6 +108,18 @@ extern "C" void ssvi_destroy(SsviHandle* h) {
     cudaEventDestroy(h->loop_ev_noise);
   }
   delete h;
+}
+
+extern "C" int ssvi_set_row_windows(SsviHandle* h, const int64_t* lo, const int64_t* n) {
+  if (!h || !lo || !n) return SSVI_E_INVALID;
+  for (int d = 0; d < h->cfg.order; ++d)
+    if (lo[d] < 0 || n[d] < 1 || lo[d] + n[d] > h->cfg.dims[d])
+      return fail(h, SSVI_E_INVALID, "set_row_windows: window outside the mode's index range%s");
+  for (int d = 0; d < h->cfg.order; ++d) {
+    h->win_lo[d] = lo[d];
+    h->win_n[d] = n[d];
+  }
+  return SSVI_OK;
 }
 
 extern "C" int ssvi_set_tuning(SsviHandle* h, int32_t tuning) {
@@ -333,7 +346,7 @@ extern "C" int64_t ssvi_sweep_table_bytes(const SsviHandle* h, int32_t dim, int3
   if (!h || !sweep_full_ok(h->cfg) || dim < 0 || dim >= h->cfg.order || n_slots < 1) return 0;   // diagonal: no table
   int64_t recs = 0;
   for (int d = 0; d < h->cfg.order; ++d)
-    if (d != dim || table_tc(h->cfg)) recs += h->cfg.dims[d] * (int64_t)n_slots;   // tensor-core path: + the swept mode's own samples
+    if (d != dim || table_tc(h->cfg)) recs += h->win_n[d] * (int64_t)n_slots;   // tensor-core path: + the swept mode's own samples
   return recs * memo_rec_len(h->cfg.rank, h->cfg.k1) * (int64_t)(table_f32(h->cfg) ? sizeof(float) : sizeof(double));
 }
 
@@ -592,22 +605,24 @@ extern "C" int ssvi_sweep_accumulate(SsviHandle* h, int32_t dim, int32_t slot_lo
   for (int d = 0; d < h->cfg.order; ++d) {
     if (d == dim) continue;
     mv.od[jj] = d;
-    mv.n_rows[jj] = h->cfg.dims[d];
+    mv.n_rows[jj] = h->win_n[d];
+    mv.row_lo[jj] = h->win_lo[d];
     mv.rec_base[jj] = base;
     mv.blk_base[jj] = blocks;
-    base += h->cfg.dims[d] * (int64_t)n_slots;
-    blocks += ((h->cfg.dims[d] + 7) / 8) * (int64_t)n_slots;
+    base += h->win_n[d] * (int64_t)n_slots;
+    blocks += ((h->win_n[d] + 7) / 8) * (int64_t)n_slots;
     ++jj;
   }
   mv.own = mv.tab32 == 2 ? 1 : 0;
   mv.n_modes = mv.n_oth + mv.own;
   if (mv.own) {                                         // the swept mode's own samples as one more "mode" of the table
     mv.od[jj] = dim;
-    mv.n_rows[jj] = h->cfg.dims[dim];
+    mv.n_rows[jj] = h->win_n[dim];
+    mv.row_lo[jj] = h->win_lo[dim];
     mv.rec_base[jj] = base;
     mv.blk_base[jj] = blocks;
-    base += h->cfg.dims[dim] * (int64_t)n_slots;
-    blocks += ((h->cfg.dims[dim] + 7) / 8) * (int64_t)n_slots;
+    base += h->win_n[dim] * (int64_t)n_slots;
+    blocks += ((h->win_n[dim] + 7) / 8) * (int64_t)n_slots;
     ++jj;
   }
   mv.rec_base[jj] = base;

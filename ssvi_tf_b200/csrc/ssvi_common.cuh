@@ -36,6 +36,8 @@ struct SsviHandle {
   const int32_t* stop;   // set only while ssvi_factorize_iterations runs: device stop word honoured by the state-writing kernels
   int sm_count;
   int max_smem_optin;
+  // sweep path: the sample table covers rows [win_lo, win_lo + win_n) of every mode (ssvi_set_row_windows; default: all)
+  int64_t win_lo[SSVI_MAX_ORDER], win_n[SSVI_MAX_ORDER];
   // ssvi_factorize_iterations: the side stream the next row update's minibatch plan is drawn on, created on first use
   cudaStream_t loop_stream;
   cudaEvent_t loop_ev_plan[2], loop_ev_free[2], loop_ev_acc, loop_ev_noise;

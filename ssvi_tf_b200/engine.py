@@ -255,6 +255,12 @@ class Engine(object):
         for d in range(self.N):
             ne = np.nonzero(np.diff(self.rowptr_h[d]))[0]
             self.row_window.append((int(ne[0]), int(ne[-1])) if len(ne) else (0, 0))
+        # ... and the sweep path samples its table for those rows only (matters for sharded runs: at 8 ranks a rank touches
+        # half of every mode of config 5, and sampling all 10k rows per mode was 5.5 % of its sweep)
+        self._win_lo = np.array([w[0] for w in self.row_window], dtype=np.int64)
+        self._win_n = np.array([w[1] - w[0] + 1 for w in self.row_window], dtype=np.int64)
+        self._call(self.lib.ssvi_set_row_windows, ctypes.c_void_p(self._win_lo.ctypes.data),
+                   ctypes.c_void_p(self._win_n.ctypes.data))
 
         # ---- state ------------------------------------------------------------------------------
         f64 = dict(device=self.device, dtype=torch.float64)
@@ -696,9 +702,10 @@ class Engine(object):
         per_slot = int(self.lib.ssvi_sweep_table_bytes(self.h, dim, 1))
         others = [d for d in range(self.N) if d != dim]
         touched = sum(self.row_window[d][1] - self.row_window[d][0] + 1 for d in others)
-        # the records this shard gathers (the tensor-core table also carries the swept mode's own samples: not gathered)
-        per_slot = per_slot * touched // max(sum(self.dims[d] for d in others) +
-                                             (self.dims[dim] if self.table_dtype == "f32_tc" else 0), 1)
+        # the records this shard gathers: the table covers the row windows only (ssvi_set_row_windows); the tensor-core
+        # table also carries the swept mode's own samples, which are read once per chunk, not gathered
+        own = (self.row_window[dim][1] - self.row_window[dim][0] + 1) if self.table_dtype == "f32_tc" else 0
+        per_slot = per_slot * touched // max(touched + own, 1)
         budget = max(self.table_budget_bytes, 1)
         if self.table_dtype == "f32_tc":
             # the tensor-core kernel waits on its gathers, not on a math pipe: it wants the tile well inside the L2

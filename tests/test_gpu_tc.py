@@ -261,3 +261,34 @@ def test_fp32_option_diagonal_kernels(model, lik, dims, D, P, W, capsys):
     with capsys.disabled():
         print("\n  fp32 diagonal kernel (%s, %s) vs fp64, largest record deviation / max |record|: %.2e (dims %s, D %d)"
               % (model, lik, worst, dims, D))
+
+
+@pytest.mark.parametrize("table", [torch.float64, "f32_tc"])
+@pytest.mark.parametrize("D", [20, 50])
+def test_sample_table_covers_the_row_window_only(table, D):
+    """A shard cut along index-space blocks touches a sub-range of every mode (ssvi_set_row_windows): the sweep path samples
+    its table for those rows only.  Entries confined to rows [2, 7) x [3, 9) x [1, 6) of a 9 x 11 x 8 tensor: smaller table,
+    and the same accumulators as the direct kernel (which uses no table) on every row."""
+    from ssvi_tf_b200.engine import Engine, NoisePool
+    rng = np.random.default_rng(3 + D)
+    dims, lo, sub, P = [9, 11, 8], [2, 3, 1], [5, 6, 5], 3
+    cfg = so.make_config("d", "bernoulli", D, diag=False, k1=64, k2=4, batch_size=10 ** 9)
+    coords, vals = random_problem(rng, "bernoulli", sub, int(0.8 * np.prod(sub)))
+    coords = coords + np.asarray(lo)[None, :]
+    st0 = random_state(rng, cfg, dims)
+    pool = so.make_tape(rng, cfg, 3, P)
+    eng = Engine(cfg, dims, coords, vals, device="cuda", noise_dtype=torch.float64, table_dtype=table, table_budget_bytes=1)
+    assert [w for w in eng.row_window] == [(l, l + n - 1) for l, n in zip(lo, sub)]
+    eng.set_noise(NoisePool.from_tape(pool, eng.device, torch.float64, diag=False))
+    engine_load_state(eng, st0)
+    rec = 8 * ((D + 7) // 8) * 64 * (4 if table == "f32_tc" else 8)               # bytes of one table record
+    for dim in range(3):
+        plan = eng.plan_sweep(dim)
+        rows_in_table = sum(sub) - (0 if table == "f32_tc" else sub[dim])         # the tensor-core table holds U as well
+        assert plan.table_bytes == rows_in_table * rec * plan.groups[0][1]
+        acc = eng.accumulate(plan).cpu().numpy().copy()
+        direct = eng.accumulate(eng.plan_full(dim)).cpu().numpy().copy()
+        eng.check_flags()
+        tol = 1e-9 if table != "f32_tc" else 2e-5
+        np.testing.assert_allclose(acc, direct, rtol=0, atol=tol * np.abs(direct).max())
+    eng.close()
