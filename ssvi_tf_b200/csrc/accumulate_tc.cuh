@@ -2,17 +2,17 @@
 // (SSVI_TABLE_F32_TC; BASELINE.json: 1e-4 in fp32) with the contraction on the tcgen05 tensor cores.
 //
 // Same slot-major sample-table scheme, chunk tables and chunk records as accumulate_memo.cuh; what differs is the
-// arithmetic.  The table holds float samples X(j, s) in the lane order of tc_rec_index (tc_ops.cuh).  One CTA (4 warps)
+// arithmetic.  The table holds float samples X(j, s) in the lane order of tc_rec_index (tc_layout.cuh).  One CTA (4 warps)
 // per chunk; warp w takes entries w, w + 4, ...  ("quad" q = the four entries 4q .. 4q + 3).  Per entry a warp
-//   * gathers the N - 1 records (two coalesced 16-byte loads per lane and item, one item ahead), forms V = Hadamard
+//   * gathers the N - 1 records (two coalesced 16-byte loads per lane and item, two items in flight), forms V = Hadamard
 //     product in fp32 registers, f_k = u_k . v_k against the own-row sample U(row, slot) (a record of the table like the
 //     others: sample_table_kernel samples the swept mode too, so a chunk's prologue is one 8 KB copy into shared memory),
 //     and the row sums SUM_k V[n][k]                                                             (SSVI_TF_d.py:31-46);
 //   * writes rows 32 w .. 32 w + 31 of the quad's operand tile: a V split into fp16 hi + lo (22 significand bits), K-major,
 //     no swizzle, straight from registers;
 //   * evaluates the k1-averaged log-likelihood derivatives in fp64 (two samples per lane; quirk Q3) -> weights aw, dw.
-// The last of the four warps to arrive (a shared-memory counter) issues, from one thread, 12 tcgen05.mma (kind::f16, M = N = 128, K = 16): per K-step
-// hi hi^T + hi lo^T + lo hi^T into a 128 x 128 fp32 accumulator in tensor memory whose diagonal 32 x 32 blocks are the
+// The last of the four warps to arrive (a shared-memory counter) issues, from one thread, 12 tcgen05.mma (kind::f16,
+// M = N = 128, K = 16): per K-step hi hi^T + hi lo^T + lo hi^T into a 128 x 128 fp32 accumulator in tensor memory whose diagonal 32 x 32 blocks are the
 // entries' V V^T (the off-diagonal blocks are the price of the 128-row minimum of the instruction; the tensor pipe has the
 // time: profiles/r3a_tc_probe.txt).  While the next quad is being formed, each warp reads ITS block of the previous
 // accumulator (tcgen05.ld: lane n gets row n) and folds it into registers with the entry's weight:
@@ -34,8 +34,8 @@
 // memory, two CTAs per SM.  It LOSES: config 5 at full size 2.11e8 against 3.37e8 entry-updates/s on the same plans
 // (profiles/r3g_bench_c5tc_ring.json): 1 KB bulk copies are served far more slowly than the 32 LDG.128 of the default path
 // move the same bytes.  An L2 prefetch of the next entry's records (prefetch.global.L2, an entry ahead) was measured too:
-// 3.19e8 against 3.32e8 (profiles/r3h).  Default: register prefetch one item ahead, 72 KB, <= 168 registers, three CTAs
-// per SM.
+// 3.19e8 against 3.32e8 (profiles/r3h).  Default: two register buffers refilled in place (PF below), 72 KB, <= 168
+// registers, three CTAs per SM.
 #define SSVI_TC_U_BYTES(NT) ((NT) * 2048)
 __host__ __device__ constexpr int tc_ring_stages(int NOTH, bool RING) { return RING ? (NOTH == 3 ? 2 : 4) : 0; }
 __host__ __device__ constexpr int tc_ring_bytes(int NOTH, bool RING) { return 4 * tc_ring_stages(NOTH, RING) * NOTH * 1024; }
