@@ -69,3 +69,59 @@ def test_single_exponential_form_equals_reference_poisson_terms():
     np.testing.assert_allclose(A[f < 0], A_ref[f < 0], rtol=5e-14)         # the reference's rounding, digit for digit
     np.testing.assert_allclose(sg, sg_ref, rtol=1e-14)
     np.testing.assert_allclose(rE1[f < 600], rE1_ref[f < 600], rtol=1e-14)
+
+
+# ---- the fp32 option's operand split (csrc/tc_ops.cuh: tc_store_split8) ---------------------------------
+
+def _split_fp16(x32):
+    hi = x32.astype(np.float16)
+    lo = (x32 - hi.astype(np.float32)).astype(np.float16)
+    return hi, lo
+
+
+def test_fp16_split_carries_22_bits():
+    """hi = rn16(x), lo = rn16(x - hi): hi + lo reproduces a float to 2^-22 relative wherever lo stays a normal half
+    (|x| >= 2^-3 here: lo's exponent is 11 below x's and fp16 normals end at 2^-14)."""
+    rng = np.random.default_rng(5)
+    x = (rng.standard_normal(200000) * np.exp2(rng.integers(-3, 6, 200000))).astype(np.float32)
+    x = x[np.abs(x) >= 2.0 ** -3]
+    hi, lo = _split_fp16(x)
+    back = hi.astype(np.float64) + lo.astype(np.float64)
+    assert np.max(np.abs(back - x) / np.abs(x)) <= 2.0 ** -22
+
+
+def test_split_contraction_meets_the_fp32_bar():
+    """V V^T the way the tensor-core kernel forms it (accumulate_tc.cuh) -- the entry's D x k1 Hadamard product in
+    fp32, split, three half x half products per K-step accumulated in fp32 (hi hi^T + hi lo^T + lo hi^T; lo lo^T
+    dropped), then G += w_b * (V V^T) with the entry's k1-averaged weight (SSVI_TF_d.py:47-56) -- against the fp64
+    contraction: far inside the 1e-4 the contract states for the fp32 option, at the ranks of the BASELINE configs."""
+    rng = np.random.default_rng(6)
+    for D, k1 in ((32, 64), (50, 64), (64, 64), (7, 64)):
+        worst = 0.0
+        for _ in range(20):
+            V = (0.3 + rng.standard_normal((D, k1))).astype(np.float32)             # Hadamard products of sampled rows
+            w = np.float32(-abs(rng.standard_normal()) - 0.1)
+            hi, lo = _split_fp16(V)
+            h32, l32 = hi.astype(np.float32), lo.astype(np.float32)
+            P = np.zeros((D, D), dtype=np.float32)
+            for s in range(0, k1, 16):                                             # one MMA K-step = 16 samples
+                sl = slice(s, s + 16)
+                P += h32[:, sl] @ h32[:, sl].T
+                P += h32[:, sl] @ l32[:, sl].T
+                P += l32[:, sl] @ h32[:, sl].T
+            G = w * P
+            ref = float(w) * (V.astype(np.float64) @ V.astype(np.float64).T)
+            worst = max(worst, np.max(np.abs(G - ref)) / np.max(np.abs(ref)))
+        assert worst < 2e-6, (D, k1, worst)
+
+
+def test_split_overflow_is_what_the_range_flag_reports():
+    """A scaled operand beyond fp16's range turns into inf in `hi` (the kernel's accumulators then hold non-finite
+    values and the call returns SSVI_FLAG_TC_RANGE); a power-of-two scale (tc_scale_log2) brings it back exactly."""
+    x = np.array([7.0e4, -1.0e5, 3.0], dtype=np.float32)
+    hi, _ = _split_fp16(x)
+    assert np.isinf(hi[:2]).all() and np.isfinite(hi[2])
+    a = np.float32(2.0 ** -4)
+    hi, lo = _split_fp16(x * a)
+    back = (hi.astype(np.float64) + lo.astype(np.float64)) / float(a)
+    assert np.all(np.abs(back - x) <= np.abs(x) * 2.0 ** -22)
