@@ -28,6 +28,13 @@ def test_header_symbols_exported_and_bound():
     assert set(_lib.SIGNATURES) == set(names)
 
 
+def test_every_entry_point_is_documented_for_the_reference_maintainer():
+    """INTEGRATION.md's table (entry point <-> the reference lines it replaces) names every symbol of the header."""
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    missing = [n for n in _declared() if n not in doc]
+    assert not missing, missing
+
+
 def test_version_and_acc_len():
     from ssvi_tf_b200 import _lib
     lib = _lib.load()
